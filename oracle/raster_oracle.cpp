@@ -569,3 +569,62 @@ void preprocess_bwd(int P, int D, int M, const R* means, const int32_t* radii, c
 }
 
 }  // namespace
+
+// ---------------------------------------------------------------------------------------------------
+// C ABI (ctypes).  Every entry point exists as <name>_f32 and <name>_f64.
+#define ORC_EXPORTS(SUF, R)                                                                                          \
+  ORC_API void orc_preprocess_fwd_##SUF(int P, int D, int M, const R* means, const R* scales, R mod, const R* rots,  \
+                                        const R* opac, const R* shs, const R* cov3D_precomp, const R* colors_precomp, \
+                                        const R* view, const R* proj, const R* campos, int W, int H, R tanx, R tany,  \
+                                        int32_t* radii, R* xy, R* depths, R* cov3Ds, R* rgb, R* conic_op,             \
+                                        uint32_t* tiles, uint8_t* clamped) {                                          \
+    preprocess_fwd<R>(P, D, M, means, scales, mod, rots, opac, shs, cov3D_precomp, colors_precomp, view, proj,       \
+                      campos, W, H, tanx, tany, radii, xy, depths, cov3Ds, rgb, conic_op, tiles, clamped);            \
+  }                                                                                                                  \
+  ORC_API void orc_binning_##SUF(int P, int W, int H, const R* xy, const R* depths, const int32_t* radii,            \
+                                 const uint32_t* tiles, uint64_t* keys_sorted, uint32_t* vals_sorted,                 \
+                                 uint32_t* ranges) {                                                                  \
+    binning<R>(P, W, H, xy, depths, radii, tiles, keys_sorted, vals_sorted, ranges);                                 \
+  }                                                                                                                  \
+  ORC_API void orc_render_fwd_##SUF(int W, int H, int F, const uint32_t* ranges, const uint32_t* point_list,         \
+                                    const R* xy, const R* feat, const R* lang, const R* depths, const R* conic_op,    \
+                                    const R* bg, int include_feature, R* final_T, uint32_t* n_contrib, R* out_color,  \
+                                    R* out_lang, R* out_depth) {                                                      \
+    render_fwd<R>(W, H, F, ranges, point_list, xy, feat, lang, depths, conic_op, bg, include_feature, final_T,       \
+                  n_contrib, out_color, out_lang, out_depth);                                                        \
+  }                                                                                                                  \
+  ORC_API void orc_render_bwd_##SUF(int W, int H, int F, const uint32_t* ranges, const uint32_t* point_list,         \
+                                    const R* bg, const R* xy, const R* conic_op, const R* colors, const R* lang,      \
+                                    const R* depths, const R* final_T, const uint32_t* n_contrib, const R* dpix,      \
+                                    const R* dpix_F, const R* dpix_depth, int include_feature, double* g_mean2D,      \
+                                    double* g_conic, double* g_opacity, double* g_color, double* g_lang,              \
+                                    double* g_depth) {                                                                \
+    render_bwd<R>(W, H, F, ranges, point_list, bg, xy, conic_op, colors, lang, depths, final_T, n_contrib, dpix,     \
+                  dpix_F, dpix_depth, include_feature, g_mean2D, g_conic, g_opacity, g_color, g_lang, g_depth);      \
+  }                                                                                                                  \
+  ORC_API void orc_cov2d_bwd_##SUF(int P, const R* means, const int32_t* radii, const R* cov3Ds, int W, int H,       \
+                                   R tanx, R tany, const R* view, const R* dL_dconic3, R* dL_dmeans, R* dL_dcov) {   \
+    const R fy = H / (2 * tany), fx = W / (2 * tanx);                                                                \
+    cov2d_bwd<R>(P, means, radii, cov3Ds, fx, fy, tanx, tany, view, dL_dconic3, dL_dmeans, dL_dcov);                 \
+  }                                                                                                                  \
+  ORC_API void orc_preprocess_bwd_##SUF(int P, int D, int M, const R* means, const int32_t* radii, const R* shs,     \
+                                        const uint8_t* clamped, const R* scales, const R* rots, R mod, const R* view, \
+                                        const R* proj, const R* campos, const R* dL_dmean2D, R* dL_dmeans,            \
+                                        const R* dL_dcolor, const R* dL_ddepth, const R* dL_dcov3D, R* dL_dsh,        \
+                                        R* dL_dscale, R* dL_drot) {                                                   \
+    preprocess_bwd<R>(P, D, M, means, radii, shs, clamped, scales, rots, mod, view, proj, campos, dL_dmean2D,        \
+                      dL_dmeans, dL_dcolor, dL_ddepth, dL_dcov3D, dL_dsh, dL_dscale, dL_drot);                       \
+  }
+
+ORC_EXPORTS(f32, float)
+ORC_EXPORTS(f64, double)
+
+// rasterizer_impl.cu:54-66 checkFrustum / auxiliary.h:139-164
+ORC_API void orc_mark_visible_f32(int P, const float* means, const float* view, uint8_t* present) {
+  for (int i = 0; i < P; ++i) {
+    V3<float> p = {means[3 * i], means[3 * i + 1], means[3 * i + 2]};
+    present[i] = xform4x3(p, view).z > 0.2f;
+  }
+}
+
+ORC_API uint32_t orc_higher_msb(uint32_t n) { return higher_msb(n); }
