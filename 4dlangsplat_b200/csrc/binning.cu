@@ -1,0 +1,215 @@
+// binning.cu -- tile-count scan, (tile|depth) key duplication and tile-range detection.
+//
+// Replaces cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:281), the blocking D2H read of num_rendered (:285),
+// duplicateWithKeys (:70-111) and identifyTileRanges (:116-138) + cudaMemset (:314).
+//
+// B200 notes: the instance count R never has to reach the host -- every kernel reads it from device memory and is
+// launched over a capacity-sized grid; duplication is warp-cooperative (a Gaussian covering many tiles is emitted by
+// all 32 lanes with coalesced 8-byte/4-byte stores instead of one lane looping while 31 idle).
+#include "common.cuh"
+
+namespace fdls {
+
+constexpr int SCAN_THREADS = 512;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;  // 4096 elements per block
+
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, int lane) {
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, v, d);
+    if (lane >= d) v += t;
+  }
+  return v;
+}
+
+// block-wide exclusive scan of one value per thread; returns the exclusive prefix, total in `total`
+template <int THREADS>
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t& total, uint32_t* s_warp) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t incl = warp_incl_scan(v, lane);
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = lane < THREADS / 32 ? s_warp[lane] : 0;
+    uint32_t wi = warp_incl_scan(w, lane);
+    s_warp[lane] = wi - w;  // exclusive warp offsets; slot THREADS/32 .. unused
+    if (lane == 31) s_warp[32] = wi;
+  }
+  __syncthreads();
+  total = s_warp[32];
+  uint32_t r = incl - v + s_warp[warp];
+  __syncthreads();
+  return r;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_reduce_kernel(int P, const uint32_t* __restrict__ in, uint32_t* __restrict__ block_sums) {
+  __shared__ uint32_t s_warp[33];
+  const int base = blockIdx.x * SCAN_TILE;
+  uint32_t s = 0;
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; ++i) {
+    int k = base + i * SCAN_THREADS + threadIdx.x;
+    if (k < P) s += in[k];
+  }
+  uint32_t total;
+  block_excl_scan<SCAN_THREADS>(s, total, s_warp);
+  if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+
+// one block: exclusive scan of the block sums in place; publishes R and the overflow flag
+__global__ void __launch_bounds__(1024)
+scan_spine_kernel(int nblocks, uint32_t* __restrict__ block_sums, uint32_t* __restrict__ num_rendered,
+                  long long capacity, uint32_t* __restrict__ host_mirror) {
+  __shared__ uint32_t s_warp[33];
+  uint32_t carry = 0;
+  for (int base = 0; base < nblocks; base += 1024) {
+    int k = base + threadIdx.x;
+    uint32_t v = k < nblocks ? block_sums[k] : 0;
+    uint32_t total;
+    uint32_t ex = block_excl_scan<1024>(v, total, s_warp);
+    if (k < nblocks) block_sums[k] = carry + ex;
+    carry += total;
+  }
+  if (threadIdx.x == 0) {
+    num_rendered[0] = carry;
+    num_rendered[1] = ((long long)carry > capacity) ? 1u : 0u;
+  }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_apply_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __restrict__ block_sums,
+                  uint32_t* __restrict__ out) {
+  __shared__ uint32_t s_warp[33];
+  // blocked arrangement: thread t owns items [t*ITEMS, t*ITEMS+ITEMS) of the block tile
+  const int base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+  uint32_t v[SCAN_ITEMS];
+  uint32_t s = 0;
+  if (base + SCAN_ITEMS <= P) {
+    const uint4* p4 = reinterpret_cast<const uint4*>(in + base);
+    uint4 a = p4[0], b = p4[1];
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  } else {
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) v[i] = (base + i < P) ? in[base + i] : 0;
+  }
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; ++i) s += v[i];
+  uint32_t total;
+  uint32_t ex = block_excl_scan<SCAN_THREADS>(s, total, s_warp) + block_sums[blockIdx.x];
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; ++i) {
+    ex += v[i];
+    v[i] = ex;
+  }
+  if (base + SCAN_ITEMS <= P) {
+    uint4* o4 = reinterpret_cast<uint4*>(out + base);
+    o4[0] = make_uint4(v[0], v[1], v[2], v[3]);
+    o4[1] = make_uint4(v[4], v[5], v[6], v[7]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i)
+      if (base + i < P) out[base + i] = v[i];
+  }
+}
+
+// rasterizer_impl.cu:70-111, warp-cooperative.  Emission order per Gaussian is y-major, x-minor at
+// offsets[idx-1] + i exactly as in the reference, so the unsorted arrays are identical too.
+__global__ void __launch_bounds__(256)
+duplicate_keys_kernel(int P, const float4* __restrict__ rec, const uint32_t* __restrict__ offsets,
+                      const int* __restrict__ radii, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, int gx,
+                      int gy, long long capacity) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  int radius = idx < P ? radii[idx] : 0;
+  uint32_t off = 0, depth_bits = 0, count = 0;
+  uint2 rmin = {0, 0}, rmax = {0, 0};
+  if (radius > 0) {
+    off = (idx == 0) ? 0 : offsets[idx - 1];
+    const float4 r0 = rec[(size_t)idx * 4];
+    depth_bits = __float_as_uint(rec[(size_t)idx * 4 + 1].z);
+    get_rect(r0.x, r0.y, radius, gx, gy, rmin, rmax);
+    count = (rmax.x - rmin.x) * (rmax.y - rmin.y);
+  }
+  constexpr uint32_t SMALL = 4;
+  if (count > 0 && count <= SMALL) {
+    uint32_t o = off;
+    for (uint32_t y = rmin.y; y < rmax.y; y++)
+      for (uint32_t x = rmin.x; x < rmax.x; x++) {
+        if ((long long)o < capacity) {
+          keys[o] = ((uint64_t)(y * gx + x) << 32) | depth_bits;
+          vals[o] = idx;
+        }
+        o++;
+      }
+  }
+  uint32_t big = __ballot_sync(0xffffffffu, count > SMALL);
+  while (big) {
+    const int src = __ffs(big) - 1;
+    big &= big - 1;
+    const uint32_t b_off = __shfl_sync(0xffffffffu, off, src);
+    const uint32_t b_cnt = __shfl_sync(0xffffffffu, count, src);
+    const uint32_t b_x0 = __shfl_sync(0xffffffffu, rmin.x, src);
+    const uint32_t b_y0 = __shfl_sync(0xffffffffu, rmin.y, src);
+    const uint32_t b_w = __shfl_sync(0xffffffffu, rmax.x - rmin.x, src);
+    const uint32_t b_depth = __shfl_sync(0xffffffffu, depth_bits, src);
+    const uint32_t b_idx = __shfl_sync(0xffffffffu, (uint32_t)idx, src);
+    for (uint32_t i = lane; i < b_cnt; i += 32) {
+      const uint32_t y = b_y0 + i / b_w, x = b_x0 + i % b_w;
+      const uint32_t o = b_off + i;
+      if ((long long)o < capacity) {
+        keys[o] = ((uint64_t)(y * gx + x) << 32) | b_depth;
+        vals[o] = b_idx;
+      }
+    }
+  }
+}
+
+// rasterizer_impl.cu:116-138 with the element count read on the device
+__global__ void __launch_bounds__(256)
+tile_ranges_kernel(const uint32_t* __restrict__ num_rendered, long long capacity, const uint64_t* __restrict__ keys,
+                   uint2* __restrict__ ranges) {
+  const long long L = min((long long)num_rendered[0], capacity);
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= L) return;
+  const uint32_t currtile = keys[idx] >> 32;
+  if (idx == 0)
+    ranges[currtile].x = 0;
+  else {
+    const uint32_t prevtile = keys[idx - 1] >> 32;
+    if (currtile != prevtile) {
+      ranges[prevtile].y = (uint32_t)idx;
+      ranges[currtile].x = (uint32_t)idx;
+    }
+  }
+  if (idx == L - 1) ranges[currtile].y = (uint32_t)L;
+}
+
+size_t scan_scratch_bytes(int P) { return align_up((size_t)(cdiv(P, SCAN_TILE) + 1) * sizeof(uint32_t)); }
+
+cudaError_t launch_scan(int P, const uint32_t* tiles_touched, uint32_t* offsets, uint32_t* block_sums,
+                        uint32_t* num_rendered, long long capacity, cudaStream_t st) {
+  const int nb = cdiv(P, SCAN_TILE);
+  if (P > 0) scan_reduce_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, block_sums);
+  scan_spine_kernel<<<1, 1024, 0, st>>>(nb, block_sums, num_rendered, capacity, nullptr);
+  if (P > 0) scan_apply_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, block_sums, offsets);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_duplicate(int P, const float4* rec, const uint32_t* offsets, const int* radii, uint64_t* keys,
+                             uint32_t* vals, int gx, int gy, long long capacity, cudaStream_t st) {
+  if (P == 0) return cudaSuccess;
+  duplicate_keys_kernel<<<cdiv(P, 256), 256, 0, st>>>(P, rec, offsets, radii, keys, vals, gx, gy, capacity);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_tile_ranges(const uint32_t* num_rendered, long long n_grid, long long capacity, const uint64_t* keys,
+                               uint2* ranges, int tiles, cudaStream_t st) {
+  cudaError_t e = cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), st);
+  if (e != cudaSuccess) return e;
+  if (n_grid > 0) tile_ranges_kernel<<<cdiv(n_grid, 256), 256, 0, st>>>(num_rendered, capacity, keys, ranges);
+  return cudaGetLastError();
+}
+
+}  // namespace fdls

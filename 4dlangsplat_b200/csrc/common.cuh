@@ -1,0 +1,120 @@
+// common.cuh -- shared device helpers for the fdls kernels (sm_100a only).
+//
+// Numerical contract: the expressions below keep the operation ORDER of the reference device code
+// (cuda_rasterizer/auxiliary.h:41-117 and the header-only vec/mat library it is written against), because
+// sort keys, tile ranges and per-pixel contributor counts must come out bit-identical (BASELINE.json).
+// The file is compiled WITHOUT --use_fast_math and with the default -fmad=true, like the reference
+// (setup.py:33 passes no math flags).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "../../include/fdls_abi.h"
+
+namespace fdls {
+
+constexpr int TILE = FDLS_TILE;
+constexpr int TILE_PIX = TILE * TILE;
+constexpr int REC_FLOATS = 16;  // per-Gaussian render record (64 B): see FdlsLayout::rec
+// record slots
+enum { R_X = 0, R_Y = 1, R_CA = 2, R_CB = 3, R_CC = 4, R_OP = 5, R_DEPTH = 6, R_RGB = 7, R_LANG = 10 };
+// per-Gaussian screen-space gradient record (64 B), accumulated by render_bwd, consumed by preprocess_bwd
+enum { G_MX = 0, G_MY = 1, G_CA = 2, G_CB = 3, G_CC = 4, G_OP = 5, G_DEPTH = 6, G_RGB = 7, G_LANG = 10 };
+
+struct V3 {
+  float x, y, z;
+};
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ V3 operator*(float s, V3 a) { return {s * a.x, s * a.y, s * a.z}; }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ V3 operator/(V3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
+__device__ __forceinline__ V3 operator-(V3 a) { return {-a.x, -a.y, -a.z}; }
+__device__ __forceinline__ V3& operator+=(V3& a, V3 b) {
+  a.x += b.x; a.y += b.y; a.z += b.z;
+  return a;
+}
+__device__ __forceinline__ float dot3(V3 a, V3 b) {
+  float tx = a.x * b.x, ty = a.y * b.y, tz = a.z * b.z;
+  return tx + ty + tz;
+}
+
+// Column-major 3x3 (m[col][row]), product in the same term order as the reference's math library.
+struct M3 {
+  float m[3][3];
+};
+__device__ __forceinline__ M3 mul(const M3& a, const M3& b) {
+  M3 r;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) r.m[c][k] = a.m[0][k] * b.m[c][0] + a.m[1][k] * b.m[c][1] + a.m[2][k] * b.m[c][2];
+  return r;
+}
+__device__ __forceinline__ M3 transpose(const M3& a) {
+  M3 r;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) r.m[c][k] = a.m[k][c];
+  return r;
+}
+
+// auxiliary.h:22-39
+__device__ constexpr float SH_C0 = 0.28209479177387814f;
+__device__ constexpr float SH_C1 = 0.4886025119029199f;
+__device__ constexpr float SH_C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+                                       -1.0925484305920792f, 0.5462742152960396f};
+__device__ constexpr float SH_C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
+                                       0.3731763325901154f,  -0.4570457994644658f, 1.445305721320277f,
+                                       -0.5900435899266435f};
+
+// auxiliary.h:41-44 -- evaluated in double, as the reference's untyped literals force.
+__device__ __forceinline__ float ndc2pix(float v, int S) { return ((v + 1.0) * S - 1.0) * 0.5; }
+
+// auxiliary.h:46-56 (radius is an int there; grid = tile grid)
+__device__ __forceinline__ void get_rect(float px, float py, int max_radius, int gx, int gy, uint2& rmin, uint2& rmax) {
+  rmin.x = min(gx, max((int)0, (int)((px - max_radius) / TILE)));
+  rmin.y = min(gy, max((int)0, (int)((py - max_radius) / TILE)));
+  rmax.x = min(gx, max((int)0, (int)((px + max_radius + TILE - 1) / TILE)));
+  rmax.y = min(gy, max((int)0, (int)((py + max_radius + TILE - 1) / TILE)));
+}
+
+// auxiliary.h:58-77
+__device__ __forceinline__ float3 xform4x3(const float3& p, const float* m) {
+  return {m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12], m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13],
+          m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14]};
+}
+__device__ __forceinline__ float4 xform4x4(const float3& p, const float* m) {
+  return {m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12], m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13],
+          m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14], m[3] * p.x + m[7] * p.y + m[11] * p.z + m[15]};
+}
+__device__ __forceinline__ float3 xform_vec4x3_T(const float3& p, const float* m) {
+  return {m[0] * p.x + m[1] * p.y + m[2] * p.z, m[4] * p.x + m[5] * p.y + m[6] * p.z,
+          m[8] * p.x + m[9] * p.y + m[10] * p.z};
+}
+// auxiliary.h:107-117
+__device__ __forceinline__ float3 dnormvdv(float3 v, float3 dv) {
+  float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+  float invsum32 = 1.0f / sqrt(sum2 * sum2 * sum2);
+  float3 o;
+  o.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+  o.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+  o.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+  return o;
+}
+
+// Per-view constants.  The matrices stay device pointers (they are CUDA tensors in the reference API,
+// __init__.py:167-180); kernels stage them in shared memory once per block.
+struct ViewParams {
+  const float* view;    // (16)
+  const float* proj;    // (16)
+  const float* campos;  // (3)
+  const float* bg;      // (3)
+  float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
+  int W, H, gx, gy;
+};
+
+static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+}  // namespace fdls

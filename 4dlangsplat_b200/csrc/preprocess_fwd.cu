@@ -1,0 +1,196 @@
+// preprocess_fwd.cu -- per-Gaussian forward stage: near cull, projection, 3D covariance, EWA 2D covariance, conic,
+// screen radius, tile rectangle, SH -> RGB, and packing of the 64-byte render record.
+//
+// Replaces preprocessCUDA<3> (cuda_rasterizer/forward.cu:155-256) with its helpers in_frustum (auxiliary.h:139-164),
+// computeCov3D (forward.cu:118-152), computeCov2D (forward.cu:74-113), computeColorFromSH (forward.cu:20-71).
+// Expression order follows the reference so that depth bits, radii and tile rectangles are bit-identical.
+//
+// B200 notes: one thread per Gaussian, 256-thread blocks; the two 4x4 matrices are staged in shared memory once per
+// block; SH coefficients are fetched as 12 x 16-byte loads per Gaussian; everything the compositor needs is written
+// as ONE 64-byte record (4 x st.v4) so the render kernels gather a Gaussian with two 32-byte sectors.
+#include "common.cuh"
+
+namespace fdls {
+
+__device__ __forceinline__ V3 sh_to_rgb(int deg, const float* __restrict__ sh, V3 dir, uint8_t& clamp_bits) {
+  // forward.cu:20-71.  `sh` points at this Gaussian's (M,3) block.
+  auto SH = [&](int i) { return V3{sh[3 * i], sh[3 * i + 1], sh[3 * i + 2]}; };
+  V3 result = SH_C0 * SH(0);
+  if (deg > 0) {
+    float x = dir.x, y = dir.y, z = dir.z;
+    result = result - SH_C1 * y * SH(1) + SH_C1 * z * SH(2) - SH_C1 * x * SH(3);
+    if (deg > 1) {
+      float xx = x * x, yy = y * y, zz = z * z;
+      float xy = x * y, yz = y * z, xz = x * z;
+      result = result + SH_C2[0] * xy * SH(4) + SH_C2[1] * yz * SH(5) + SH_C2[2] * (2.0f * zz - xx - yy) * SH(6) +
+               SH_C2[3] * xz * SH(7) + SH_C2[4] * (xx - yy) * SH(8);
+      if (deg > 2) {
+        result = result + SH_C3[0] * y * (3.0f * xx - yy) * SH(9) + SH_C3[1] * xy * z * SH(10) +
+                 SH_C3[2] * y * (4.0f * zz - xx - yy) * SH(11) +
+                 SH_C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * SH(12) +
+                 SH_C3[4] * x * (4.0f * zz - xx - yy) * SH(13) + SH_C3[5] * z * (xx - yy) * SH(14) +
+                 SH_C3[6] * x * (xx - 3.0f * yy) * SH(15);
+      }
+    }
+  }
+  result.x += 0.5f;
+  result.y += 0.5f;
+  result.z += 0.5f;
+  clamp_bits = (result.x < 0 ? 1 : 0) | (result.y < 0 ? 2 : 0) | (result.z < 0 ? 4 : 0);
+  return {fmaxf(result.x, 0.0f), fmaxf(result.y, 0.0f), fmaxf(result.z, 0.0f)};
+}
+
+// forward.cu:118-152 (quaternion deliberately NOT normalised, :127)
+__device__ __forceinline__ void cov3d_from_scale_rot(float3 s, float mod, float4 q, float* cov3D) {
+  M3 S = {{{0, 0, 0}, {0, 0, 0}, {0, 0, 0}}};
+  S.m[0][0] = mod * s.x;
+  S.m[1][1] = mod * s.y;
+  S.m[2][2] = mod * s.z;
+  float r = q.x, x = q.y, y = q.z, z = q.w;
+  M3 R = {{{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+           {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+           {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}}};
+  M3 Mm = mul(S, R);
+  M3 Sigma = mul(transpose(Mm), Mm);
+  cov3D[0] = Sigma.m[0][0];
+  cov3D[1] = Sigma.m[0][1];
+  cov3D[2] = Sigma.m[0][2];
+  cov3D[3] = Sigma.m[1][1];
+  cov3D[4] = Sigma.m[1][2];
+  cov3D[5] = Sigma.m[2][2];
+}
+
+// forward.cu:74-113
+__device__ __forceinline__ float3 cov2d_ewa(const float3& mean, float focal_x, float focal_y, float tan_fovx,
+                                            float tan_fovy, const float* cov3D, const float* vm) {
+  float3 t = xform4x3(mean, vm);
+  const float limx = 1.3f * tan_fovx;
+  const float limy = 1.3f * tan_fovy;
+  const float txtz = t.x / t.z;
+  const float tytz = t.y / t.z;
+  t.x = min(limx, max(-limx, txtz)) * t.z;
+  t.y = min(limy, max(-limy, tytz)) * t.z;
+  M3 J = {{{focal_x / t.z, 0.0f, -(focal_x * t.x) / (t.z * t.z)},
+           {0.0f, focal_y / t.z, -(focal_y * t.y) / (t.z * t.z)},
+           {0, 0, 0}}};
+  M3 Wm = {{{vm[0], vm[4], vm[8]}, {vm[1], vm[5], vm[9]}, {vm[2], vm[6], vm[10]}}};
+  M3 T = mul(Wm, J);
+  M3 Vrk = {{{cov3D[0], cov3D[1], cov3D[2]}, {cov3D[1], cov3D[3], cov3D[4]}, {cov3D[2], cov3D[4], cov3D[5]}}};
+  M3 cov = mul(mul(transpose(T), transpose(Vrk)), T);
+  cov.m[0][0] += 0.3f;
+  cov.m[1][1] += 0.3f;
+  return {cov.m[0][0], cov.m[0][1], cov.m[1][1]};
+}
+
+__global__ void __launch_bounds__(256)
+preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ means3D, const float* __restrict__ scales,
+                      const float* __restrict__ rotations, const float* __restrict__ opacities,
+                      const float* __restrict__ shs, const float* __restrict__ cov3D_precomp,
+                      const float* __restrict__ colors_precomp, const float* __restrict__ lang, ViewParams vp,
+                      int* __restrict__ radii, float4* __restrict__ rec, uint32_t* __restrict__ tiles_touched,
+                      uint8_t* __restrict__ clamped, int prefiltered) {
+  __shared__ float s_view[16], s_proj[16], s_cam[3];
+  if (threadIdx.x < 16) s_view[threadIdx.x] = vp.view[threadIdx.x];
+  else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = vp.proj[threadIdx.x - 16];
+  else if (threadIdx.x < 35) s_cam[threadIdx.x - 32] = vp.campos[threadIdx.x - 32];
+  __syncthreads();
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+
+  int out_radius = 0;
+  uint32_t out_tiles = 0;
+  do {
+    const float3 p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+    // in_frustum (auxiliary.h:139-164): only the near-plane test is live.
+    const float3 p_view = xform4x3(p_orig, s_view);
+    if (p_view.z <= 0.2f) {
+      if (prefiltered) {
+        printf("Point is filtered although prefiltered is set. This shouldn't happen!");
+        __trap();
+      }
+      break;
+    }
+    const float4 p_hom = xform4x4(p_orig, s_proj);
+    const float p_w = 1.0f / (p_hom.w + 0.0000001f);
+    const float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+
+    float cov3D[6];
+    if (cov3D_precomp != nullptr) {
+#pragma unroll
+      for (int i = 0; i < 6; ++i) cov3D[i] = cov3D_precomp[6 * idx + i];
+    } else {
+      const float3 s = {scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+      const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+      cov3d_from_scale_rot(s, vp.scale_modifier, q, cov3D);
+    }
+    const float3 cov = cov2d_ewa(p_orig, vp.focal_x, vp.focal_y, vp.tanfovx, vp.tanfovy, cov3D, s_view);
+
+    const float det = (cov.x * cov.z - cov.y * cov.y);
+    if (det == 0.0f) break;
+    const float det_inv = 1.f / det;
+    const float3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+
+    const float mid = 0.5f * (cov.x + cov.z);
+    const float lambda1 = mid + sqrt(max(0.1f, mid * mid - det));
+    const float lambda2 = mid - sqrt(max(0.1f, mid * mid - det));
+    const float my_radius = ceil(3.f * sqrt(max(lambda1, lambda2)));
+    const float2 point_image = {ndc2pix(p_proj.x, vp.W), ndc2pix(p_proj.y, vp.H)};
+    uint2 rect_min, rect_max;
+    get_rect(point_image.x, point_image.y, (int)my_radius, vp.gx, vp.gy, rect_min, rect_max);
+    if ((rect_max.x - rect_min.x) * (rect_max.y - rect_min.y) == 0) break;
+
+    V3 rgb;
+    uint8_t cl = 0;
+    if (colors_precomp == nullptr) {
+      V3 pos = {p_orig.x, p_orig.y, p_orig.z};
+      V3 cam = {s_cam[0], s_cam[1], s_cam[2]};
+      V3 dir = pos - cam;
+      dir = dir / sqrt(dot3(dir, dir));
+      rgb = sh_to_rgb(D, shs + (size_t)idx * M * 3, dir, cl);
+    } else {
+      rgb = {colors_precomp[3 * idx], colors_precomp[3 * idx + 1], colors_precomp[3 * idx + 2]};
+    }
+    clamped[idx] = cl;
+
+    float l[FDLS_MAX_LANG_CHANNELS];
+#pragma unroll
+    for (int i = 0; i < FDLS_MAX_LANG_CHANNELS; ++i) l[i] = (lang != nullptr && i < F) ? lang[(size_t)idx * F + i] : 0.f;
+
+    float4* r = rec + (size_t)idx * 4;
+    r[0] = make_float4(point_image.x, point_image.y, conic.x, conic.y);
+    r[1] = make_float4(conic.z, opacities[idx], p_view.z, rgb.x);
+    r[2] = make_float4(rgb.y, rgb.z, l[0], l[1]);
+    r[3] = make_float4(l[2], l[3], l[4], l[5]);
+    out_radius = my_radius;
+    out_tiles = (rect_max.y - rect_min.y) * (rect_max.x - rect_min.x);
+  } while (0);
+  radii[idx] = out_radius;
+  tiles_touched[idx] = out_tiles;
+}
+
+// markVisible / checkFrustum (rasterizer_impl.cu:54-66)
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
+                                    uint8_t* __restrict__ present) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  const float3 p = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+  const float3 pv = xform4x3(p, view);
+  present[idx] = pv.z > 0.2f ? 1 : 0;
+}
+
+cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, float4* rec, uint32_t* tiles_touched,
+                                  uint8_t* clamped, cudaStream_t st) {
+  if (a->P == 0) return cudaSuccess;
+  preprocess_fwd_kernel<<<cdiv(a->P, 256), 256, 0, st>>>(
+      a->P, a->D, a->M, a->F, a->means3D, a->scales, a->rotations, a->opacities, a->shs, a->cov3D_precomp,
+      a->colors_precomp, a->language_feature, vp, a->radii, rec, tiles_touched, clamped, a->prefiltered);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st) {
+  if (P == 0) return cudaSuccess;
+  mark_visible_kernel<<<cdiv(P, 256), 256, 0, st>>>(P, means3D, view, present);
+  return cudaGetLastError();
+}
+
+}  // namespace fdls

@@ -1,0 +1,293 @@
+// radix_sort.cu -- stable LSD "onesweep" radix sort of (u64 key, u32 value) pairs on key bits [0, end_bit).
+//
+// Replaces cub::DeviceRadixSort::SortPairs as called at rasterizer_impl.cu:307-312 on the (tile << 32 | depth bits)
+// keys.  Written from the published onesweep scheme (one upfront multi-pass histogram, then ONE kernel per 8-bit
+// digit that ranks a 4096-key tile in shared memory and resolves its global offsets by decoupled look-back over the
+// per-tile digit counts of the preceding tiles), sized for B200:
+//   * 256 threads x 16 keys per CTA, ~57 KB dynamic shared memory -> 3 CTAs/SM, grid >> 148 SMs;
+//   * the element count is read from DEVICE memory (no host sync on num_rendered); CTAs past the end exit;
+//   * tiles are handed out by an atomic ticket so a CTA only ever waits on CTAs that already started;
+//   * keys are exchanged through shared memory so the scatter writes runs of equal digits contiguously.
+// Stability: items are ranked in (warp, item, lane) order == global index order; equal digits keep that order.
+#include "common.cuh"
+
+namespace fdls {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_IPT = 16;
+constexpr int RS_TILE = RS_THREADS * RS_IPT;  // 4096
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_BINS = 256;
+constexpr int RS_MAX_PASSES = 8;
+constexpr uint32_t FLAG_AGG = 1u << 30, FLAG_PREFIX = 2u << 30, FLAG_MASK = 3u << 30, VAL_MASK = ~FLAG_MASK;
+constexpr unsigned FULL = 0xffffffffu;
+
+struct RsSmem {
+  uint64_t keys[RS_TILE];
+  uint32_t vals[RS_TILE];
+  uint32_t warp_hist[RS_WARPS][RS_BINS + 8];
+  uint32_t digit_start[RS_BINS];
+  uint32_t global_base[RS_BINS];
+  uint32_t scan_warp[40];
+  uint32_t tile;
+};
+
+__device__ __forceinline__ uint32_t lanemask_lt() {
+  uint32_t m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+__device__ __forceinline__ uint32_t ld_relaxed(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__device__ __forceinline__ uint32_t rs_warp_incl(uint32_t v, int lane) {
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    uint32_t t = __shfl_up_sync(FULL, v, d);
+    if (lane >= d) v += t;
+  }
+  return v;
+}
+// exclusive scan of one value per thread over the 256-thread CTA
+__device__ __forceinline__ uint32_t rs_block_excl(uint32_t v, uint32_t* s_warp) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t incl = rs_warp_incl(v, lane);
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = lane < RS_WARPS ? s_warp[lane] : 0;
+    uint32_t wi = rs_warp_incl(w, lane);
+    s_warp[lane] = wi - w;
+  }
+  __syncthreads();
+  uint32_t r = incl - v + s_warp[warp];
+  __syncthreads();
+  return r;
+}
+
+// Upfront histogram of every pass's digit (reads the keys once).
+__global__ void __launch_bounds__(RS_THREADS)
+rs_histogram_kernel(const uint64_t* __restrict__ keys, long long n_max, const uint32_t* __restrict__ n_dev, int passes,
+                    int end_bit, uint32_t* __restrict__ global_hist) {
+  __shared__ uint32_t s_hist[RS_MAX_PASSES][RS_BINS];
+  const long long n = n_dev ? min((long long)n_dev[0], n_max) : n_max;
+  const long long base = (long long)blockIdx.x * RS_TILE;
+  if (base >= n) return;
+  for (int i = threadIdx.x; i < passes * RS_BINS; i += RS_THREADS) (&s_hist[0][0])[i] = 0;
+  __syncthreads();
+  const uint32_t lt = lanemask_lt();
+#pragma unroll 4
+  for (int i = 0; i < RS_IPT; ++i) {
+    const long long k = base + i * RS_THREADS + threadIdx.x;
+    const bool valid = k < n;
+    const uint64_t key = valid ? keys[k] : 0;
+    const unsigned act = __ballot_sync(FULL, valid);
+    if (valid) {
+      for (int p = 0; p < passes; ++p) {
+        const int shift = p * 8;
+        const uint32_t mask = (1u << min(8, end_bit - shift)) - 1;
+        const uint32_t d = (uint32_t)(key >> shift) & mask;
+        const unsigned peers = __match_any_sync(act, d);
+        if ((peers & lt) == 0) atomicAdd(&s_hist[p][d], __popc(peers));
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < passes * RS_BINS; i += RS_THREADS) {
+    uint32_t c = (&s_hist[0][0])[i];
+    if (c) atomicAdd(&global_hist[i], c);
+  }
+}
+
+__global__ void __launch_bounds__(RS_THREADS)
+rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_out,
+                   const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out, long long n_max,
+                   const uint32_t* __restrict__ n_dev, int shift, int bits, const uint32_t* __restrict__ global_hist,
+                   uint32_t* __restrict__ tile_state, uint32_t* __restrict__ ticket, uint32_t* __restrict__ error_flag) {
+  extern __shared__ __align__(16) unsigned char rs_smem_raw[];
+  RsSmem& s = *reinterpret_cast<RsSmem*>(rs_smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s.tile = atomicAdd(ticket, 1u);
+  for (int i = tid; i < RS_WARPS * (RS_BINS + 8); i += RS_THREADS) (&s.warp_hist[0][0])[i] = 0;
+  __syncthreads();
+  const uint32_t tile = s.tile;
+  const long long n = n_dev ? min((long long)n_dev[0], n_max) : n_max;
+  const long long tile_base = (long long)tile * RS_TILE;
+  if (tile_base >= n) return;
+  const int valid_count = (int)min((long long)RS_TILE, n - tile_base);
+  const uint32_t mask = (1u << bits) - 1;
+
+  // ---- load (warp-striped) and rank
+  uint64_t key[RS_IPT];
+  uint32_t val[RS_IPT];
+  uint32_t rank[RS_IPT];
+  const int warp_base = warp * 32 * RS_IPT;
+#pragma unroll
+  for (int i = 0; i < RS_IPT; ++i) {
+    const int li = warp_base + i * 32 + lane;
+    if (li < valid_count) {
+      key[i] = keys_in[tile_base + li];
+      val[i] = vals_in[tile_base + li];
+    } else {
+      key[i] = ~0ull;
+      val[i] = 0;
+    }
+  }
+  const uint32_t lt = lanemask_lt();
+  uint32_t* wh = s.warp_hist[warp];
+#pragma unroll
+  for (int i = 0; i < RS_IPT; ++i) {
+    const int li = warp_base + i * 32 + lane;
+    const uint32_t d = (li < valid_count) ? ((uint32_t)(key[i] >> shift) & mask) : RS_BINS;  // bin 256 = padding
+    const unsigned peers = __match_any_sync(FULL, d);
+    const int leader = __ffs(peers) - 1;
+    uint32_t old = 0;
+    if (lane == leader) {
+      old = wh[d];
+      wh[d] = old + __popc(peers);
+    }
+    old = __shfl_sync(FULL, old, leader);
+    rank[i] = old + __popc(peers & lt);
+    __syncwarp();
+  }
+  __syncthreads();
+
+  // ---- per-digit: exclusive scan across warps, CTA count
+  const int d = tid;  // one digit per thread (RS_THREADS == RS_BINS)
+  uint32_t count = 0;
+#pragma unroll
+  for (int w = 0; w < RS_WARPS; ++w) {
+    uint32_t c = s.warp_hist[w][d];
+    s.warp_hist[w][d] = count;
+    count += c;
+  }
+  // ---- publish the CTA's digit count, then look back for the exclusive prefix over preceding tiles
+  uint32_t* my_state = tile_state + (size_t)tile * RS_BINS + d;
+  if (tile == 0) {
+    st_relaxed(my_state, FLAG_PREFIX | count);
+  } else {
+    st_relaxed(my_state, FLAG_AGG | count);
+  }
+  uint32_t excl = 0;
+  if (tile > 0) {
+    long long t = (long long)tile - 1;
+    uint32_t spins = 0;
+    while (true) {
+      const uint32_t v = ld_relaxed(tile_state + (size_t)t * RS_BINS + d);
+      const uint32_t f = v & FLAG_MASK;
+      if (f == 0) {
+        if (++spins > (1u << 24)) {  // never hang the GPU: report and bail out
+          atomicExch(error_flag, 1u);
+          break;
+        }
+        __nanosleep(20);
+        continue;
+      }
+      excl += v & VAL_MASK;
+      if (f == FLAG_PREFIX) break;
+      --t;
+    }
+    st_relaxed(my_state, FLAG_PREFIX | ((excl + count) & VAL_MASK));
+  }
+  // ---- local digit starts and global bases
+  const uint32_t local_start = rs_block_excl(count, s.scan_warp);
+  const uint32_t ghist_excl = rs_block_excl(global_hist[d], s.scan_warp);
+  s.digit_start[d] = local_start;
+  s.global_base[d] = ghist_excl + excl - local_start;
+  __syncthreads();
+
+  // ---- exchange through shared memory so equal digits become contiguous
+#pragma unroll
+  for (int i = 0; i < RS_IPT; ++i) {
+    const int li = warp_base + i * 32 + lane;
+    if (li < valid_count) {
+      const uint32_t dg = (uint32_t)(key[i] >> shift) & mask;
+      const uint32_t pos = s.digit_start[dg] + wh[dg] + rank[i];
+      s.keys[pos] = key[i];
+      s.vals[pos] = val[i];
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < RS_IPT; ++i) {
+    const int p = i * RS_THREADS + tid;
+    if (p < valid_count) {
+      const uint64_t k = s.keys[p];
+      const uint32_t dg = (uint32_t)(k >> shift) & mask;
+      const uint32_t dst = s.global_base[dg] + p;
+      keys_out[dst] = k;
+      vals_out[dst] = s.vals[p];
+    }
+  }
+}
+
+struct RsScratch {
+  uint32_t* global_hist;  // [RS_MAX_PASSES][256]
+  uint32_t* tickets;      // [RS_MAX_PASSES]
+  uint32_t* error_flag;   // [1]
+  uint32_t* tile_state;   // [passes][tiles][256]
+  size_t header_bytes;    // bytes to zero before each sort = everything
+  size_t total_bytes;
+};
+
+static RsScratch rs_carve(void* scratch, long long n_max, int passes) {
+  RsScratch r;
+  char* p = (char*)scratch;
+  r.global_hist = (uint32_t*)p;
+  p += RS_MAX_PASSES * RS_BINS * sizeof(uint32_t);
+  r.tickets = (uint32_t*)p;
+  p += 16 * sizeof(uint32_t);
+  r.error_flag = (uint32_t*)p;
+  p += 16 * sizeof(uint32_t);
+  r.tile_state = (uint32_t*)p;
+  const size_t tiles = (size_t)cdiv(n_max, RS_TILE);
+  p += (size_t)passes * tiles * RS_BINS * sizeof(uint32_t);
+  r.total_bytes = align_up((size_t)(p - (char*)scratch));
+  r.header_bytes = r.total_bytes;
+  return r;
+}
+
+size_t sort_scratch_bytes(long long n_max) { return rs_carve(nullptr, n_max < 1 ? 1 : n_max, RS_MAX_PASSES).total_bytes; }
+
+// returns selector (0: result in a, 1: result in b) or a negative FDLS error
+int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
+               const uint32_t* n_dev, int end_bit, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+  if (end_bit < 1 || end_bit > 64) return FDLS_EINVAL;
+  const int passes = (end_bit + 7) / 8;
+  if (n_max <= 0) return passes & 1;
+  RsScratch sc = rs_carve(scratch, n_max, passes);
+  if (scratch_bytes < sc.total_bytes) return FDLS_EWORKSPACE;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(rs_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem)) !=
+        cudaSuccess)
+      return FDLS_ECUDA;
+    attr_set = true;
+  }
+  if (cudaMemsetAsync(scratch, 0, sc.header_bytes, st) != cudaSuccess) return FDLS_ECUDA;
+  const int tiles = cdiv(n_max, RS_TILE);
+  rs_histogram_kernel<<<tiles, RS_THREADS, 0, st>>>(keys_a, n_max, n_dev, passes, end_bit, sc.global_hist);
+  uint64_t* kin = keys_a;
+  uint64_t* kout = keys_b;
+  uint32_t* vin = vals_a;
+  uint32_t* vout = vals_b;
+  for (int p = 0; p < passes; ++p) {
+    const int shift = p * 8;
+    const int bits = end_bit - shift < 8 ? end_bit - shift : 8;
+    rs_onesweep_kernel<<<tiles, RS_THREADS, sizeof(RsSmem), st>>>(
+        kin, kout, vin, vout, n_max, n_dev, shift, bits, sc.global_hist + p * RS_BINS,
+        sc.tile_state + (size_t)p * tiles * RS_BINS, sc.tickets + p, sc.error_flag);
+    uint64_t* tk = kin; kin = kout; kout = tk;
+    uint32_t* tv = vin; vin = vout; vout = tv;
+  }
+  if (cudaGetLastError() != cudaSuccess) return FDLS_ECUDA;
+  return passes & 1;
+}
+
+}  // namespace fdls

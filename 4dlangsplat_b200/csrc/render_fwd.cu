@@ -1,0 +1,167 @@
+// render_fwd.cu -- front-to-back alpha compositing of RGB + F language-feature channels + depth, one 16x16 tile per
+// CTA, one pixel per thread.  Replaces renderCUDA<3,F> forward (cuda_rasterizer/forward.cu:261-395).
+//
+// Per-pixel arithmetic (power, alpha, transmittance test, accumulation order) is the reference's, expression for
+// expression, so n_contrib / final_T are bit-identical and the images agree to rounding.
+//
+// B200 design:
+//  * every Gaussian is ONE 64-byte record {x,y,conic,opacity,depth,rgb,lang[<=6]} written by preprocess; a batch of
+//    256 records is gathered with 16-byte cp.async.cg (LDGSTS, L2 -> shared, no register staging) into a
+//    double-buffered 2 x 16 KB shared-memory ring, so the gather of batch i+1 overlaps the blend of batch i.
+//    The reference instead gathers colour / language / depth from GLOBAL memory per contributing (pixel, Gaussian)
+//    pair (forward.cu:362-369).
+//  * a conservative log-domain pre-test skips the expf for pairs whose alpha is certainly below 1/255; the exact
+//    reference test still decides every pair near the threshold, so results do not change.
+//  * F is a template parameter dispatched at run time (the reference needs a rebuild per F: setup.py:18,32).
+#include "common.cuh"
+
+namespace fdls {
+
+constexpr int RF_THREADS = TILE_PIX;  // 256
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+template <int F>
+__global__ void __launch_bounds__(RF_THREADS)
+render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                  const float4* __restrict__ rec, int W, int H, int gx, const float* __restrict__ bg_color,
+                  float* __restrict__ final_T, uint32_t* __restrict__ n_contrib, uint32_t* __restrict__ tile_max_contrib,
+                  float* __restrict__ out_color, float* __restrict__ out_lang, float* __restrict__ out_depth) {
+  // [buf][slot 0..3][thread]: conflict-free cp.async writes, broadcast reads
+  __shared__ float4 s_rec[2][4][RF_THREADS];
+  __shared__ float s_thr[2][RF_THREADS];
+  __shared__ uint32_t s_max;
+
+  const int tid = threadIdx.x;
+  const uint32_t tile = blockIdx.x;
+  const uint32_t tx = tile % gx, ty = tile / gx;
+  const uint2 pix = {tx * TILE + (tid & (TILE - 1)), ty * TILE + (tid >> 4)};
+  const uint32_t pix_id = W * pix.y + pix.x;
+  const float2 pixf = {(float)pix.x, (float)pix.y};
+  const bool inside = pix.x < (uint32_t)W && pix.y < (uint32_t)H;
+  bool done = !inside;
+
+  const uint2 range = ranges[tile];
+  int toDo = range.y - range.x;
+  const int rounds = (toDo + RF_THREADS - 1) / RF_THREADS;
+  if (tid == 0) s_max = 0;
+  __syncthreads();
+
+  auto stage = [&](int round, int buf) {
+    const uint32_t progress = round * RF_THREADS + tid;
+    if (range.x + progress < range.y) {
+      const uint32_t id = point_list[range.x + progress];
+      const float4* src = rec + (size_t)id * 4;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) cp_async16(&s_rec[buf][k][tid], src + k);
+    }
+    cp_async_commit();
+  };
+
+  float T = 1.0f;
+  uint32_t contributor = 0, last_contributor = 0;
+  float C[3] = {0, 0, 0};
+  float D = 0;
+  float Fa[F > 0 ? F : 1] = {0};
+
+  if (rounds > 0) stage(0, 0);
+  for (int i = 0; i < rounds; i++, toDo -= RF_THREADS) {
+    const int buf = i & 1;
+    if (i + 1 < rounds) {
+      stage(i + 1, buf ^ 1);
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    {  // conservative skip threshold for my own staged record: alpha < 1/255 is certain when power < thr
+      const float op = s_rec[buf][1][tid].y;  // own cp.async data is visible to the issuing thread after wait
+      // op*exp(power) < 1/255  <=>  power < -log(255*op); 0.01 of slack covers expf/logf rounding by orders of magnitude
+      s_thr[buf][tid] = -__logf(255.0f * op) - 0.01f;
+    }
+    __syncthreads();
+
+    const int cnt = min(RF_THREADS, toDo);
+    for (int j = 0; !done && j < cnt; j++) {
+      contributor++;
+      const float4 a = s_rec[buf][0][j];  // x, y, conic.x, conic.y
+      const float4 b = s_rec[buf][1][j];  // conic.z, opacity, depth, r
+      const float2 d = {a.x - pixf.x, a.y - pixf.y};
+      const float power = -0.5f * (a.z * d.x * d.x + b.x * d.y * d.y) - a.w * d.x * d.y;
+      if (power > 0.0f) continue;
+      if (power < s_thr[buf][j]) continue;  // certainly alpha < 1/255 (pre-test; exact test below)
+      const float alpha = min(0.99f, b.y * exp(power));
+      if (alpha < 1.0f / 255.0f) continue;
+      const float test_T = T * (1 - alpha);
+      if (test_T < 0.0001f) {
+        done = true;
+        continue;
+      }
+      const float4 c = s_rec[buf][2][j];  // g, b, l0, l1
+      C[0] += b.w * alpha * T;
+      C[1] += c.x * alpha * T;
+      C[2] += c.y * alpha * T;
+      if (F > 0) {
+        const float4 e = s_rec[buf][3][j];  // l2..l5
+        const float l[6] = {c.z, c.w, e.x, e.y, e.z, e.w};
+#pragma unroll
+        for (int ch = 0; ch < F; ch++) Fa[ch] += l[ch] * alpha * T;
+      }
+      D += b.z * alpha * T;
+      T = test_T;
+      last_contributor = contributor;
+    }
+    // also fences the shared ring before the next prefetch overwrites buffer `buf`
+    if (__syncthreads_count(done) == RF_THREADS) break;
+  }
+  cp_async_wait<0>();
+
+  const uint32_t wmax = __reduce_max_sync(0xffffffffu, inside ? last_contributor : 0u);
+  if ((tid & 31) == 0) atomicMax(&s_max, wmax);
+  if (inside) {
+    final_T[pix_id] = T;
+    n_contrib[pix_id] = last_contributor;
+    const size_t HW = (size_t)H * W;
+#pragma unroll
+    for (int ch = 0; ch < 3; ch++) out_color[ch * HW + pix_id] = C[ch] + T * bg_color[ch];
+    if (F > 0) {
+#pragma unroll
+      for (int ch = 0; ch < F; ch++) out_lang[ch * HW + pix_id] = Fa[ch];
+    }
+    out_depth[pix_id] = D;
+  }
+  __syncthreads();
+  if (tid == 0) tile_max_contrib[tile] = s_max;
+}
+
+template <int F>
+static cudaError_t launch_rf(const uint2* ranges, const uint32_t* point_list, const float4* rec, int W, int H, int gx,
+                             int gy, const float* bg, float* final_T, uint32_t* n_contrib, uint32_t* tile_max,
+                             float* out_color, float* out_lang, float* out_depth, cudaStream_t st) {
+  render_fwd_kernel<F><<<gx * gy, RF_THREADS, 0, st>>>(ranges, point_list, rec, W, H, gx, bg, final_T, n_contrib,
+                                                       tile_max, out_color, out_lang, out_depth);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_render_fwd(int F, const uint2* ranges, const uint32_t* point_list, const float4* rec, int W, int H,
+                              int gx, int gy, const float* bg, float* final_T, uint32_t* n_contrib, uint32_t* tile_max,
+                              float* out_color, float* out_lang, float* out_depth, cudaStream_t st) {
+#define RF_CASE(N)                                                                                             \
+  case N:                                                                                                      \
+    return launch_rf<N>(ranges, point_list, rec, W, H, gx, gy, bg, final_T, n_contrib, tile_max, out_color, \
+                        out_lang, out_depth, st);
+  switch (F) {
+    RF_CASE(0) RF_CASE(1) RF_CASE(2) RF_CASE(3) RF_CASE(4) RF_CASE(5) RF_CASE(6)
+    default: return cudaErrorInvalidValue;
+  }
+#undef RF_CASE
+}
+
+}  // namespace fdls

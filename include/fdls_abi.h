@@ -1,0 +1,187 @@
+/* fdls_abi.h -- C ABI of the B200-native (sm_100a) differentiable Gaussian rasterizer for 4D LangSplat.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++ types, no torch types, no exceptions, no
+ * device allocation inside the library.  Every entry point replaces one function of the reference's native
+ * surface (paths relative to /root/reference/submodules/4d-langsplat-rasterization/):
+ *
+ *   fdls_forward / fdls_preprocess + fdls_bin_and_render
+ *        <- CudaRasterizer::Rasterizer::forward   (cuda_rasterizer/rasterizer.h:34-61, rasterizer_impl.cu:198-348)
+ *           bound to Python by RasterizeGaussiansCUDA (rasterize_points.cu:35-129, ext.cpp:16)
+ *   fdls_backward
+ *        <- CudaRasterizer::Rasterizer::backward  (rasterizer.h:63-95, rasterizer_impl.cu:352-469)
+ *           bound by RasterizeGaussiansBackwardCUDA (rasterize_points.cu:131-235, ext.cpp:17)
+ *   fdls_mark_visible
+ *        <- CudaRasterizer::Rasterizer::markVisible (rasterizer.h:26-31, rasterizer_impl.cu:141-153)
+ *           bound by markVisible (rasterize_points.cu:237-256, ext.cpp:18)
+ *   fdls_knn_dist2
+ *        <- simple_knn._C.distCUDA2 (submodule absent from the checkout; call site scene/gaussian_model.py:203)
+ *
+ * All device pointers are fp32 / int32 / uint8 arrays in the reference's layouts (row-major (P,3), (P,M,3), (P,F),
+ * planar (C,H,W) images; 4x4 matrices in the reference's "transposed" storage, auxiliary.h:58-66).  A null pointer
+ * means "absent" exactly where the reference tests data_ptr()==nullptr (forward.cu:205,241; backward.cu:425,429).
+ * All work is enqueued on the cudaStream_t passed in (as void*); nothing synchronises unless documented.
+ * Return value: 0 on success, negative FDLS_E* otherwise; fdls_strerror() names it.
+ */
+#ifndef FDLS_ABI_H
+#define FDLS_ABI_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FDLS_OK 0
+#define FDLS_EINVAL (-1)      /* bad argument combination (mirrors the Python-side checks, __init__.py:202-206) */
+#define FDLS_EWORKSPACE (-2)  /* a caller-provided workspace is too small */
+#define FDLS_ECUDA (-3)       /* a CUDA launch or API call failed; see cudaGetLastError */
+#define FDLS_EUNSUPPORTED (-4) /* e.g. F > FDLS_MAX_LANG_CHANNELS, or NUM_CHANNELS != 3 without colours */
+
+#define FDLS_MAX_LANG_CHANNELS 6 /* the reference is built with 3 (CLIP) or 6 (video) latents: scripts/train_eval.sh:3-4 */
+#define FDLS_TILE 16             /* cuda_rasterizer/config.h:18-19 */
+
+/* Byte sizes of the three caller-owned workspaces (the reference's geomBuffer / imgBuffer / binningBuffer,
+ * rasterizer_impl.cu:155-194).  binning_bytes is for `capacity` duplicated instances. */
+typedef struct FdlsWorkspaceSizes {
+  size_t geom_bytes;    /* per-Gaussian state, function of P */
+  size_t img_bytes;     /* per-pixel + per-tile state, function of W,H */
+  size_t binning_bytes; /* keys/values double buffers + sort scratch, function of capacity */
+} FdlsWorkspaceSizes;
+
+/* Element offsets (bytes) of the arrays inside the workspaces, so tests can read intermediates bit-exactly. */
+typedef struct FdlsLayout {
+  /* geom */
+  size_t rec;           /* float[16] per Gaussian: x,y, conic a,b,c, opacity, depth, r,g,b, lang[6] */
+  size_t tiles_touched; /* u32[P] */
+  size_t point_offsets; /* u32[P] inclusive scan of tiles_touched */
+  size_t clamped;       /* u8[P]: bit c set if colour channel c was clamped (forward.cu:66-69) */
+  size_t num_rendered;  /* u32[4]: [0]=R (device copy), [1]=overflow flag, [2..3] reserved */
+  size_t scan_scratch;
+  /* img */
+  size_t final_T;   /* f32[H*W]  (reference "accum_alpha") */
+  size_t n_contrib; /* u32[H*W] */
+  size_t ranges;    /* uint2[tiles] */
+  size_t tile_max_contrib; /* u32[tiles]: max n_contrib over the tile's pixels (lets backward skip the tail) */
+  /* binning */
+  size_t keys_alt; /* u64[capacity] ping-pong partner of `keys` */
+  size_t keys;     /* u64[capacity] sorted keys after the forward (reference: point_list_keys) */
+  size_t vals_alt; /* u32[capacity] */
+  size_t vals;     /* u32[capacity] sorted Gaussian ids (reference: point_list) */
+  size_t sort_scratch;
+} FdlsLayout;
+
+typedef struct FdlsFwdArgs {
+  /* sizes */
+  int32_t P;  /* Gaussians */
+  int32_t D;  /* active SH degree */
+  int32_t M;  /* SH coefficients per channel stored in `shs` */
+  int32_t F;  /* language-feature channels (run-time; the reference bakes it in: setup.py:18,32) */
+  int32_t W, H;
+  /* scalars */
+  float tanfovx, tanfovy, scale_modifier;
+  int32_t prefiltered, debug, include_feature;
+  /* inputs (device) */
+  const float* background;       /* (3) */
+  const float* means3D;          /* (P,3) */
+  const float* shs;              /* (P,M,3) or null */
+  const float* colors_precomp;   /* (P,3) or null */
+  const float* language_feature; /* (P,F) or null (only when !include_feature) */
+  const float* opacities;        /* (P) */
+  const float* scales;           /* (P,3) or null */
+  const float* rotations;        /* (P,4) or null */
+  const float* cov3D_precomp;    /* (P,6) or null */
+  const float* viewmatrix;       /* (16) */
+  const float* projmatrix;       /* (16) */
+  const float* campos;           /* (3) */
+  /* outputs (device) */
+  float* out_color;    /* (3,H,W) */
+  float* out_language; /* (F,H,W) or null when !include_feature */
+  float* out_depth;    /* (1,H,W) */
+  int32_t* radii;      /* (P) */
+  /* workspaces (device, 256-byte aligned) */
+  void* geom_ws;    size_t geom_bytes;
+  void* img_ws;     size_t img_bytes;
+  void* binning_ws; size_t binning_bytes;
+  int64_t capacity; /* instances the binning workspace was sized for */
+  /* optional pinned-host uint32[2]: asynchronously receives {R, overflow}; valid after the stream reaches that point */
+  uint32_t* num_rendered_host;
+  /* host-known instance count for grid sizing in fdls_bin_and_render; <0 = unknown, size grids by capacity */
+  int64_t num_rendered_hint;
+} FdlsFwdArgs;
+
+typedef struct FdlsBwdArgs {
+  int32_t P, D, M, F, W, H;
+  float tanfovx, tanfovy, scale_modifier;
+  int32_t debug, include_feature;
+  int64_t num_rendered; /* R of the forward that filled the workspaces */
+  const float* background;
+  const float* means3D;
+  const float* shs;
+  const float* colors_precomp;
+  const float* language_feature;
+  const float* scales;
+  const float* rotations;
+  const float* cov3D_precomp;
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* campos;
+  const int32_t* radii;
+  /* forward state */
+  const void* geom_ws; const void* img_ws; const void* binning_ws; int64_t capacity;
+  /* upstream gradients */
+  const float* dL_dout_color;    /* (3,H,W) */
+  const float* dL_dout_language; /* (F,H,W) or null */
+  const float* dL_dout_depth;    /* (1,H,W) or null (treated as zeros) */
+  /* scratch: float[16*P] per-Gaussian screen-space gradient records, zeroed by the library */
+  void* grad_ws; size_t grad_bytes;
+  /* gradient outputs (device); every array is fully written (zeros for invisible Gaussians); null = not wanted */
+  float* dL_dmeans3D;  /* (P,3) */
+  float* dL_dmeans2D;  /* (P,3), .z = 0 */
+  float* dL_dsh;       /* (P,M,3) */
+  float* dL_dcolors;   /* (P,3) */
+  float* dL_dlanguage; /* (P,F) */
+  float* dL_dopacity;  /* (P) */
+  float* dL_dscales;   /* (P,3) */
+  float* dL_drotations;/* (P,4) */
+  float* dL_dcov3D;    /* (P,6) */
+  float* dL_dconic;    /* (P,4) optional (reference returns it internally only) */
+  float* dL_ddepths;   /* (P) optional */
+} FdlsBwdArgs;
+
+int fdls_abi_version(void);
+const char* fdls_strerror(int code);
+
+int fdls_workspace_sizes(int32_t P, int32_t W, int32_t H, int64_t capacity, FdlsWorkspaceSizes* out);
+int fdls_workspace_layout(int32_t P, int32_t W, int32_t H, int64_t capacity, FdlsLayout* out);
+size_t fdls_grad_workspace_bytes(int32_t P);
+
+/* Stage 1: preprocess + tile-count scan.  Writes radii, the geometry workspace and R (device + optional pinned host). */
+int fdls_preprocess(const FdlsFwdArgs* a, void* stream);
+/* Stage 2: key duplication, radix sort, tile ranges, compositing.  Instances beyond `capacity` are dropped and the
+ * overflow flag is raised (caller re-runs stage 2 with a larger binning workspace). */
+int fdls_bin_and_render(const FdlsFwdArgs* a, void* stream);
+/* Both stages back to back (no host synchronisation). */
+int fdls_forward(const FdlsFwdArgs* a, void* stream);
+
+int fdls_backward(const FdlsBwdArgs* a, void* stream);
+
+int fdls_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                      uint8_t* present, void* stream);
+
+size_t fdls_knn_workspace_bytes(int32_t N);
+int fdls_knn_dist2(int32_t N, const float* xyz, float* out_dist2, void* ws, size_t ws_bytes, void* stream);
+
+/* Stable LSD radix sort of (u64 key, u32 value) pairs on key bits [0, end_bit); exported for the parity tests
+ * (replaces cub::DeviceRadixSort::SortPairs, rasterizer_impl.cu:307-312).  Double-buffered like cub::DoubleBuffer:
+ * input in (keys_a, vals_a); returns 0 if the sorted result is in the `a` buffers, 1 if in the `b` buffers
+ * (= number of 8-bit passes modulo 2), negative on error.  n_dev may be null (then n = n_max); otherwise the
+ * element count is min(*n_dev, n_max), read on the device. */
+size_t fdls_sort_scratch_bytes(int64_t n_max);
+int fdls_sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, int64_t n_max,
+                    const uint32_t* n_dev, int end_bit, void* scratch, size_t scratch_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FDLS_ABI_H */
