@@ -1,0 +1,221 @@
+"""Torch-facing binding of the C ABI: the three functions the reference's pybind module `_C` exports
+(RAST/ext.cpp:15-19, rasterize_points.cu:35-256), same argument order, same return tuples.
+
+PyTorch is plumbing only here: it owns device memory (outputs, gradients, the three workspaces) and the current
+stream; all arithmetic happens in libfdls.so.  There is no CPU or eager fallback: non-CUDA tensors raise.
+
+Instance-count handling (the reference blocks on a D2H copy of num_rendered, rasterizer_impl.cu:285):
+  * exact mode: preprocess, wait for R in pinned host memory, size the binning workspace to R exactly.
+  * speculative mode (default once a previous frame is known; env FDLS_SPECULATIVE=0 disables): the binning
+    workspace is sized from the previous frame's R with head-room, both stages are enqueued back to back, and the host
+    only waits for the tiny R copy (which completes right after the scan, while sort/compositing are still running).
+    If R overflowed the guess, stage 2 is simply re-run with the right size.  Results are identical in both modes.
+"""
+import ctypes as C
+import os
+
+import torch
+
+from . import _lib
+
+_state = {}  # per-device: pinned R buffer, last R
+
+
+def _dev_state(device):
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    st = _state.get(key)
+    if st is None:
+        st = {"pinned": torch.zeros(2, dtype=torch.int32).pin_memory(), "last_R": None, "grad_ws": None}
+        _state[key] = st
+    return st
+
+
+def _ptr(t):
+    """Device address or NULL for the reference's empty-tensor placeholders (rasterize_points.cu relies on
+    data_ptr()==nullptr for torch.Tensor([]))."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _prep(t, name):
+    if t is None or t.numel() == 0:
+        return t
+    if not t.is_cuda:
+        raise RuntimeError("%s must be a CUDA tensor (this build has no CPU path)" % name)
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def rasterize_gaussians(background, means3D, colors, language_feature, opacity, scales, rotations, scale_modifier,
+                        cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh,
+                        degree, campos, prefiltered, debug, include_feature):
+    """RasterizeGaussiansCUDA (rasterize_points.cu:35-129).  Returns
+    (num_rendered, out_color, out_language_feature, out_depth, radii, geomBuffer, binningBuffer, imgBuffer)."""
+    lib = _lib.load()
+    if means3D.ndim != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")  # rasterize_points.cu:59-61
+    means3D = _prep(means3D, "means3D")
+    dev = means3D.device
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    background, colors, language_feature, opacity, scales, rotations, cov3D_precomp, viewmatrix, projmatrix, sh, campos = [
+        _prep(t, n) for t, n in ((background, "bg"), (colors, "colors_precomp"), (language_feature, "language_feature"),
+                                 (opacity, "opacities"), (scales, "scales"), (rotations, "rotations"),
+                                 (cov3D_precomp, "cov3D_precomp"), (viewmatrix, "viewmatrix"),
+                                 (projmatrix, "projmatrix"), (sh, "shs"), (campos, "campos"))]
+    F = language_feature.size(1) if (language_feature is not None and language_feature.numel() > 0) else 0
+    if F > _lib.FDLS_MAX_LANG_CHANNELS:
+        raise RuntimeError("language_feature has %d channels; this build supports up to %d" %
+                           (F, _lib.FDLS_MAX_LANG_CHANNELS))
+    M = sh.size(1) if (sh is not None and sh.numel() > 0) else 0
+    f32 = dict(dtype=torch.float32, device=dev)
+    out_color = torch.empty((3, H, W), **f32)
+    out_depth = torch.empty((1, H, W), **f32)
+    # rasterize_points.cu:72-78: a (1,) tensor stands in for the feature image when include_feature is false
+    out_lang = torch.empty((F, H, W), **f32) if include_feature else torch.zeros((1,), **f32)
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    sizes = _lib.workspace_sizes(P, W, H, 0)
+    geom = torch.empty(sizes.geom_bytes, dtype=torch.uint8, device=dev)
+    img = torch.empty(sizes.img_bytes, dtype=torch.uint8, device=dev)
+    if P == 0:  # rasterize_points.cu:91: kernels skipped, images are the fill values
+        out_color.zero_(); out_depth.zero_(); out_lang.zero_()
+        return 0, out_color, out_lang, out_depth, radii, geom, torch.empty(0, dtype=torch.uint8, device=dev), img
+
+    st = _dev_state(dev)
+    a = _lib.FdlsFwdArgs()
+    a.P, a.D, a.M, a.F, a.W, a.H = P, int(degree), M, F, W, H
+    a.tanfovx, a.tanfovy, a.scale_modifier = float(tan_fovx), float(tan_fovy), float(scale_modifier)
+    a.prefiltered, a.debug, a.include_feature = int(bool(prefiltered)), int(bool(debug)), int(bool(include_feature))
+    a.background, a.means3D, a.shs, a.colors_precomp = _ptr(background), _ptr(means3D), _ptr(sh), _ptr(colors)
+    a.language_feature, a.opacities, a.scales, a.rotations = _ptr(language_feature), _ptr(opacity), _ptr(scales), _ptr(rotations)
+    a.cov3D_precomp, a.viewmatrix, a.projmatrix, a.campos = _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos)
+    a.out_color, a.out_depth, a.radii = out_color.data_ptr(), out_depth.data_ptr(), radii.data_ptr()
+    a.out_language = out_lang.data_ptr() if include_feature else None
+    a.geom_ws, a.geom_bytes, a.img_ws, a.img_bytes = geom.data_ptr(), sizes.geom_bytes, img.data_ptr(), sizes.img_bytes
+    a.num_rendered_host = st["pinned"].data_ptr()
+    a.num_rendered_hint = -1
+    stream = _stream()
+
+    def run_stage2(capacity, hint):
+        bs = _lib.workspace_sizes(P, W, H, capacity).binning_bytes if capacity > 0 else 0
+        binning = torch.empty(bs, dtype=torch.uint8, device=dev)
+        a.binning_ws, a.binning_bytes, a.capacity = (binning.data_ptr() if bs else None), bs, capacity
+        a.num_rendered_hint = hint
+        _lib.check(lib.fdls_bin_and_render(C.byref(a), stream), "fdls_bin_and_render")
+        return binning
+
+    speculative = os.environ.get("FDLS_SPECULATIVE", "1") != "0" and st["last_R"] is not None and not debug
+    a.capacity = 0
+    if speculative:
+        capacity = int(st["last_R"] * 1.25) + 4096
+        a.capacity = capacity
+        _lib.check(lib.fdls_preprocess(C.byref(a), stream), "fdls_preprocess")
+        ev = torch.cuda.Event()
+        ev.record()
+        binning = run_stage2(capacity, -1)
+        ev.synchronize()
+        R = int(st["pinned"][0])
+        if R > capacity:
+            binning = run_stage2(R, R)
+    else:
+        _lib.check(lib.fdls_preprocess(C.byref(a), stream), "fdls_preprocess")
+        torch.cuda.current_stream().synchronize()
+        R = int(st["pinned"][0])
+        binning = run_stage2(R, R)
+    st["last_R"] = R
+    if debug:  # CHECK_CUDA semantics (auxiliary.h:166-173): surface asynchronous errors here
+        torch.cuda.current_stream().synchronize()
+    return R, out_color, out_lang, out_depth, radii, geom, binning, img
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, language_feature, scales, rotations,
+                                 scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
+                                 dL_dout_color, dL_dout_language_feature, dL_dout_depth, sh, degree, campos, geomBuffer,
+                                 R, binningBuffer, imageBuffer, debug, include_feature):
+    """RasterizeGaussiansBackwardCUDA (rasterize_points.cu:131-235).  Returns (dL_dmeans2D, dL_dcolors,
+    dL_dlanguage_feature, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)."""
+    lib = _lib.load()
+    means3D = _prep(means3D, "means3D")
+    dev = means3D.device
+    P = means3D.size(0)
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)  # rasterize_points.cu:160-161
+    colors, language_feature, scales, rotations, cov3D_precomp, sh = [
+        _prep(t, n) for t, n in ((colors, "colors_precomp"), (language_feature, "language_feature"),
+                                 (scales, "scales"), (rotations, "rotations"), (cov3D_precomp, "cov3D_precomp"),
+                                 (sh, "shs"))]
+    background, viewmatrix, projmatrix, campos = [
+        _prep(t, n) for t, n in ((background, "bg"), (viewmatrix, "viewmatrix"), (projmatrix, "projmatrix"),
+                                 (campos, "campos"))]
+    dL_dout_color = _prep(dL_dout_color, "dL_dout_color")
+    dL_dout_language_feature = _prep(dL_dout_language_feature, "dL_dout_language_feature")
+    dL_dout_depth = _prep(dL_dout_depth, "dL_dout_depth")
+    F = language_feature.size(1) if (language_feature is not None and language_feature.numel() > 0) else 0
+    M = sh.size(1) if (sh is not None and sh.numel() > 0) else 0
+    f32 = dict(dtype=torch.float32, device=dev)
+    # every element of these is written by the backward kernels (zeros for culled Gaussians): no zero-fill pass
+    g_means3D = torch.empty((P, 3), **f32)
+    g_means2D = torch.empty((P, 3), **f32)
+    g_colors = torch.empty((P, 3), **f32)
+    g_lang = torch.empty((P, F), **f32) if include_feature else torch.zeros((1,), **f32)
+    g_opacity = torch.empty((P, 1), **f32)
+    g_cov3D = torch.empty((P, 6), **f32)
+    g_sh = torch.empty((P, M, 3), **f32) if M > 0 else torch.zeros((P, 0, 3), **f32)
+    g_scales = torch.empty((P, 3), **f32)
+    g_rot = torch.empty((P, 4), **f32)
+    if P == 0:
+        return g_means2D, g_colors, g_lang, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rot
+    gb = lib.fdls_grad_workspace_bytes(P)
+    grad_ws = torch.empty(gb, dtype=torch.uint8, device=dev)
+    a = _lib.FdlsBwdArgs()
+    a.P, a.D, a.M, a.F, a.W, a.H = P, int(degree), M, F, W, H
+    a.tanfovx, a.tanfovy, a.scale_modifier = float(tan_fovx), float(tan_fovy), float(scale_modifier)
+    a.debug, a.include_feature, a.num_rendered = int(bool(debug)), int(bool(include_feature)), int(R)
+    a.background, a.means3D, a.shs, a.colors_precomp = _ptr(background), _ptr(means3D), _ptr(sh), _ptr(colors)
+    a.language_feature, a.scales, a.rotations, a.cov3D_precomp = _ptr(language_feature), _ptr(scales), _ptr(rotations), _ptr(cov3D_precomp)
+    a.viewmatrix, a.projmatrix, a.campos, a.radii = _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos), radii.data_ptr()
+    a.geom_ws, a.img_ws, a.binning_ws, a.capacity = geomBuffer.data_ptr(), imageBuffer.data_ptr(), _ptr(binningBuffer), int(R)
+    a.dL_dout_color = dL_dout_color.data_ptr()
+    a.dL_dout_language = _ptr(dL_dout_language_feature) if include_feature else None
+    a.dL_dout_depth = _ptr(dL_dout_depth)
+    a.grad_ws, a.grad_bytes = grad_ws.data_ptr(), gb
+    a.dL_dmeans3D, a.dL_dmeans2D, a.dL_dcolors = g_means3D.data_ptr(), g_means2D.data_ptr(), g_colors.data_ptr()
+    a.dL_dsh = g_sh.data_ptr() if M > 0 else None
+    a.dL_dlanguage = g_lang.data_ptr() if include_feature else None
+    a.dL_dopacity, a.dL_dcov3D = g_opacity.data_ptr(), g_cov3D.data_ptr()
+    a.dL_dscales, a.dL_drotations = g_scales.data_ptr(), g_rot.data_ptr()
+    a.dL_dconic, a.dL_ddepths = None, None
+    _lib.check(lib.fdls_backward(C.byref(a), _stream()), "fdls_backward")
+    if debug:
+        torch.cuda.current_stream().synchronize()
+    return g_means2D, g_colors, g_lang, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rot
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """markVisible (rasterize_points.cu:237-256): bool (P,) of Gaussians in front of the near plane."""
+    lib = _lib.load()
+    means3D = _prep(means3D, "means3D")
+    P = means3D.size(0)
+    present = torch.zeros((P,), dtype=torch.bool, device=means3D.device)
+    if P:
+        _lib.check(lib.fdls_mark_visible(P, means3D.data_ptr(), _prep(viewmatrix, "viewmatrix").data_ptr(),
+                                         _prep(projmatrix, "projmatrix").data_ptr(), present.data_ptr(), _stream()),
+                   "fdls_mark_visible")
+    return present
+
+
+def dist_cuda2(points):
+    """simple_knn._C.distCUDA2 (call site scene/gaussian_model.py:203): (N,3) -> (N,) mean squared 3-NN distance."""
+    lib = _lib.load()
+    points = _prep(points, "points")
+    N = points.size(0)
+    out = torch.empty((N,), dtype=torch.float32, device=points.device)
+    if N:
+        wb = lib.fdls_knn_workspace_bytes(N)
+        ws = torch.empty(wb, dtype=torch.uint8, device=points.device)
+        _lib.check(lib.fdls_knn_dist2(N, points.data_ptr(), out.data_ptr(), ws.data_ptr(), wb, _stream()), "fdls_knn_dist2")
+    return out

@@ -1,0 +1,275 @@
+// api.cu -- the extern "C" entry points declared in include/fdls_abi.h: argument checks, workspace carving, and the
+// launch sequences that replace CudaRasterizer::Rasterizer::forward / backward / markVisible
+// (cuda_rasterizer/rasterizer_impl.cu:198-348, :352-469, :141-153).  No device allocation, no host synchronisation.
+#include <cstdio>
+#include "common.cuh"
+
+namespace fdls {
+// preprocess_fwd.cu
+cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, float4* rec, uint32_t* tiles_touched,
+                                  uint8_t* clamped, cudaStream_t st);
+cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
+// binning.cu
+size_t scan_scratch_bytes(int P);
+cudaError_t launch_scan(int P, const uint32_t* tiles_touched, uint32_t* offsets, uint32_t* block_sums,
+                        uint32_t* num_rendered, long long capacity, cudaStream_t st);
+cudaError_t launch_duplicate(int P, const float4* rec, const uint32_t* offsets, const int* radii, uint64_t* keys,
+                             uint32_t* vals, int gx, int gy, long long capacity, cudaStream_t st);
+cudaError_t launch_tile_ranges(const uint32_t* num_rendered, long long n_grid, long long capacity, const uint64_t* keys,
+                               uint2* ranges, int tiles, cudaStream_t st);
+// radix_sort.cu
+size_t sort_scratch_bytes(long long n_max);
+int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
+               const uint32_t* n_dev, int end_bit, void* scratch, size_t scratch_bytes, cudaStream_t st);
+// render_fwd.cu / render_bwd.cu / preprocess_bwd.cu
+cudaError_t launch_render_fwd(int F, const uint2* ranges, const uint32_t* point_list, const float4* rec, int W, int H,
+                              int gx, int gy, const float* bg, float* final_T, uint32_t* n_contrib, uint32_t* tile_max,
+                              float* out_color, float* out_lang, float* out_depth, cudaStream_t st);
+cudaError_t launch_render_bwd(int F, const uint2* ranges, const uint32_t* point_list, const float4* rec, int W, int H,
+                              int gx, int gy, const float* bg, const float* final_T, const uint32_t* n_contrib,
+                              const uint32_t* tile_max, const float* dpix, const float* dpix_F, const float* dpix_D,
+                              float* grad_rec, cudaStream_t st);
+cudaError_t launch_preprocess_bwd(const FdlsBwdArgs* a, const ViewParams& vp, const uint8_t* clamped,
+                                  const float4* grad_rec, cudaStream_t st);
+// knn.cu
+size_t knn_workspace_bytes(int N);
+int knn_dist2(int N, const float* xyz, float* out, void* ws, size_t ws_bytes, cudaStream_t st);
+
+// rasterizer_impl.cu:35-50
+static uint32_t higher_msb(uint32_t n) {
+  uint32_t msb = sizeof(n) * 4;
+  uint32_t step = msb;
+  while (step > 1) {
+    step /= 2;
+    if (n >> msb) msb += step;
+    else msb -= step;
+  }
+  if (n >> msb) msb++;
+  return msb;
+}
+
+static void compute_layout(int P, int W, int H, long long capacity, FdlsLayout* L, FdlsWorkspaceSizes* S) {
+  const int gx = cdiv(W, TILE), gy = cdiv(H, TILE);
+  const size_t tiles = (size_t)gx * gy, HW = (size_t)W * H, Pz = (size_t)(P < 1 ? 1 : P);
+  const size_t cap = (size_t)(capacity < 1 ? 1 : capacity);
+  size_t o = 0;
+  L->rec = o;           o += align_up(Pz * REC_FLOATS * sizeof(float));
+  L->tiles_touched = o; o += align_up(Pz * 4);
+  L->point_offsets = o; o += align_up(Pz * 4);
+  L->clamped = o;       o += align_up(Pz);
+  L->num_rendered = o;  o += align_up(16);
+  L->scan_scratch = o;  o += scan_scratch_bytes((int)Pz);
+  S->geom_bytes = o;
+  o = 0;
+  L->final_T = o;          o += align_up(HW * 4);
+  L->n_contrib = o;        o += align_up(HW * 4);
+  L->ranges = o;           o += align_up(tiles * 8);
+  L->tile_max_contrib = o; o += align_up(tiles * 4);
+  S->img_bytes = o;
+  o = 0;
+  L->vals = o;         o += align_up(cap * 4);  // first: the backward finds point_list without knowing capacity
+  L->vals_alt = o;     o += align_up(cap * 4);
+  L->keys = o;         o += align_up(cap * 8);
+  L->keys_alt = o;     o += align_up(cap * 8);
+  L->sort_scratch = o; o += sort_scratch_bytes((long long)cap);
+  S->binning_bytes = o;
+}
+
+static ViewParams make_view(const float* view, const float* proj, const float* campos, const float* bg, int W, int H,
+                            float tanfovx, float tanfovy, float scale_modifier) {
+  ViewParams vp;
+  vp.view = view; vp.proj = proj; vp.campos = campos; vp.bg = bg;
+  vp.tanfovx = tanfovx; vp.tanfovy = tanfovy;
+  vp.focal_y = H / (2.0f * tanfovy);  // rasterizer_impl.cu:226-227
+  vp.focal_x = W / (2.0f * tanfovx);
+  vp.scale_modifier = scale_modifier;
+  vp.W = W; vp.H = H; vp.gx = cdiv(W, TILE); vp.gy = cdiv(H, TILE);
+  return vp;
+}
+
+static int check_fwd(const FdlsFwdArgs* a) {
+  if (!a || a->P < 0 || a->W <= 0 || a->H <= 0) return FDLS_EINVAL;
+  if (a->F < 0 || a->F > FDLS_MAX_LANG_CHANNELS) return FDLS_EUNSUPPORTED;
+  if (a->P > 0) {
+    if (!a->means3D || !a->opacities || !a->viewmatrix || !a->projmatrix || !a->radii) return FDLS_EINVAL;
+    if ((a->shs == nullptr) == (a->colors_precomp == nullptr)) return FDLS_EINVAL;  // __init__.py:202-203
+    if (a->shs && (a->M < (a->D + 1) * (a->D + 1) || a->D > 3 || !a->campos)) return FDLS_EINVAL;
+    const bool sr = a->scales != nullptr && a->rotations != nullptr;
+    if (sr == (a->cov3D_precomp != nullptr)) return FDLS_EINVAL;  // __init__.py:205-206
+    if ((a->scales == nullptr) != (a->rotations == nullptr)) return FDLS_EINVAL;
+  }
+  if (a->include_feature && (a->F < 1 || !a->language_feature || !a->out_language)) return FDLS_EINVAL;
+  if (!a->out_color || !a->out_depth || !a->background) return FDLS_EINVAL;
+  if (!a->geom_ws || !a->img_ws) return FDLS_EINVAL;
+  return FDLS_OK;
+}
+
+}  // namespace fdls
+
+using namespace fdls;
+
+extern "C" {
+
+#define FDLS_API __attribute__((visibility("default")))
+
+FDLS_API int fdls_abi_version(void) { return 1; }
+
+FDLS_API const char* fdls_strerror(int code) {
+  switch (code) {
+    case FDLS_OK: return "ok";
+    case FDLS_EINVAL: return "invalid argument";
+    case FDLS_EWORKSPACE: return "workspace too small";
+    case FDLS_ECUDA: return "CUDA error";
+    case FDLS_EUNSUPPORTED: return "unsupported configuration";
+    default: return "unknown error";
+  }
+}
+
+FDLS_API int fdls_workspace_sizes(int32_t P, int32_t W, int32_t H, int64_t capacity, FdlsWorkspaceSizes* out) {
+  if (!out || P < 0 || W <= 0 || H <= 0 || capacity < 0) return FDLS_EINVAL;
+  FdlsLayout L;
+  compute_layout(P, W, H, capacity, &L, out);
+  return FDLS_OK;
+}
+
+FDLS_API int fdls_workspace_layout(int32_t P, int32_t W, int32_t H, int64_t capacity, FdlsLayout* out) {
+  if (!out || P < 0 || W <= 0 || H <= 0 || capacity < 0) return FDLS_EINVAL;
+  FdlsWorkspaceSizes S;
+  compute_layout(P, W, H, capacity, out, &S);
+  return FDLS_OK;
+}
+
+FDLS_API size_t fdls_grad_workspace_bytes(int32_t P) { return align_up((size_t)(P < 1 ? 1 : P) * 16 * sizeof(float)); }
+
+FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
+  int rc = check_fwd(a);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  FdlsLayout L;
+  FdlsWorkspaceSizes S;
+  compute_layout(a->P, a->W, a->H, a->capacity < 0 ? 0 : a->capacity, &L, &S);
+  if (a->geom_bytes < S.geom_bytes || a->img_bytes < S.img_bytes) return FDLS_EWORKSPACE;
+  char* g = (char*)a->geom_ws;
+  ViewParams vp = make_view(a->viewmatrix, a->projmatrix, a->campos, a->background, a->W, a->H, a->tanfovx, a->tanfovy,
+                            a->scale_modifier);
+  uint32_t* nr = (uint32_t*)(g + L.num_rendered);
+  if (launch_preprocess_fwd(a, vp, (float4*)(g + L.rec), (uint32_t*)(g + L.tiles_touched), (uint8_t*)(g + L.clamped),
+                            st) != cudaSuccess)
+    return FDLS_ECUDA;
+  if (launch_scan(a->P, (uint32_t*)(g + L.tiles_touched), (uint32_t*)(g + L.point_offsets),
+                  (uint32_t*)(g + L.scan_scratch), nr, a->capacity, st) != cudaSuccess)
+    return FDLS_ECUDA;
+  if (a->num_rendered_host &&
+      cudaMemcpyAsync(a->num_rendered_host, nr, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st) != cudaSuccess)
+    return FDLS_ECUDA;
+  return FDLS_OK;
+}
+
+FDLS_API int fdls_bin_and_render(const FdlsFwdArgs* a, void* stream) {
+  int rc = check_fwd(a);
+  if (rc) return rc;
+  if (a->capacity < 0 || (a->capacity > 0 && !a->binning_ws)) return FDLS_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  FdlsLayout L;
+  FdlsWorkspaceSizes S;
+  compute_layout(a->P, a->W, a->H, a->capacity, &L, &S);
+  if (a->geom_bytes < S.geom_bytes || a->img_bytes < S.img_bytes) return FDLS_EWORKSPACE;
+  if (a->capacity > 0 && a->binning_bytes < S.binning_bytes) return FDLS_EWORKSPACE;
+  char* g = (char*)a->geom_ws;
+  char* im = (char*)a->img_ws;
+  char* b = (char*)a->binning_ws;
+  const int gx = cdiv(a->W, TILE), gy = cdiv(a->H, TILE);
+  uint32_t* nr = (uint32_t*)(g + L.num_rendered);
+  long long n_grid = a->capacity;
+  if (a->num_rendered_hint >= 0 && a->num_rendered_hint < n_grid) n_grid = a->num_rendered_hint;
+  uint2* ranges = (uint2*)(im + L.ranges);
+  const uint32_t* point_list = nullptr;
+  if (n_grid > 0) {
+    const int end_bit = 32 + (int)higher_msb((uint32_t)(gx * gy));  // rasterizer_impl.cu:304
+    const int passes = (end_bit + 7) / 8;
+    // choose the input buffer so that the sorted result lands in (keys, vals)
+    uint64_t* k_in = (uint64_t*)(b + ((passes & 1) ? L.keys_alt : L.keys));
+    uint64_t* k_out = (uint64_t*)(b + ((passes & 1) ? L.keys : L.keys_alt));
+    uint32_t* v_in = (uint32_t*)(b + ((passes & 1) ? L.vals_alt : L.vals));
+    uint32_t* v_out = (uint32_t*)(b + ((passes & 1) ? L.vals : L.vals_alt));
+    if (launch_duplicate(a->P, (const float4*)(g + L.rec), (const uint32_t*)(g + L.point_offsets), a->radii, k_in, v_in,
+                         gx, gy, a->capacity, st) != cudaSuccess)
+      return FDLS_ECUDA;
+    rc = sort_pairs(k_in, k_out, v_in, v_out, n_grid, nr, end_bit, b + L.sort_scratch, S.binning_bytes - L.sort_scratch,
+                    st);
+    if (rc < 0) return rc;
+    point_list = (const uint32_t*)(b + L.vals);
+    if (launch_tile_ranges(nr, n_grid, a->capacity, (const uint64_t*)(b + L.keys), ranges, gx * gy, st) != cudaSuccess)
+      return FDLS_ECUDA;
+  } else {
+    if (cudaMemsetAsync(ranges, 0, (size_t)gx * gy * sizeof(uint2), st) != cudaSuccess) return FDLS_ECUDA;
+  }
+  const int F = a->include_feature ? a->F : 0;
+  if (launch_render_fwd(F, ranges, point_list, (const float4*)(g + L.rec), a->W, a->H, gx, gy, a->background,
+                        (float*)(im + L.final_T), (uint32_t*)(im + L.n_contrib), (uint32_t*)(im + L.tile_max_contrib),
+                        a->out_color, a->out_language, a->out_depth, st) != cudaSuccess)
+    return FDLS_ECUDA;
+  return FDLS_OK;
+}
+
+FDLS_API int fdls_forward(const FdlsFwdArgs* a, void* stream) {
+  int rc = fdls_preprocess(a, stream);
+  if (rc) return rc;
+  return fdls_bin_and_render(a, stream);
+}
+
+FDLS_API int fdls_backward(const FdlsBwdArgs* a, void* stream) {
+  if (!a || a->P < 0 || a->W <= 0 || a->H <= 0) return FDLS_EINVAL;
+  if (a->F < 0 || a->F > FDLS_MAX_LANG_CHANNELS) return FDLS_EUNSUPPORTED;
+  if (a->P == 0) return FDLS_OK;
+  if (!a->geom_ws || !a->img_ws || !a->grad_ws || !a->dL_dout_color || !a->radii || !a->means3D) return FDLS_EINVAL;
+  if (a->include_feature && (a->F < 1 || !a->dL_dout_language)) return FDLS_EINVAL;
+  if (a->grad_bytes < fdls_grad_workspace_bytes(a->P)) return FDLS_EWORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  FdlsLayout L;
+  FdlsWorkspaceSizes S;
+  compute_layout(a->P, a->W, a->H, a->capacity < 0 ? 0 : a->capacity, &L, &S);
+  const char* g = (const char*)a->geom_ws;
+  const char* im = (const char*)a->img_ws;
+  const char* b = (const char*)a->binning_ws;
+  const int gx = cdiv(a->W, TILE), gy = cdiv(a->H, TILE);
+  ViewParams vp = make_view(a->viewmatrix, a->projmatrix, a->campos, a->background, a->W, a->H, a->tanfovx, a->tanfovy,
+                            a->scale_modifier);
+  if (cudaMemsetAsync(a->grad_ws, 0, (size_t)a->P * 16 * sizeof(float), st) != cudaSuccess) return FDLS_ECUDA;
+  if (a->num_rendered > 0 && b) {
+    const int F = a->include_feature ? a->F : 0;
+    if (launch_render_bwd(F, (const uint2*)(im + L.ranges), (const uint32_t*)(b + L.vals), (const float4*)(g + L.rec),
+                          a->W, a->H, gx, gy, a->background, (const float*)(im + L.final_T),
+                          (const uint32_t*)(im + L.n_contrib), (const uint32_t*)(im + L.tile_max_contrib),
+                          a->dL_dout_color, a->dL_dout_language, a->dL_dout_depth, (float*)a->grad_ws,
+                          st) != cudaSuccess)
+      return FDLS_ECUDA;
+  }
+  if (launch_preprocess_bwd(a, vp, (const uint8_t*)(g + L.clamped), (const float4*)a->grad_ws, st) != cudaSuccess)
+    return FDLS_ECUDA;
+  return FDLS_OK;
+}
+
+FDLS_API int fdls_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                               uint8_t* present, void* stream) {
+  (void)projmatrix;  // the reference's x/y frustum test is commented out (auxiliary.h:154)
+  if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return FDLS_EINVAL;
+  return launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream) == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
+}
+
+FDLS_API size_t fdls_knn_workspace_bytes(int32_t N) { return knn_workspace_bytes(N); }
+
+FDLS_API int fdls_knn_dist2(int32_t N, const float* xyz, float* out_dist2, void* ws, size_t ws_bytes, void* stream) {
+  if (N < 0 || (N > 0 && (!xyz || !out_dist2 || !ws))) return FDLS_EINVAL;
+  return knn_dist2(N, xyz, out_dist2, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+FDLS_API size_t fdls_sort_scratch_bytes(int64_t n_max) { return sort_scratch_bytes(n_max); }
+
+FDLS_API int fdls_sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, int64_t n_max,
+                             const uint32_t* n_dev, int end_bit, void* scratch, size_t scratch_bytes, void* stream) {
+  if (n_max < 0 || (n_max > 0 && (!keys_a || !keys_b || !vals_a || !vals_b || !scratch))) return FDLS_EINVAL;
+  return sort_pairs(keys_a, keys_b, vals_a, vals_b, n_max, n_dev, end_bit, scratch, scratch_bytes, (cudaStream_t)stream);
+}
+
+}  // extern "C"

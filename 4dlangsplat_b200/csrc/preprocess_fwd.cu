@@ -8,6 +8,7 @@
 // B200 notes: one thread per Gaussian, 256-thread blocks; the two 4x4 matrices are staged in shared memory once per
 // block; SH coefficients are fetched as 12 x 16-byte loads per Gaussian; everything the compositor needs is written
 // as ONE 64-byte record (4 x st.v4) so the render kernels gather a Gaussian with two 32-byte sectors.
+#include <cstdio>
 #include "common.cuh"
 
 namespace fdls {

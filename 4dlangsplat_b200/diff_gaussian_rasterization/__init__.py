@@ -1,0 +1,123 @@
+"""Host-side mirror of the reference's `diff_gaussian_rasterization` package
+(submodules/4d-langsplat-rasterization/diff_gaussian_rasterization/__init__.py): same public names, argument
+meaning, return order, shapes, dtypes and error behaviour, so gaussian_renderer/__init__.py:219-228 runs unchanged.
+
+    GaussianRasterizationSettings   NamedTuple, 13 fields in the reference order          (ref :167-180)
+    GaussianRasterizer              nn.Module: forward(...), markVisible(positions)        (ref :182-235)
+    rasterize_gaussians             functional entry                                        (ref :21-44)
+    _RasterizeGaussians             torch.autograd.Function, 10 inputs -> 4 outputs         (ref :46-165)
+
+Underneath, `_C` is the ctypes binding of the C ABI (include/fdls_abi.h) instead of a pybind module.
+"""
+from typing import NamedTuple
+
+import torch
+from torch import nn
+
+from .. import _C
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+    include_feature: bool
+
+
+def _snapshot(values):
+    """Host copies of every tensor argument, for the debug dump (ref cpu_deep_copy_tuple :17-19)."""
+    return tuple(v.detach().cpu().clone() if isinstance(v, torch.Tensor) else v for v in values)
+
+
+def _guarded(fn, args, debug, dump_path, banner):
+    """Debug mode reproduces the reference's behaviour: on any exception dump the inputs and re-raise (ref :88-95)."""
+    if not debug:
+        return fn(*args)
+    saved = _snapshot(args)
+    try:
+        return fn(*args)
+    except Exception:
+        torch.save(saved, dump_path)
+        print(banner)
+        raise
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, language_feature_precomp, opacities, scales, rotations,
+                cov3Ds_precomp, raster_settings):
+        rs = raster_settings
+        native_args = (rs.bg, means3D, colors_precomp, language_feature_precomp, opacities, scales, rotations,
+                       rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
+                       rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug,
+                       rs.include_feature)
+        (num_rendered, color, language_feature, depth, radii, geomBuffer, binningBuffer,
+         imgBuffer) = _guarded(_C.rasterize_gaussians, native_args, rs.debug, "snapshot_fw.dump",
+                               "\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.save_for_backward(colors_precomp, language_feature_precomp, means3D, scales, rotations, cov3Ds_precomp,
+                              radii, sh, geomBuffer, binningBuffer, imgBuffer)
+        ctx.mark_non_differentiable(radii)
+        return color, language_feature, radii, depth
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_out_language_feature, grad_radii, grad_depth):
+        rs = ctx.raster_settings
+        (colors_precomp, language_feature_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
+         binningBuffer, imgBuffer) = ctx.saved_tensors
+        native_args = (rs.bg, means3D, radii, colors_precomp, language_feature_precomp, scales, rotations,
+                       rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
+                       grad_out_color, grad_out_language_feature, grad_depth, sh, rs.sh_degree, rs.campos, geomBuffer,
+                       ctx.num_rendered, binningBuffer, imgBuffer, rs.debug, rs.include_feature)
+        (grad_means2D, grad_colors_precomp, grad_language_feature_precomp, grad_opacities, grad_means3D,
+         grad_cov3Ds_precomp, grad_sh, grad_scales, grad_rotations) = _guarded(
+             _C.rasterize_gaussians_backward, native_args, rs.debug, "snapshot_bw.dump",
+             "\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
+        # input order of forward(); the settings get no gradient (ref :152-163)
+        return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_language_feature_precomp,
+                grad_opacities, grad_scales, grad_rotations, grad_cov3Ds_precomp, None)
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, language_feature_precomp, opacities, scales, rotations,
+                        cov3Ds_precomp, raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, language_feature_precomp, opacities,
+                                     scales, rotations, cov3Ds_precomp, raster_settings)
+
+
+def _or_empty(t):
+    # the reference stands in a CPU torch.Tensor([]) for every absent optional (ref :208-221); the native side
+    # recognises it by data_ptr()==nullptr
+    return torch.Tensor([]) if t is None else t
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        with torch.no_grad():
+            rs = self.raster_settings
+            return _C.mark_visible(positions, rs.viewmatrix, rs.projmatrix)
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, language_feature_precomp=None,
+                scales=None, rotations=None, cov3D_precomp=None):
+        if (shs is None) == (colors_precomp is None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        have_sr = scales is not None and rotations is not None
+        any_sr = scales is not None or rotations is not None
+        if (not have_sr and cov3D_precomp is None) or (any_sr and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        return rasterize_gaussians(means3D, means2D, _or_empty(shs), _or_empty(colors_precomp),
+                                   _or_empty(language_feature_precomp), opacities, _or_empty(scales),
+                                   _or_empty(rotations), _or_empty(cov3D_precomp), self.raster_settings)

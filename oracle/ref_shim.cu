@@ -96,6 +96,11 @@ __attribute__((visibility("default"))) void ref_mark_visible(int P, float* means
   CudaRasterizer::Rasterizer::markVisible(P, means3D, view, proj, present);
 }
 
+// Plain device-to-device copy so the tests can pull intermediates out of the reference buffers.
+__attribute__((visibility("default"))) int ref_copy_d2d(void* dst, const void* src, size_t bytes) {
+  return (int)cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToDevice);
+}
+
 // Decode the three byte buffers of the last forward with the reference's own fromChunk layouts.
 __attribute__((visibility("default"))) void ref_state(void* hv, int P, int R, int HW, RefState* o) {
   Handle* h = static_cast<Handle*>(hv);

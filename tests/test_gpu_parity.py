@@ -1,0 +1,216 @@
+"""GPU parity: the product CUDA path (through the C ABI) against the UNMODIFIED reference CUDA rasterizer rebuilt
+for sm_100a (oracle/_ref/libref_f{3,6}.so) on identical synthetic inputs.
+
+Bars (BASELINE.json north_star): sort keys/values, tile ranges, per-pixel contributor counts bit-exact; forward
+images within 1e-5 relative; gradients within 1e-4 relative (atomic-order nondeterminism on both sides).
+"""
+import numpy as np
+import pytest
+import torch
+
+import helpers
+import refcuda
+
+pytestmark = pytest.mark.gpu
+
+IMG_RTOL = 1e-5
+GRAD_RTOL = 1e-4
+
+
+def _need_ref(F):
+    if not refcuda.available(F):
+        pytest.fail("oracle/_ref/libref_f%d.so missing: run python oracle/build_ref.py in the build container" % F)
+
+
+def _assert_same(a, b, what):
+    a, b = a.cpu(), b.cpu()
+    assert a.shape == b.shape, what
+    if a.dtype.is_floating_point:
+        a, b = a.contiguous().view(torch.int32), b.contiguous().view(torch.int32)
+    n = int((a != b).sum())
+    assert n == 0, "%s: %d of %d elements differ" % (what, n, a.numel())
+
+
+def _assert_close(a, b, rtol, what, atol_frac=1e-6):
+    ok, worst, nbad = helpers.rel_close(a, b, rtol, atol_frac)
+    assert ok, "%s: %d elements outside rtol=%g (worst rel err %.3g)" % (what, nbad, rtol, worst)
+
+
+CASES = [("tiny", 3, (1, 1, 1)), ("tiny", 6, (0, 0, 0)), ("small", 3, (1, 1, 1)), ("small", 6, (1, 1, 1))]
+
+
+@pytest.mark.parametrize("name,F,bg", CASES)
+def test_forward_bit_exact_stages(synth, name, F, bg):
+    _need_ref(F)
+    s = synth.scene(name, F=F, bg=bg)
+    ref = refcuda.Ref(F)
+    r = ref.forward(s)
+    o = helpers.run_forward(s)
+    assert o.R == r.R
+    _assert_same(o.radii, r.radii, "radii")
+    vis = (r.radii > 0)
+    _assert_same(o.tiles_touched, r.tiles_touched, "tiles_touched")
+    _assert_same(o.point_offsets, r.point_offsets, "point_offsets")
+    _assert_same(o.depths[vis], r.depths[vis], "depths")
+    _assert_same(o.means2D[vis], r.means2D[vis], "means2D")
+    _assert_same(o.conic_opacity[vis], r.conic_opacity[vis], "conic_opacity")
+    _assert_same(o.rgb[vis], r.rgb[vis], "rgb")
+    cl = torch.stack([(o.clamped & 1) != 0, (o.clamped & 2) != 0, (o.clamped & 4) != 0], 1).to(torch.uint8)
+    _assert_same(cl[vis], (r.clamped[vis] != 0).to(torch.uint8), "clamped")
+    _assert_same(o.keys, r.keys, "sorted keys")
+    _assert_same(o.point_list, r.point_list, "sorted values")
+    _assert_same(o.ranges, r.ranges, "tile ranges")
+    _assert_same(o.n_contrib, r.n_contrib, "n_contrib")
+    _assert_same(o.final_T, r.final_T, "final_T")
+    _assert_close(o.color, r.color, IMG_RTOL, "color")
+    _assert_close(o.lang, r.lang, IMG_RTOL, "language feature")
+    _assert_close(o.depth, r.depth, IMG_RTOL, "depth")
+    # tile_max_contrib is an addition of this build: must equal the per-tile max of n_contrib
+    H, W = s.H, s.W
+    gx, gy = (W + 15) // 16, (H + 15) // 16
+    nc = torch.zeros((gy * 16, gx * 16), dtype=torch.int32, device="cuda")
+    nc[:H, :W] = r.n_contrib
+    tm = nc.view(gy, 16, gx, 16).permute(0, 2, 1, 3).reshape(gy * gx, 256).max(1).values
+    _assert_same(o.tile_max, tm, "tile_max_contrib")
+
+
+@pytest.mark.parametrize("name,F,bg", CASES)
+@pytest.mark.parametrize("depth_grad", [False, True])
+def test_backward_matches_reference(synth, name, F, bg, depth_grad):
+    _need_ref(F)
+    s = synth.scene(name, F=F, bg=bg)
+    dcol, dlang, ddepth = synth.upstream_grads(s, depth=depth_grad)
+    ref = refcuda.Ref(F)
+    ref.forward(s)
+    gr = ref.backward(dcol, dlang, ddepth)
+    o = helpers.run_forward(s)
+    g = helpers.run_backward(s, o, dcol, dlang, ddepth)
+    for nm, a, b in (("means2D", g.means2D, gr.means2D), ("colors", g.colors, gr.colors), ("lang", g.lang, gr.lang),
+                     ("opacity", g.opacity, gr.opacity), ("means3D", g.means3D, gr.means3D),
+                     ("cov3D", g.cov3D, gr.cov3D), ("sh", g.sh, gr.sh), ("scales", g.scales, gr.scales),
+                     ("rots", g.rots, gr.rots)):
+        _assert_close(a, b, GRAD_RTOL, "dL_d" + nm, atol_frac=1e-5)
+
+
+def test_no_feature_and_precomputed_inputs(synth):
+    """include_feature=False (base stages), colors_precomp instead of SH, cov3D_precomp instead of scale/rotation."""
+    _need_ref(3)
+    s = synth.scene("tiny")
+    ref = refcuda.Ref(3)
+    r0 = ref.forward(s)
+    colors = np.nan_to_num(r0.rgb.cpu().numpy().copy(), nan=0.0, posinf=0.0, neginf=0.0)  # culled rows are uninitialised
+    cov3D = np.nan_to_num(r0.cov3D.cpu().numpy().copy(), nan=0.0, posinf=0.0, neginf=0.0)
+    dcol, dlang, ddepth = synth.upstream_grads(s)
+    for kw in (dict(include_feature=False), dict(colors_precomp=colors), dict(cov3D_precomp=cov3D),
+               dict(colors_precomp=colors, cov3D_precomp=cov3D, include_feature=False)):
+        r = ref.forward(s, **kw)
+        gr = ref.backward(dcol, dlang, ddepth)
+        o = helpers.run_forward(s, **kw)
+        _assert_same(o.keys, r.keys, "keys %s" % list(kw))
+        _assert_same(o.point_list, r.point_list, "values %s" % list(kw))
+        _assert_same(o.n_contrib, r.n_contrib, "n_contrib %s" % list(kw))
+        _assert_close(o.color, r.color, IMG_RTOL, "color %s" % list(kw))
+        inc = kw.get("include_feature", True)
+        if inc:
+            _assert_close(o.lang, r.lang, IMG_RTOL, "lang")
+        else:
+            assert tuple(o.lang.shape) == (1,)
+        g = helpers.run_backward(s, o, dcol, dlang, ddepth, include_feature=inc)
+        pairs = [("means2D", g.means2D, gr.means2D), ("colors", g.colors, gr.colors), ("opacity", g.opacity, gr.opacity),
+                 ("means3D", g.means3D, gr.means3D), ("cov3D", g.cov3D, gr.cov3D)]
+        if "colors_precomp" not in kw:
+            pairs.append(("sh", g.sh, gr.sh))
+        if "cov3D_precomp" not in kw:
+            pairs += [("scales", g.scales, gr.scales), ("rots", g.rots, gr.rots)]
+        if inc:
+            pairs.append(("lang", g.lang, gr.lang))
+        for nm, a, b in pairs:
+            _assert_close(a, b, GRAD_RTOL, "dL_d%s %s" % (nm, list(kw)), atol_frac=1e-5)
+
+
+def test_speculative_and_exact_modes_agree(synth, monkeypatch):
+    s = synth.scene("small")
+    monkeypatch.setenv("FDLS_SPECULATIVE", "0")
+    a = helpers.run_forward(s)
+    monkeypatch.setenv("FDLS_SPECULATIVE", "1")
+    b = helpers.run_forward(s)  # capacity guessed from the previous frame
+    big = synth.scene("small", P=60000)  # R grows past the guess -> overflow -> transparent re-run
+    c = helpers.run_forward(big)
+    monkeypatch.setenv("FDLS_SPECULATIVE", "0")
+    d = helpers.run_forward(big)
+    _assert_same(a.color, b.color, "color exact vs speculative")
+    _assert_same(a.point_list, b.point_list, "values exact vs speculative")
+    assert c.R == d.R and c.R > 1.25 * a.R + 4096
+    _assert_same(c.color, d.color, "color after overflow re-run")
+    _assert_same(c.n_contrib, d.n_contrib, "n_contrib after overflow re-run")
+
+
+def test_mark_visible(synth, fdls):
+    _need_ref(3)
+    s = synth.scene("small")
+    d = helpers.to_dev(s)
+    ref = refcuda.Ref(3)
+    want = ref.mark_visible(d.means3D, d.view, d.proj)
+    got = fdls._C.mark_visible(d.means3D, d.view, d.proj)
+    assert got.dtype == torch.bool and torch.equal(got, want)
+    assert 0 < int(got.sum()) < s.P
+
+
+@pytest.mark.parametrize("n,end_bit", [(1, 8), (255, 13), (4096, 44), (4097, 45), (100_000, 43), (1_000_003, 64),
+                                       (300_000, 5)])
+def test_sort_pairs_stable(fdls, n, end_bit):
+    import ctypes as C
+    lib = fdls._lib.load()
+    g = torch.Generator(device="cpu").manual_seed(n)
+    lo = torch.randint(0, 2 ** 31 - 1, (n,), generator=g, dtype=torch.int64)
+    hi = torch.randint(0, 2 ** 31 - 1, (n,), generator=g, dtype=torch.int64)
+    keys = ((hi << 32) | lo)
+    if end_bit < 64:
+        keys = keys & ((1 << end_bit) - 1)
+    keys[: n // 3] = keys[n // 2: n // 2 + n // 3].clone()  # plenty of duplicates to exercise stability
+    keys = keys.cuda()
+    vals = torch.arange(n, dtype=torch.int32, device="cuda")
+    ka, kb, va, vb = keys.clone(), torch.empty_like(keys), vals.clone(), torch.empty_like(vals)
+    sb = lib.fdls_sort_scratch_bytes(n)
+    scratch = torch.empty(sb, dtype=torch.uint8, device="cuda")
+    sel = lib.fdls_sort_pairs(ka.data_ptr(), kb.data_ptr(), va.data_ptr(), vb.data_ptr(), n, None, end_bit,
+                              scratch.data_ptr(), sb, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    assert sel in (0, 1)
+    ko, vo = (kb, vb) if sel else (ka, va)
+    # unsigned order: keys here are < 2^63 so the signed sort agrees
+    want_k, order = torch.sort(keys, stable=True)
+    assert torch.equal(ko, want_k)
+    assert torch.equal(vo.long(), order)
+
+
+def test_sort_pairs_device_count(fdls):
+    """Element count read on the device: only the first *n_dev pairs are sorted."""
+    import ctypes as C
+    lib = fdls._lib.load()
+    n_max, n = 50_000, 12_345
+    g = torch.Generator(device="cpu").manual_seed(5)
+    keys = torch.randint(0, 2 ** 40, (n_max,), generator=g, dtype=torch.int64).cuda()
+    vals = torch.arange(n_max, dtype=torch.int32, device="cuda")
+    ka, kb, va, vb = keys.clone(), torch.zeros_like(keys), vals.clone(), torch.zeros_like(vals)
+    n_dev = torch.tensor([n], dtype=torch.int32, device="cuda")
+    sb = lib.fdls_sort_scratch_bytes(n_max)
+    scratch = torch.empty(sb, dtype=torch.uint8, device="cuda")
+    sel = lib.fdls_sort_pairs(ka.data_ptr(), kb.data_ptr(), va.data_ptr(), vb.data_ptr(), n_max, n_dev.data_ptr(), 40,
+                              scratch.data_ptr(), sb, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    ko, vo = (kb, vb) if sel else (ka, va)
+    want_k, order = torch.sort(keys[:n], stable=True)
+    assert torch.equal(ko[:n], want_k) and torch.equal(vo[:n].long(), order)
+
+
+@pytest.mark.parametrize("n", [4, 1000, 1025, 50_000])
+def test_knn_dist2(fdls, n):
+    from scipy.spatial import cKDTree
+    rng = np.random.default_rng(n)
+    pts = rng.normal(size=(n, 3)).astype(np.float32)
+    pts[: n // 10] *= 0.01  # a dense cluster
+    got = fdls.simple_knn._C.distCUDA2(torch.as_tensor(pts).cuda()).cpu().numpy()
+    d, _ = cKDTree(pts.astype(np.float64)).query(pts.astype(np.float64), k=4)
+    want = (d[:, 1:4] ** 2).mean(1)
+    np.testing.assert_allclose(got, want, rtol=1e-4, atol=1e-12)
