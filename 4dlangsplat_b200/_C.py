@@ -19,6 +19,8 @@ import torch
 from . import _lib
 
 _state = {}  # per-device: pinned R buffer, last R
+# bench.py hooks: ctypes arrays of cudaEvent_t handles (FDLS_FWD_EVENTS / FDLS_BWD_EVENTS entries) or None
+profile = {"fwd": None, "bwd": None}
 
 
 def _dev_state(device):
@@ -99,6 +101,8 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
     a.geom_ws, a.geom_bytes, a.img_ws, a.img_bytes = geom.data_ptr(), sizes.geom_bytes, img.data_ptr(), sizes.img_bytes
     a.num_rendered_host = st["pinned"].data_ptr()
     a.num_rendered_hint = -1
+    if profile["fwd"] is not None:
+        a.stage_events = profile["fwd"]
     stream = _stream()
 
     def run_stage2(capacity, hint):
@@ -128,6 +132,7 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
         R = int(st["pinned"][0])
         binning = run_stage2(R, R)
     st["last_R"] = R
+    st["last_capacity"] = int(a.capacity)  # read by the tests to decode the binning workspace
     if debug:  # CHECK_CUDA semantics (auxiliary.h:166-173): surface asynchronous errors here
         torch.cuda.current_stream().synchronize()
     return R, out_color, out_lang, out_depth, radii, geom, binning, img
@@ -189,6 +194,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, language_fe
     a.dL_dopacity, a.dL_dcov3D = g_opacity.data_ptr(), g_cov3D.data_ptr()
     a.dL_dscales, a.dL_drotations = g_scales.data_ptr(), g_rot.data_ptr()
     a.dL_dconic, a.dL_ddepths = None, None
+    if profile["bwd"] is not None:
+        a.stage_events = profile["bwd"]
     _lib.check(lib.fdls_backward(C.byref(a), _stream()), "fdls_backward")
     if debug:
         torch.cuda.current_stream().synchronize()

@@ -11,6 +11,8 @@ LIB_PATH = os.path.join(_HERE, "libfdls.so")
 
 FDLS_MAX_LANG_CHANNELS = 6
 FDLS_TILE = 16
+FDLS_FWD_EVENTS = 7
+FDLS_BWD_EVENTS = 4
 
 _f32p = C.c_void_p  # device pointers travel as plain addresses
 
@@ -41,6 +43,7 @@ class FdlsFwdArgs(C.Structure):
         ("capacity", C.c_int64),
         ("num_rendered_host", C.c_void_p),
         ("num_rendered_hint", C.c_int64),
+        ("stage_events", C.POINTER(C.c_void_p)),
     ]
 
 
@@ -59,12 +62,14 @@ class FdlsBwdArgs(C.Structure):
         ("dL_dmeans3D", _f32p), ("dL_dmeans2D", _f32p), ("dL_dsh", _f32p), ("dL_dcolors", _f32p),
         ("dL_dlanguage", _f32p), ("dL_dopacity", _f32p), ("dL_dscales", _f32p), ("dL_drotations", _f32p),
         ("dL_dcov3D", _f32p), ("dL_dconic", _f32p), ("dL_ddepths", _f32p),
+        ("stage_events", C.POINTER(C.c_void_p)),
     ]
 
 
 # every symbol include/fdls_abi.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "fdls_abi_version": (C.c_int, []),
+    "fdls_kernel_launches": (C.c_uint64, []),
     "fdls_strerror": (C.c_char_p, [C.c_int]),
     "fdls_workspace_sizes": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.POINTER(FdlsWorkspaceSizes)]),
     "fdls_workspace_layout": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.POINTER(FdlsLayout)]),

@@ -1,10 +1,16 @@
 // api.cu -- the extern "C" entry points declared in include/fdls_abi.h: argument checks, workspace carving, and the
 // launch sequences that replace CudaRasterizer::Rasterizer::forward / backward / markVisible
 // (cuda_rasterizer/rasterizer_impl.cu:198-348, :352-469, :141-153).  No device allocation, no host synchronisation.
+#include <atomic>
 #include <cstdio>
 #include "common.cuh"
 
 namespace fdls {
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+static inline void rec(void** ev, int i, cudaStream_t st) {
+  if (ev && ev[i]) cudaEventRecord((cudaEvent_t)ev[i], st);
+}
 // preprocess_fwd.cu
 cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, float4* rec, uint32_t* tiles_touched,
                                   uint8_t* clamped, cudaStream_t st);
@@ -113,6 +119,7 @@ extern "C" {
 #define FDLS_API __attribute__((visibility("default")))
 
 FDLS_API int fdls_abi_version(void) { return 1; }
+FDLS_API uint64_t fdls_kernel_launches(void) { return g_launches.load(std::memory_order_relaxed); }
 
 FDLS_API const char* fdls_strerror(int code) {
   switch (code) {
@@ -153,12 +160,15 @@ FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
   ViewParams vp = make_view(a->viewmatrix, a->projmatrix, a->campos, a->background, a->W, a->H, a->tanfovx, a->tanfovy,
                             a->scale_modifier);
   uint32_t* nr = (uint32_t*)(g + L.num_rendered);
+  rec(a->stage_events, 0, st);
   if (launch_preprocess_fwd(a, vp, (float4*)(g + L.rec), (uint32_t*)(g + L.tiles_touched), (uint8_t*)(g + L.clamped),
                             st) != cudaSuccess)
     return FDLS_ECUDA;
+  rec(a->stage_events, 1, st);
   if (launch_scan(a->P, (uint32_t*)(g + L.tiles_touched), (uint32_t*)(g + L.point_offsets),
                   (uint32_t*)(g + L.scan_scratch), nr, a->capacity, st) != cudaSuccess)
     return FDLS_ECUDA;
+  rec(a->stage_events, 2, st);
   if (a->num_rendered_host &&
       cudaMemcpyAsync(a->num_rendered_host, nr, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st) != cudaSuccess)
     return FDLS_ECUDA;
@@ -195,20 +205,24 @@ FDLS_API int fdls_bin_and_render(const FdlsFwdArgs* a, void* stream) {
     if (launch_duplicate(a->P, (const float4*)(g + L.rec), (const uint32_t*)(g + L.point_offsets), a->radii, k_in, v_in,
                          gx, gy, a->capacity, st) != cudaSuccess)
       return FDLS_ECUDA;
+    rec(a->stage_events, 3, st);
     rc = sort_pairs(k_in, k_out, v_in, v_out, n_grid, nr, end_bit, b + L.sort_scratch, S.binning_bytes - L.sort_scratch,
                     st);
     if (rc < 0) return rc;
+    rec(a->stage_events, 4, st);
     point_list = (const uint32_t*)(b + L.vals);
     if (launch_tile_ranges(nr, n_grid, a->capacity, (const uint64_t*)(b + L.keys), ranges, gx * gy, st) != cudaSuccess)
       return FDLS_ECUDA;
   } else {
     if (cudaMemsetAsync(ranges, 0, (size_t)gx * gy * sizeof(uint2), st) != cudaSuccess) return FDLS_ECUDA;
   }
+  rec(a->stage_events, 5, st);
   const int F = a->include_feature ? a->F : 0;
   if (launch_render_fwd(F, ranges, point_list, (const float4*)(g + L.rec), a->W, a->H, gx, gy, a->background,
                         (float*)(im + L.final_T), (uint32_t*)(im + L.n_contrib), (uint32_t*)(im + L.tile_max_contrib),
                         a->out_color, a->out_language, a->out_depth, st) != cudaSuccess)
     return FDLS_ECUDA;
+  rec(a->stage_events, 6, st);
   return FDLS_OK;
 }
 
@@ -235,7 +249,9 @@ FDLS_API int fdls_backward(const FdlsBwdArgs* a, void* stream) {
   const int gx = cdiv(a->W, TILE), gy = cdiv(a->H, TILE);
   ViewParams vp = make_view(a->viewmatrix, a->projmatrix, a->campos, a->background, a->W, a->H, a->tanfovx, a->tanfovy,
                             a->scale_modifier);
+  rec(a->stage_events, 0, st);
   if (cudaMemsetAsync(a->grad_ws, 0, (size_t)a->P * 16 * sizeof(float), st) != cudaSuccess) return FDLS_ECUDA;
+  rec(a->stage_events, 1, st);
   if (a->num_rendered > 0 && b) {
     const int F = a->include_feature ? a->F : 0;
     if (launch_render_bwd(F, (const uint2*)(im + L.ranges), (const uint32_t*)(b + L.vals), (const float4*)(g + L.rec),
@@ -245,8 +261,10 @@ FDLS_API int fdls_backward(const FdlsBwdArgs* a, void* stream) {
                           st) != cudaSuccess)
       return FDLS_ECUDA;
   }
+  rec(a->stage_events, 2, st);
   if (launch_preprocess_bwd(a, vp, (const uint8_t*)(g + L.clamped), (const float4*)a->grad_ws, st) != cudaSuccess)
     return FDLS_ECUDA;
+  rec(a->stage_events, 3, st);
   return FDLS_OK;
 }
 

@@ -191,16 +191,16 @@ size_t scan_scratch_bytes(int P) { return align_up((size_t)(cdiv(P, SCAN_TILE) +
 cudaError_t launch_scan(int P, const uint32_t* tiles_touched, uint32_t* offsets, uint32_t* block_sums,
                         uint32_t* num_rendered, long long capacity, cudaStream_t st) {
   const int nb = cdiv(P, SCAN_TILE);
-  if (P > 0) scan_reduce_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, block_sums);
-  scan_spine_kernel<<<1, 1024, 0, st>>>(nb, block_sums, num_rendered, capacity, nullptr);
-  if (P > 0) scan_apply_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, block_sums, offsets);
+  if (P > 0) { scan_reduce_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, block_sums); count_launch(); }
+  scan_spine_kernel<<<1, 1024, 0, st>>>(nb, block_sums, num_rendered, capacity, nullptr); count_launch();
+  if (P > 0) { scan_apply_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, block_sums, offsets); count_launch(); }
   return cudaGetLastError();
 }
 
 cudaError_t launch_duplicate(int P, const float4* rec, const uint32_t* offsets, const int* radii, uint64_t* keys,
                              uint32_t* vals, int gx, int gy, long long capacity, cudaStream_t st) {
   if (P == 0) return cudaSuccess;
-  duplicate_keys_kernel<<<cdiv(P, 256), 256, 0, st>>>(P, rec, offsets, radii, keys, vals, gx, gy, capacity);
+  duplicate_keys_kernel<<<cdiv(P, 256), 256, 0, st>>>(P, rec, offsets, radii, keys, vals, gx, gy, capacity); count_launch();
   return cudaGetLastError();
 }
 
@@ -208,7 +208,7 @@ cudaError_t launch_tile_ranges(const uint32_t* num_rendered, long long n_grid, l
                                uint2* ranges, int tiles, cudaStream_t st) {
   cudaError_t e = cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), st);
   if (e != cudaSuccess) return e;
-  if (n_grid > 0) tile_ranges_kernel<<<cdiv(n_grid, 256), 256, 0, st>>>(num_rendered, capacity, keys, ranges);
+  if (n_grid > 0) { tile_ranges_kernel<<<cdiv(n_grid, 256), 256, 0, st>>>(num_rendered, capacity, keys, ranges); count_launch(); }
   return cudaGetLastError();
 }
 

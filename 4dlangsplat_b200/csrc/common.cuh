@@ -114,6 +114,8 @@ struct ViewParams {
   int W, H, gx, gy;
 };
 
+void count_launch(int n = 1);  // api.cu: feeds fdls_kernel_launches()
+
 static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 

@@ -194,13 +194,13 @@ int knn_dist2(int N, const float* xyz, float* out, void* ws, size_t ws_bytes, cu
   KnnWs k = knn_carve(ws, N);
   if (ws_bytes < k.total) return FDLS_EWORKSPACE;
   const int nb = cdiv(N, KNN_BOX);
-  knn_bbox_kernel<<<1, 1024, 0, st>>>(N, xyz, k.mm);
-  knn_morton_kernel<<<cdiv(N, 256), 256, 0, st>>>(N, xyz, k.mm, k.ka, k.va);
+  knn_bbox_kernel<<<1, 1024, 0, st>>>(N, xyz, k.mm); count_launch();
+  knn_morton_kernel<<<cdiv(N, 256), 256, 0, st>>>(N, xyz, k.mm, k.ka, k.va); count_launch();
   int sel = sort_pairs(k.ka, k.kb, k.va, k.vb, N, nullptr, 30, k.sort, k.sort_bytes, st);
   if (sel < 0) return sel;
   const uint32_t* order = sel ? k.vb : k.va;
-  knn_box_kernel<<<nb, KNN_BOX, 0, st>>>(N, xyz, order, k.boxes, k.pts);
-  knn_search_kernel<<<cdiv(N, 256), 256, 0, st>>>(N, nb, k.pts, k.boxes, out);
+  knn_box_kernel<<<nb, KNN_BOX, 0, st>>>(N, xyz, order, k.boxes, k.pts); count_launch();
+  knn_search_kernel<<<cdiv(N, 256), 256, 0, st>>>(N, nb, k.pts, k.boxes, out); count_launch();
   return cudaGetLastError() == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
 }
 

@@ -338,6 +338,7 @@ cudaError_t launch_preprocess_bwd(const FdlsBwdArgs* a, const ViewParams& vp, co
   BwdOut o = {a->dL_dmeans3D, a->dL_dmeans2D, a->dL_dsh, a->dL_dcolors, a->dL_dlanguage, a->dL_dopacity,
               a->dL_dscales, a->dL_drotations, a->dL_dcov3D, a->dL_dconic, a->dL_ddepths};
   const int grid = cdiv(a->P, 256);
+  count_launch();
   if (a->M == 16)
     preprocess_bwd_kernel<true><<<grid, 256, 0, st>>>(a->P, a->D, a->M, a->F, a->means3D, a->radii, a->shs, clamped,
                                                       a->scales, a->rotations, a->cov3D_precomp, vp, grad_rec, o);

@@ -184,13 +184,13 @@ cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, fl
   if (a->P == 0) return cudaSuccess;
   preprocess_fwd_kernel<<<cdiv(a->P, 256), 256, 0, st>>>(
       a->P, a->D, a->M, a->F, a->means3D, a->scales, a->rotations, a->opacities, a->shs, a->cov3D_precomp,
-      a->colors_precomp, a->language_feature, vp, a->radii, rec, tiles_touched, clamped, a->prefiltered);
+      a->colors_precomp, a->language_feature, vp, a->radii, rec, tiles_touched, clamped, a->prefiltered); count_launch();
   return cudaGetLastError();
 }
 
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st) {
   if (P == 0) return cudaSuccess;
-  mark_visible_kernel<<<cdiv(P, 256), 256, 0, st>>>(P, means3D, view, present);
+  mark_visible_kernel<<<cdiv(P, 256), 256, 0, st>>>(P, means3D, view, present); count_launch();
   return cudaGetLastError();
 }
 

@@ -272,7 +272,7 @@ int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* v
   }
   if (cudaMemsetAsync(scratch, 0, sc.header_bytes, st) != cudaSuccess) return FDLS_ECUDA;
   const int tiles = cdiv(n_max, RS_TILE);
-  rs_histogram_kernel<<<tiles, RS_THREADS, 0, st>>>(keys_a, n_max, n_dev, passes, end_bit, sc.global_hist);
+  rs_histogram_kernel<<<tiles, RS_THREADS, 0, st>>>(keys_a, n_max, n_dev, passes, end_bit, sc.global_hist); count_launch();
   uint64_t* kin = keys_a;
   uint64_t* kout = keys_b;
   uint32_t* vin = vals_a;
@@ -282,7 +282,7 @@ int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* v
     const int bits = end_bit - shift < 8 ? end_bit - shift : 8;
     rs_onesweep_kernel<<<tiles, RS_THREADS, sizeof(RsSmem), st>>>(
         kin, kout, vin, vout, n_max, n_dev, shift, bits, sc.global_hist + p * RS_BINS,
-        sc.tile_state + (size_t)p * tiles * RS_BINS, sc.tickets + p, sc.error_flag);
+        sc.tile_state + (size_t)p * tiles * RS_BINS, sc.tickets + p, sc.error_flag); count_launch();
     uint64_t* tk = kin; kin = kout; kout = tk;
     uint32_t* tv = vin; vin = vout; vout = tv;
   }

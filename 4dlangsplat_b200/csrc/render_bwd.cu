@@ -234,6 +234,7 @@ static cudaError_t launch_rb(bool depth_grad, const uint2* ranges, const uint32_
                              int H, int gx, int gy, const float* bg, const float* final_T, const uint32_t* n_contrib,
                              const uint32_t* tile_max, const float* dpix, const float* dpix_F, const float* dpix_D,
                              float* grad_rec, cudaStream_t st) {
+  count_launch();
   if (depth_grad)
     render_bwd_kernel<F, true><<<gx * gy, RB_THREADS, 0, st>>>(ranges, point_list, rec, W, H, gx, bg, final_T,
                                                                n_contrib, tile_max, dpix, dpix_F, dpix_D, grad_rec);

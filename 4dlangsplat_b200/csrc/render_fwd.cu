@@ -146,7 +146,7 @@ static cudaError_t launch_rf(const uint2* ranges, const uint32_t* point_list, co
                              int gy, const float* bg, float* final_T, uint32_t* n_contrib, uint32_t* tile_max,
                              float* out_color, float* out_lang, float* out_depth, cudaStream_t st) {
   render_fwd_kernel<F><<<gx * gy, RF_THREADS, 0, st>>>(ranges, point_list, rec, W, H, gx, bg, final_T, n_contrib,
-                                                       tile_max, out_color, out_lang, out_depth);
+                                                       tile_max, out_color, out_lang, out_depth); count_launch();
   return cudaGetLastError();
 }
 

@@ -1,0 +1,383 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the rasterizer hot path (BASELINE.json: render frames/s on the HyperNeRF
+americano-shaped config: 300k Gaussians, 536x960, RGB + 3 language channels, forward render sweep over timestamps).
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload cfg2]
+
+One step = FRAMES_PER_STEP consecutive timestamps of the render sweep (one forward of the hot path per timestamp).
+Prints ONE JSON line (rank 0).  `value` = frames/s with all inputs resident in HBM; `e2e` = the same through the public
+GaussianRasterizer API with the per-frame inputs (camera, per-timestamp means) in pinned HOST memory and the rendered
+images copied back to the host, copies inside the timed region.  `--impl reference` times the UNMODIFIED reference
+CUDA rasterizer rebuilt for sm_100a (oracle/_ref; the reference has no CPU rasterizer) under the same protocol.
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "oracle")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+FRAMES_PER_STEP = 10
+N_TIMESTAMPS = 100
+N_PARAM_SETS = 3  # static per-Gaussian parameters are cycled over 3 copies (3 x 71 MB > 126 MB L2)
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons with NVML every 100 ms while the timed region runs."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting"}
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.samples, self.reasons, self.max_mhz = index, False, [], set(), None
+
+    def run(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            while not self.stop_flag:
+                self.samples.append(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+                r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h) if hasattr(
+                    pynvml, "nvmlDeviceGetCurrentClocksEventReasons") else pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, name in self.REASONS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                time.sleep(0.1)
+        except Exception as e:  # NVML missing: report nothing rather than fail the bench
+            self.error = str(e)
+
+    def result(self):
+        self.stop_flag = True
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def dist_setup(n_gpus):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return rank, world, local
+
+
+def barrier(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(x, world):
+    if world == 1:
+        return x
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(x, world):
+    if world == 1:
+        return x
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+class Workload:
+    """Synthetic render sweep: per-timestamp Gaussian centres (a smooth displacement stands in for the HexPlane
+    deformation output) + N_PARAM_SETS copies of the static parameters, on the device and mirrored in pinned host memory."""
+
+    def __init__(self, name, rank, world):
+        synth = importlib.import_module("4dlangsplat_b200.synth")
+        self.s = s = synth.scene(name)
+        self.name = name
+        dev = "cuda"
+        t = lambda a: torch.as_tensor(np.ascontiguousarray(a), device=dev)
+        rng = np.random.default_rng(99)
+        amp = rng.normal(0, 0.03, (s.P, 3)).astype(np.float32)
+        phase = rng.uniform(0, 2 * np.pi, (s.P, 1)).astype(np.float32)
+        base, amp_d, phase_d = t(s.means3D), t(amp), t(phase)
+        # this rank's shard of the sweep: timestamps rank, rank+world, ...
+        self.times = [((i * world + rank) % N_TIMESTAMPS) / (N_TIMESTAMPS - 1.0) for i in range(N_TIMESTAMPS)]
+        self.means = [base + amp_d * torch.sin(2 * np.pi * tt + phase_d) for tt in self.times]
+        self.means_host = [m.cpu().pin_memory() for m in self.means]
+        self.sets = []
+        for k in range(N_PARAM_SETS):
+            self.sets.append(dict(scales=t(s.scales).clone(), rots=t(s.rotations).clone(), opac=t(s.opacities).clone(),
+                                  shs=t(s.shs).clone(), lang=t(s.language_feature).clone()))
+        self.view, self.proj, self.campos, self.bg = t(s.viewmatrix), t(s.projmatrix), t(s.campos), t(s.bg)
+        self.cam_host = [x.cpu().pin_memory() for x in (self.view, self.proj, self.campos, self.bg)]
+        self.static_bytes = sum(v.numel() * 4 for v in self.sets[0].values())
+
+
+class EventPool:
+    """cudaEvent_t handles for the C ABI's stage_events hook, one set of `n` per frame."""
+
+    def __init__(self, n, frames):
+        self.n = n
+        self.events = [[torch.cuda.Event(enable_timing=True) for _ in range(n)] for _ in range(frames)]
+        for fr in self.events:  # torch creates the handle lazily on first record
+            for e in fr:
+                e.record()
+        torch.cuda.synchronize()
+        self.arrays = [(C.c_void_p * n)(*[C.c_void_p(e.cuda_event) for e in fr]) for fr in self.events]
+
+    def stage_ms(self, frames):
+        out = np.zeros(self.n - 1)
+        for fr in self.events[:frames]:
+            out += [fr[i].elapsed_time(fr[i + 1]) for i in range(self.n - 1)]
+        return out / max(1, frames)
+
+
+def run_ours(wl, steps, warmup, world):
+    fd = importlib.import_module("4dlangsplat_b200")
+    lib = fd._lib.load()
+    Cmod, s = fd._C, wl.s
+    dgr = fd.diff_gaussian_rasterization
+    E = torch.Tensor([])
+    Rs = []
+
+    def frame(i, record=None):
+        p = wl.sets[i % N_PARAM_SETS]
+        Cmod.profile["fwd"] = record
+        out = Cmod.rasterize_gaussians(wl.bg, wl.means[i % N_TIMESTAMPS], E, p["lang"], p["opac"], p["scales"],
+                                       p["rots"], 1.0, E, wl.view, wl.proj, s.tanfovx, s.tanfovy, s.H, s.W, p["shs"],
+                                       s.sh_degree, wl.campos, False, False, True)
+        Cmod.profile["fwd"] = None
+        return out
+
+    # ---- device-resident arm (value)
+    for i in range(warmup * FRAMES_PER_STEP):
+        frame(i)
+    n_frames = steps * FRAMES_PER_STEP
+    pool = EventPool(fd._lib.FDLS_FWD_EVENTS, n_frames)
+    barrier(world)
+    launches0 = lib.fdls_kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(n_frames):
+        out = frame(i, pool.arrays[i])
+        Rs.append(out[0])
+    e1.record()
+    barrier(world)
+    launches = lib.fdls_kernel_launches() - launches0
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    stage_ms = pool.stage_ms(n_frames)
+    radii = out[4]
+    V = int((radii > 0).sum())
+
+    # ---- end-to-end arm through the public API with host buffers
+    rs_host = wl.cam_host
+    outs_host = [torch.empty((3, s.H, s.W)).pin_memory(), torch.empty((s.F, s.H, s.W)).pin_memory(),
+                 torch.empty((1, s.H, s.W)).pin_memory()]
+    h2d = sum(x.numel() * 4 for x in rs_host) + wl.means_host[0].numel() * 4
+    d2h = sum(x.numel() * 4 for x in outs_host)
+
+    def e2e_frame(i):
+        p = wl.sets[i % N_PARAM_SETS]
+        view, proj, campos, bg = [x.to("cuda", non_blocking=True) for x in rs_host]
+        means = wl.means_host[i % N_TIMESTAMPS].to("cuda", non_blocking=True)
+        settings = dgr.GaussianRasterizationSettings(s.H, s.W, s.tanfovx, s.tanfovy, bg, 1.0, view, proj, s.sh_degree,
+                                                     campos, False, False, True)
+        with torch.no_grad():
+            color, lang, radii_, depth = dgr.GaussianRasterizer(settings)(
+                means3D=means, means2D=None, opacities=p["opac"], shs=p["shs"], language_feature_precomp=p["lang"],
+                scales=p["scales"], rotations=p["rots"])
+        outs_host[0].copy_(color, non_blocking=True)
+        outs_host[1].copy_(lang, non_blocking=True)
+        outs_host[2].copy_(depth, non_blocking=True)
+
+    for i in range(max(1, warmup) * FRAMES_PER_STEP):
+        e2e_frame(i)
+    barrier(world)
+    t0 = time.perf_counter()
+    for k in range(steps):
+        for f in range(FRAMES_PER_STEP):
+            e2e_frame(k * FRAMES_PER_STEP + f)
+        torch.cuda.synchronize()  # the step's images are on the host
+    t1 = time.perf_counter()
+    barrier(world)
+    e2e_s = max_over_ranks(t1 - t0, world)
+    return dict(ms=ms, n_frames=n_frames, stage_ms=stage_ms, R=float(np.mean(Rs)), V=V, launches=int(launches),
+                e2e_s=e2e_s, h2d=h2d * FRAMES_PER_STEP, d2h=d2h * FRAMES_PER_STEP)
+
+
+def run_reference(wl, steps, warmup, world):
+    import refcuda
+    s = wl.s
+    ref = refcuda.Ref(s.F)
+    M = s.shs.shape[1]
+    f32 = dict(dtype=torch.float32, device="cuda")
+    color, lang, depth = torch.empty((3, s.H, s.W), **f32), torch.empty((s.F, s.H, s.W), **f32), torch.empty((1, s.H, s.W), **f32)
+    radii = torch.empty(s.P, dtype=torch.int32, device="cuda")
+    Rs = []
+
+    def frame(i, means=None, cam=None):
+        p = wl.sets[i % N_PARAM_SETS]
+        view, proj, campos, bg = cam if cam is not None else (wl.view, wl.proj, wl.campos, wl.bg)
+        m = means if means is not None else wl.means[i % N_TIMESTAMPS]
+        # the reference's torch glue fills its outputs before the kernels run (rasterize_points.cu:70-78)
+        color.zero_(); lang.zero_(); depth.zero_(); radii.zero_()
+        return ref.forward_raw(s.P, s.sh_degree, M, s.W, s.H, bg, m, p["shs"], p["lang"], p["opac"], p["scales"],
+                               p["rots"], view, proj, campos, s.tanfovx, s.tanfovy, color, lang, depth, radii)
+
+    for i in range(warmup * FRAMES_PER_STEP):
+        frame(i)
+    n_frames = steps * FRAMES_PER_STEP
+    barrier(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(n_frames):
+        Rs.append(frame(i))
+    e1.record()
+    barrier(world)
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    V = int((radii > 0).sum())
+    outs_host = [torch.empty((3, s.H, s.W)).pin_memory(), torch.empty((s.F, s.H, s.W)).pin_memory(),
+                 torch.empty((1, s.H, s.W)).pin_memory()]
+    h2d = sum(x.numel() * 4 for x in wl.cam_host) + wl.means_host[0].numel() * 4
+    d2h = sum(x.numel() * 4 for x in outs_host)
+
+    def e2e_frame(i):
+        cam = [x.to("cuda", non_blocking=True) for x in wl.cam_host]
+        means = wl.means_host[i % N_TIMESTAMPS].to("cuda", non_blocking=True)
+        frame(i, means, cam)
+        outs_host[0].copy_(color, non_blocking=True)
+        outs_host[1].copy_(lang, non_blocking=True)
+        outs_host[2].copy_(depth, non_blocking=True)
+
+    for i in range(max(1, warmup) * FRAMES_PER_STEP):
+        e2e_frame(i)
+    barrier(world)
+    t0 = time.perf_counter()
+    for k in range(steps):
+        for f in range(FRAMES_PER_STEP):
+            e2e_frame(k * FRAMES_PER_STEP + f)
+        torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    barrier(world)
+    e2e_s = max_over_ranks(t1 - t0, world)
+    return dict(ms=ms, n_frames=n_frames, stage_ms=None, R=float(np.mean(Rs)), V=V, launches=0, e2e_s=e2e_s,
+                h2d=h2d * FRAMES_PER_STEP, d2h=d2h * FRAMES_PER_STEP)
+
+
+def cpu_baseline(wl, frames=1):
+    """CPU restatement (oracle/raster_oracle.cpp, OpenMP over all host cores) of the same forward on a bounded sample."""
+    import oracle as orc
+    s = wl.s
+    orc.build()
+    t0 = time.perf_counter()
+    for i in range(frames):
+        m = wl.means_host[i].numpy()
+        orc.forward(m, s.opacities, s.viewmatrix, s.projmatrix, s.campos, s.W, s.H, s.tanfovx, s.tanfovy, s.bg,
+                    shs=s.shs, language_feature=s.language_feature, scales=s.scales, rotations=s.rotations)
+    dt = time.perf_counter() - t0
+    return {"value": frames / dt, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": "%d forward frame(s) of %s on the host (C++/OpenMP restatement of the reference CUDA "
+                      "rasterizer; the reference has no CPU rasterizer)" % (frames, wl.name)}
+
+
+def stage_bytes(P, V, R, HW, T, F):
+    """Algorithmic bytes per launch sequence of each forward stage."""
+    return {"preprocess": 48 * P + 232 * V, "scan": 8 * P, "duplicate": 20 * P + 12 * R, "sort": 24 * R,
+            "tile_ranges": 8 * R + 8 * T, "render": (44 + 4 * F) * R + (24 + 4 * F) * HW}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    rank, world, local = dist_setup(a.gpus)
+    warmup = max(3, a.warmup)
+    wl = Workload(a.workload, rank, world)
+    s = wl.s
+    sampler = ClockSampler(local)
+    sampler.start()
+    r = (run_ours if a.impl == "ours" else run_reference)(wl, a.steps, warmup, world)
+    clocks = sampler.result()
+    total_frames = r["n_frames"] * world
+    value = total_frames / (r["ms"] * 1e-3)
+    e2e_value = total_frames / r["e2e_s"]
+    pk, pk_kind = peaks()
+    HW, T = s.W * s.H, ((s.W + 15) // 16) * ((s.H + 15) // 16)
+    line = {
+        "metric": "render_frames_per_s", "value": round(value, 2), "unit": "frames/s", "n_gpus": world,
+        "steps": a.steps, "warmup": warmup, "ms_per_step": round(r["ms"] / a.steps, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "%s: %d Gaussians, %dx%d, RGB + %d language channels + depth, forward render sweep, "
+                               "%d timestamps per step" % (a.workload, s.P, s.W, s.H, s.F, FRAMES_PER_STEP),
+                   "frames_per_step": FRAMES_PER_STEP, "sh_degree": 3, "instances_per_frame": round(r["R"]),
+                   "visible_gaussians": r["V"], "sharding": "timestamps round-robin over ranks, no collective",
+                   "l2": "static parameters cycled over %d copies (%d MB) > 126 MB L2; per-timestamp means differ"
+                         % (N_PARAM_SETS, N_PARAM_SETS * wl.static_bytes // 2 ** 20)},
+        "clocks": clocks,
+        "e2e": {"value": round(e2e_value, 2), "unit": "frames/s", "h2d_bytes_per_step": r["h2d"],
+                "d2h_bytes_per_step": r["d2h"]},
+        "gpu_launches": r["launches"],
+    }
+    if a.impl == "ours":
+        names = ["preprocess", "scan", "duplicate", "sort", "tile_ranges", "render"]
+        sb = stage_bytes(s.P, r["V"], r["R"], HW, T, s.F)
+        st = dict(zip(names, [float(x) for x in r["stage_ms"]]))
+        dom = max(st, key=st.get)
+        ach = sb[dom] / (st[dom] * 1e-3) / 1e9
+        line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": round(ach, 1), "peak": pk["hbm_gbs"],
+                            "unit": "GB/s", "frac": round(ach / pk["hbm_gbs"], 4), "traffic": None,
+                            "peak_source": pk_kind + " (MEASURED_PEAKS.json hbm_gbs)" if pk_kind == "measured" else "fallback",
+                            "algorithmic_bytes_per_launch": int(sb[dom]), "avg_launch_ms": round(st[dom], 4)}
+        total_b = 48 * s.P + 232 * r["V"] + (80 + 4 * s.F) * r["R"] + (24 + 4 * s.F) * HW
+        line["stages_ms"] = {k: round(v, 4) for k, v in st.items()}
+        line["stages_gbs"] = {k: round(sb[k] / (st[k] * 1e-3) / 1e9, 1) if st[k] > 0 else None for k in names}
+        line["whole_path"] = {"algorithmic_bytes_per_frame": int(total_b),
+                              "achieved_gbs": round(total_b / (r["ms"] / r["n_frames"] * 1e-3) / 1e9, 1)}
+        if rank == 0 and world == 1 and not a.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(wl)
+    else:
+        line["impl"] = "reference"
+        line["cpu_baseline"] = {"value": line["value"], "unit": "frames/s", "cores": 1, "kind": "reference",
+                                "sample": "the reference has no CPU rasterizer: its own CUDA rasterizer "
+                                          "(cuda_rasterizer/*.cu, unmodified, rebuilt for sm_100a into oracle/_ref) is "
+                                          "timed on the same B200 over the same %d frames; 1 host thread drives it"
+                                          % r["n_frames"]}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

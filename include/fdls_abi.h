@@ -108,7 +108,11 @@ typedef struct FdlsFwdArgs {
   uint32_t* num_rendered_host;
   /* host-known instance count for grid sizing in fdls_bin_and_render; <0 = unknown, size grids by capacity */
   int64_t num_rendered_hint;
+  /* optional: array of FDLS_FWD_EVENTS cudaEvent_t handles recorded on the stream between stages
+   * [0] start, [1] preprocess, [2] scan, [3] duplicate, [4] sort, [5] tile ranges, [6] compositor; null = off */
+  void** stage_events;
 } FdlsFwdArgs;
+#define FDLS_FWD_EVENTS 7
 
 typedef struct FdlsBwdArgs {
   int32_t P, D, M, F, W, H;
@@ -147,9 +151,14 @@ typedef struct FdlsBwdArgs {
   float* dL_dcov3D;    /* (P,6) */
   float* dL_dconic;    /* (P,4) optional (reference returns it internally only) */
   float* dL_ddepths;   /* (P) optional */
+  /* optional: FDLS_BWD_EVENTS cudaEvent_t handles: [0] start, [1] zero-fill, [2] compositor bwd, [3] preprocess bwd */
+  void** stage_events;
 } FdlsBwdArgs;
+#define FDLS_BWD_EVENTS 4
 
 int fdls_abi_version(void);
+/* number of kernels this library has launched in this process so far (bench.py reports the delta as gpu_launches) */
+uint64_t fdls_kernel_launches(void);
 const char* fdls_strerror(int code);
 
 int fdls_workspace_sizes(int32_t P, int32_t W, int32_t H, int64_t capacity, FdlsWorkspaceSizes* out);

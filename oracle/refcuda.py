@@ -1,4 +1,4 @@
-"""TEST INFRASTRUCTURE: ctypes driver of oracle/_ref/libref_f{F}.so -- the UNMODIFIED reference CUDA rasterizer
+"""TEST INFRASTRUCTURE ONLY (used by tests/, __graft_entry__.smoke() and bench.py's reference arm): ctypes driver of oracle/_ref/libref_f{F}.so -- the UNMODIFIED reference CUDA rasterizer
 built for sm_100a by oracle/build_ref.py (prebuilt here, shipped to the GPU box; /root/reference is not needed at run
 time).  Device memory comes from torch.  Never imported by the product package."""
 import ctypes as C
@@ -8,12 +8,12 @@ from types import SimpleNamespace
 import numpy as np
 import torch
 
-_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_HERE = os.path.dirname(os.path.abspath(__file__))
 _libs = {}
 
 
 def lib_path(F):
-    return os.path.join(_ROOT, "oracle", "_ref", "libref_f%d.so" % F)
+    return os.path.join(_HERE, "_ref", "libref_f%d.so" % F)
 
 
 def available(F=3):
@@ -112,6 +112,23 @@ class Ref:
         o.point_list_unsorted = _view(st.point_list_unsorted, R, torch.int32, dev)
         self.out = o
         return o
+
+    def forward_raw(self, P, D, M, W, H, bg, means3D, shs, lang, opac, scales, rots, view, proj, campos, tanfovx,
+                    tanfovy, out_color, out_lang, out_depth, radii, include_feature=True, scale_modifier=1.0):
+        """Lean call for timing: torch CUDA tensors in, no intermediate read-back, debug off.  Returns R."""
+        return self.L.ref_forward(self.h, P, D, M, _p(bg), W, H, _p(means3D), _p(shs), _p(None), _p(lang), _p(opac),
+                                  _p(scales), C.c_float(scale_modifier), _p(rots), _p(None), _p(view), _p(proj),
+                                  _p(campos), C.c_float(tanfovx), C.c_float(tanfovy), 0, _p(out_color), _p(out_lang),
+                                  _p(out_depth), _p(radii), 0, int(include_feature))
+
+    def backward_raw(self, P, D, M, R, W, H, bg, means3D, shs, lang, scales, rots, view, proj, campos, tanfovx, tanfovy,
+                     radii, dcol, dlang, ddepth, g, include_feature=True, scale_modifier=1.0):
+        """Lean backward for timing; `g` is a namespace of pre-zeroed gradient tensors (see backward())."""
+        self.L.ref_backward(self.h, P, D, M, R, _p(bg), W, H, _p(means3D), _p(shs), _p(None), _p(lang), _p(scales),
+                            C.c_float(scale_modifier), _p(rots), _p(None), _p(view), _p(proj), _p(campos),
+                            C.c_float(tanfovx), C.c_float(tanfovy), _p(radii), _p(dcol), _p(dlang), _p(ddepth),
+                            _p(g.means2D), _p(g.conic), _p(g.opacity), _p(g.colors), _p(g.lang), _p(g.depths),
+                            _p(g.means3D), _p(g.cov3D), _p(g.sh), _p(g.scales), _p(g.rots), 0, int(include_feature))
 
     def backward(self, dcol, dlang, ddepth, dev="cuda"):
         s, i, o, F = self.s, self.inp, self.out, self.F

@@ -31,6 +31,11 @@ def _assert_same(a, b, what):
     assert n == 0, "%s: %d of %d elements differ" % (what, n, a.numel())
 
 
+def _assert_grad(a, b, what):
+    ok, msg = helpers.grad_close(a, b, GRAD_RTOL)
+    assert ok, "%s: %s" % (what, msg)
+
+
 def _assert_close(a, b, rtol, what, atol_frac=1e-6):
     ok, worst, nbad = helpers.rel_close(a, b, rtol, atol_frac)
     assert ok, "%s: %d elements outside rtol=%g (worst rel err %.3g)" % (what, nbad, rtol, worst)
@@ -89,7 +94,7 @@ def test_backward_matches_reference(synth, name, F, bg, depth_grad):
                      ("opacity", g.opacity, gr.opacity), ("means3D", g.means3D, gr.means3D),
                      ("cov3D", g.cov3D, gr.cov3D), ("sh", g.sh, gr.sh), ("scales", g.scales, gr.scales),
                      ("rots", g.rots, gr.rots)):
-        _assert_close(a, b, GRAD_RTOL, "dL_d" + nm, atol_frac=1e-5)
+        _assert_grad(a, b, "dL_d" + nm)
 
 
 def test_no_feature_and_precomputed_inputs(synth):
@@ -125,7 +130,7 @@ def test_no_feature_and_precomputed_inputs(synth):
         if inc:
             pairs.append(("lang", g.lang, gr.lang))
         for nm, a, b in pairs:
-            _assert_close(a, b, GRAD_RTOL, "dL_d%s %s" % (nm, list(kw)), atol_frac=1e-5)
+            _assert_grad(a, b, "dL_d%s %s" % (nm, list(kw)))
 
 
 def test_speculative_and_exact_modes_agree(synth, monkeypatch):
