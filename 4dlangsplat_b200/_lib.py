@@ -24,6 +24,7 @@ class FdlsWorkspaceSizes(C.Structure):
 class FdlsLayout(C.Structure):
     _fields_ = [(n, C.c_size_t) for n in (
         "rec", "tiles_touched", "point_offsets", "clamped", "num_rendered", "scan_scratch",
+        "depth_order", "depth_scratch",
         "final_T", "n_contrib", "ranges", "tile_max_contrib",
         "keys_alt", "keys", "vals_alt", "vals", "sort_scratch")]
 
@@ -83,7 +84,7 @@ SYMBOLS = {
     "fdls_knn_dist2": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "fdls_sort_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "fdls_sort_pairs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int,
-                                  C.c_void_p, C.c_size_t, C.c_void_p]),
+                                  C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
 }
 
 _lib = None

@@ -13,20 +13,21 @@ static inline void rec(void** ev, int i, cudaStream_t st) {
 }
 // preprocess_fwd.cu
 cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, float4* rec, uint32_t* tiles_touched,
-                                  uint8_t* clamped, cudaStream_t st);
+                                  uint8_t* clamped, uint64_t* depth_keys, uint32_t* depth_vals, cudaStream_t st);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 // binning.cu
 size_t scan_scratch_bytes(int P);
-cudaError_t launch_scan(int P, const uint32_t* tiles_touched, uint32_t* offsets, uint32_t* block_sums,
-                        uint32_t* num_rendered, long long capacity, cudaStream_t st);
-cudaError_t launch_duplicate(int P, const float4* rec, const uint32_t* offsets, const int* radii, uint64_t* keys,
-                             uint32_t* vals, int gx, int gy, long long capacity, cudaStream_t st);
+cudaError_t launch_scan(int P, const uint32_t* tiles_touched, const uint32_t* order, uint32_t* offsets,
+                        uint32_t* block_sums, uint32_t* num_rendered, long long capacity, cudaStream_t st);
+cudaError_t launch_duplicate(int P, const float4* rec, const uint32_t* order, const uint32_t* offsets, const int* radii,
+                             uint64_t* keys, uint32_t* vals, int gx, int gy, long long capacity, cudaStream_t st);
 cudaError_t launch_tile_ranges(const uint32_t* num_rendered, long long n_grid, long long capacity, const uint64_t* keys,
                                uint2* ranges, int tiles, cudaStream_t st);
 // radix_sort.cu
 size_t sort_scratch_bytes(long long n_max);
 int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
-               const uint32_t* n_dev, int end_bit, void* scratch, size_t scratch_bytes, cudaStream_t st);
+               const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes,
+               cudaStream_t st);
 // render_fwd.cu / render_bwd.cu / preprocess_bwd.cu
 cudaError_t launch_render_fwd(int F, const uint2* ranges, const uint32_t* point_list, const float4* rec, int W, int H,
                               int gx, int gy, const float* bg, float* final_T, uint32_t* n_contrib, uint32_t* tile_max,
@@ -65,6 +66,8 @@ static void compute_layout(int P, int W, int H, long long capacity, FdlsLayout* 
   L->clamped = o;       o += align_up(Pz);
   L->num_rendered = o;  o += align_up(16);
   L->scan_scratch = o;  o += scan_scratch_bytes((int)Pz);
+  L->depth_order = o;   o += align_up(Pz * 4);
+  L->depth_scratch = o; o += align_up(Pz * 8) * 2 + align_up(Pz * 4) + sort_scratch_bytes((long long)Pz);
   S->geom_bytes = o;
   o = 0;
   L->final_T = o;          o += align_up(HW * 4);
@@ -161,11 +164,24 @@ FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
                             a->scale_modifier);
   uint32_t* nr = (uint32_t*)(g + L.num_rendered);
   rec(a->stage_events, 0, st);
+  // depth-sort scratch: [keys_a | keys_b | vals_b | onesweep scratch]; vals_a is depth_order itself when the pass
+  // count is even (4 passes over 32 bits), so the sorted order lands in L.depth_order
+  const size_t Pz = (size_t)(a->P < 1 ? 1 : a->P);
+  uint64_t* dk_a = (uint64_t*)(g + L.depth_scratch);
+  uint64_t* dk_b = (uint64_t*)(g + L.depth_scratch + align_up(Pz * 8));
+  uint32_t* dv_b = (uint32_t*)(g + L.depth_scratch + 2 * align_up(Pz * 8));
+  char* dscr = g + L.depth_scratch + 2 * align_up(Pz * 8) + align_up(Pz * 4);
+  uint32_t* order = (uint32_t*)(g + L.depth_order);
   if (launch_preprocess_fwd(a, vp, (float4*)(g + L.rec), (uint32_t*)(g + L.tiles_touched), (uint8_t*)(g + L.clamped),
-                            st) != cudaSuccess)
+                            dk_a, order, st) != cudaSuccess)
     return FDLS_ECUDA;
   rec(a->stage_events, 1, st);
-  if (launch_scan(a->P, (uint32_t*)(g + L.tiles_touched), (uint32_t*)(g + L.point_offsets),
+  // (1) order the GAUSSIANS by depth bits (stable, P elements) ...
+  int sel = sort_pairs(dk_a, dk_b, order, dv_b, a->P, nullptr, 0, 32, dscr, sort_scratch_bytes((long long)Pz), st);
+  if (sel < 0) return sel;
+  if (sel != 0) return FDLS_ECUDA;  // 4 passes: result is back in the `a` buffers by construction
+  // (2) ... and scan the tile counts in that order, so instances are emitted depth-sorted
+  if (launch_scan(a->P, (uint32_t*)(g + L.tiles_touched), order, (uint32_t*)(g + L.point_offsets),
                   (uint32_t*)(g + L.scan_scratch), nr, a->capacity, st) != cudaSuccess)
     return FDLS_ECUDA;
   rec(a->stage_events, 2, st);
@@ -195,19 +211,22 @@ FDLS_API int fdls_bin_and_render(const FdlsFwdArgs* a, void* stream) {
   uint2* ranges = (uint2*)(im + L.ranges);
   const uint32_t* point_list = nullptr;
   if (n_grid > 0) {
-    const int end_bit = 32 + (int)higher_msb((uint32_t)(gx * gy));  // rasterizer_impl.cu:304
-    const int passes = (end_bit + 7) / 8;
+    // Instances were emitted in depth order, so a STABLE sort on the tile bits alone yields exactly the order of the
+    // reference's sort on bits [0, 32+bit) (rasterizer_impl.cu:304-312): 2 passes over R instead of 6.
+    const int end_bit = 32 + (int)higher_msb((uint32_t)(gx * gy));
+    const int passes = (end_bit - 32 + 7) / 8;
     // choose the input buffer so that the sorted result lands in (keys, vals)
     uint64_t* k_in = (uint64_t*)(b + ((passes & 1) ? L.keys_alt : L.keys));
     uint64_t* k_out = (uint64_t*)(b + ((passes & 1) ? L.keys : L.keys_alt));
     uint32_t* v_in = (uint32_t*)(b + ((passes & 1) ? L.vals_alt : L.vals));
     uint32_t* v_out = (uint32_t*)(b + ((passes & 1) ? L.vals : L.vals_alt));
-    if (launch_duplicate(a->P, (const float4*)(g + L.rec), (const uint32_t*)(g + L.point_offsets), a->radii, k_in, v_in,
-                         gx, gy, a->capacity, st) != cudaSuccess)
+    if (launch_duplicate(a->P, (const float4*)(g + L.rec), (const uint32_t*)(g + L.depth_order),
+                         (const uint32_t*)(g + L.point_offsets), a->radii, k_in, v_in, gx, gy, a->capacity,
+                         st) != cudaSuccess)
       return FDLS_ECUDA;
     rec(a->stage_events, 3, st);
-    rc = sort_pairs(k_in, k_out, v_in, v_out, n_grid, nr, end_bit, b + L.sort_scratch, S.binning_bytes - L.sort_scratch,
-                    st);
+    rc = sort_pairs(k_in, k_out, v_in, v_out, n_grid, nr, 32, end_bit, b + L.sort_scratch,
+                    S.binning_bytes - L.sort_scratch, st);
     if (rc < 0) return rc;
     rec(a->stage_events, 4, st);
     point_list = (const uint32_t*)(b + L.vals);
@@ -285,9 +304,11 @@ FDLS_API int fdls_knn_dist2(int32_t N, const float* xyz, float* out_dist2, void*
 FDLS_API size_t fdls_sort_scratch_bytes(int64_t n_max) { return sort_scratch_bytes(n_max); }
 
 FDLS_API int fdls_sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, int64_t n_max,
-                             const uint32_t* n_dev, int end_bit, void* scratch, size_t scratch_bytes, void* stream) {
+                             const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes,
+                             void* stream) {
   if (n_max < 0 || (n_max > 0 && (!keys_a || !keys_b || !vals_a || !vals_b || !scratch))) return FDLS_EINVAL;
-  return sort_pairs(keys_a, keys_b, vals_a, vals_b, n_max, n_dev, end_bit, scratch, scratch_bytes, (cudaStream_t)stream);
+  return sort_pairs(keys_a, keys_b, vals_a, vals_b, n_max, n_dev, begin_bit, end_bit, scratch, scratch_bytes,
+                    (cudaStream_t)stream);
 }
 
 }  // extern "C"

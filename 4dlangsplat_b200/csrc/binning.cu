@@ -44,14 +44,15 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t& total,
 }
 
 __global__ void __launch_bounds__(SCAN_THREADS)
-scan_reduce_kernel(int P, const uint32_t* __restrict__ in, uint32_t* __restrict__ block_sums) {
+scan_reduce_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __restrict__ order,
+                   uint32_t* __restrict__ block_sums) {
   __shared__ uint32_t s_warp[33];
   const int base = blockIdx.x * SCAN_TILE;
   uint32_t s = 0;
 #pragma unroll
   for (int i = 0; i < SCAN_ITEMS; ++i) {
     int k = base + i * SCAN_THREADS + threadIdx.x;
-    if (k < P) s += in[k];
+    if (k < P) s += in[order ? order[k] : k];
   }
   uint32_t total;
   block_excl_scan<SCAN_THREADS>(s, total, s_warp);
@@ -79,14 +80,25 @@ scan_spine_kernel(int nblocks, uint32_t* __restrict__ block_sums, uint32_t* __re
 }
 
 __global__ void __launch_bounds__(SCAN_THREADS)
-scan_apply_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __restrict__ block_sums,
-                  uint32_t* __restrict__ out) {
+scan_apply_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __restrict__ order,
+                  const uint32_t* __restrict__ block_sums, uint32_t* __restrict__ out) {
   __shared__ uint32_t s_warp[33];
   // blocked arrangement: thread t owns items [t*ITEMS, t*ITEMS+ITEMS) of the block tile
   const int base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
   uint32_t v[SCAN_ITEMS];
   uint32_t s = 0;
-  if (base + SCAN_ITEMS <= P) {
+  if (order != nullptr) {  // gather in depth order
+    if (base + SCAN_ITEMS <= P) {
+      const uint4* p4 = reinterpret_cast<const uint4*>(order + base);
+      const uint4 a = p4[0], b = p4[1];
+      const uint32_t id[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < SCAN_ITEMS; ++i) v[i] = in[id[i]];
+    } else {
+#pragma unroll
+      for (int i = 0; i < SCAN_ITEMS; ++i) v[i] = (base + i < P) ? in[order[base + i]] : 0;
+    }
+  } else if (base + SCAN_ITEMS <= P) {
     const uint4* p4 = reinterpret_cast<const uint4*>(in + base);
     uint4 a = p4[0], b = p4[1];
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
@@ -114,19 +126,21 @@ scan_apply_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __rest
   }
 }
 
-// rasterizer_impl.cu:70-111, warp-cooperative.  Emission order per Gaussian is y-major, x-minor at
-// offsets[idx-1] + i exactly as in the reference, so the unsorted arrays are identical too.
+// rasterizer_impl.cu:70-111, warp-cooperative.  Thread `pos` handles the pos-th Gaussian in DEPTH order
+// (order[pos]); within a Gaussian the tiles are emitted y-major, x-minor like the reference.  Because instances
+// leave this kernel already depth-sorted, the following stable sort only has to look at the tile bits.
 __global__ void __launch_bounds__(256)
-duplicate_keys_kernel(int P, const float4* __restrict__ rec, const uint32_t* __restrict__ offsets,
-                      const int* __restrict__ radii, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, int gx,
-                      int gy, long long capacity) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+duplicate_keys_kernel(int P, const float4* __restrict__ rec, const uint32_t* __restrict__ order,
+                      const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
+                      uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, int gx, int gy, long long capacity) {
+  const int pos = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
-  int radius = idx < P ? radii[idx] : 0;
+  const int idx = pos < P ? (int)order[pos] : 0;
+  int radius = pos < P ? radii[idx] : 0;
   uint32_t off = 0, depth_bits = 0, count = 0;
   uint2 rmin = {0, 0}, rmax = {0, 0};
   if (radius > 0) {
-    off = (idx == 0) ? 0 : offsets[idx - 1];
+    off = (pos == 0) ? 0 : offsets[pos - 1];
     const float4 r0 = rec[(size_t)idx * 4];
     depth_bits = __float_as_uint(rec[(size_t)idx * 4 + 1].z);
     get_rect(r0.x, r0.y, radius, gx, gy, rmin, rmax);
@@ -188,19 +202,20 @@ tile_ranges_kernel(const uint32_t* __restrict__ num_rendered, long long capacity
 
 size_t scan_scratch_bytes(int P) { return align_up((size_t)(cdiv(P, SCAN_TILE) + 1) * sizeof(uint32_t)); }
 
-cudaError_t launch_scan(int P, const uint32_t* tiles_touched, uint32_t* offsets, uint32_t* block_sums,
-                        uint32_t* num_rendered, long long capacity, cudaStream_t st) {
+cudaError_t launch_scan(int P, const uint32_t* tiles_touched, const uint32_t* order, uint32_t* offsets,
+                        uint32_t* block_sums, uint32_t* num_rendered, long long capacity, cudaStream_t st) {
   const int nb = cdiv(P, SCAN_TILE);
-  if (P > 0) { scan_reduce_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, block_sums); count_launch(); }
+  if (P > 0) { scan_reduce_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, order, block_sums); count_launch(); }
   scan_spine_kernel<<<1, 1024, 0, st>>>(nb, block_sums, num_rendered, capacity, nullptr); count_launch();
-  if (P > 0) { scan_apply_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, block_sums, offsets); count_launch(); }
+  if (P > 0) { scan_apply_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, order, block_sums, offsets); count_launch(); }
   return cudaGetLastError();
 }
 
-cudaError_t launch_duplicate(int P, const float4* rec, const uint32_t* offsets, const int* radii, uint64_t* keys,
-                             uint32_t* vals, int gx, int gy, long long capacity, cudaStream_t st) {
+cudaError_t launch_duplicate(int P, const float4* rec, const uint32_t* order, const uint32_t* offsets,
+                             const int* radii, uint64_t* keys, uint32_t* vals, int gx, int gy, long long capacity,
+                             cudaStream_t st) {
   if (P == 0) return cudaSuccess;
-  duplicate_keys_kernel<<<cdiv(P, 256), 256, 0, st>>>(P, rec, offsets, radii, keys, vals, gx, gy, capacity); count_launch();
+  duplicate_keys_kernel<<<cdiv(P, 256), 256, 0, st>>>(P, rec, order, offsets, radii, keys, vals, gx, gy, capacity); count_launch();
   return cudaGetLastError();
 }
 

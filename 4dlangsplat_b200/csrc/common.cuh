@@ -114,6 +114,35 @@ struct ViewParams {
   int W, H, gx, gy;
 };
 
+// Conservative per-tile visibility summary of one Gaussian, computed once by the thread that stages it:
+//   .x = thr : alpha = opacity*exp(power) is certainly < 1/255 whenever power < thr
+//   .y = bits: bit w set iff the 16x2-pixel strip of warp w (rows 2w, 2w+1 of the tile) can contain a pixel with
+//              power >= thr.  Uses max_dx power(dx,dy) = -0.5*dy^2*det/A (and the same in x for the whole tile).
+// Only ever used to SKIP work whose result the exact reference tests would discard anyway; the slack terms (1.001
+// relative, +0.05 px, 0.01 in the log domain) are orders of magnitude above fp32 rounding of the exact expression.
+__device__ __forceinline__ float2 strip_summary(float gx_, float gy_, float A, float B, float Cc, float op, float tile_x0,
+                                                float tile_y0) {
+  const float thr = -__logf(255.0f * op) - 0.01f;
+  uint32_t bits = 0xffu;
+  const float det = A * Cc - B * B;
+  if (thr >= 0.0f) {
+    bits = 0;  // opacity below 1/255: can never pass the alpha test (power <= 0 for every evaluated pair)
+  } else if (det > 0.0f && A > 0.0f && Cc > 0.0f) {
+    const float k = -2.0f * thr / det * 1.001f;
+    const float ymax = sqrtf(k * A) + 0.05f, xmax = sqrtf(k * Cc) + 0.05f;
+    if (gx_ + xmax < tile_x0 || gx_ - xmax > tile_x0 + (TILE - 1)) {
+      bits = 0;
+    } else {
+      const float lo = gy_ - ymax - tile_y0, hi = gy_ + ymax - tile_y0;  // admissible rows, tile-relative
+      bits = 0;
+#pragma unroll
+      for (int w = 0; w < TILE / 2; ++w)
+        if (hi >= (float)(2 * w) && lo <= (float)(2 * w + 1)) bits |= 1u << w;
+    }
+  }  // otherwise (degenerate / NaN conic): keep every strip
+  return make_float2(thr, __uint_as_float(bits));
+}
+
 void count_launch(int n = 1);  // api.cu: feeds fdls_kernel_launches()
 
 static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }

@@ -11,7 +11,8 @@
 namespace fdls {
 
 int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
-               const uint32_t* n_dev, int end_bit, void* scratch, size_t scratch_bytes, cudaStream_t st);
+               const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes,
+               cudaStream_t st);
 size_t sort_scratch_bytes(long long n_max);
 
 constexpr int KNN_BOX = 1024;
@@ -196,7 +197,7 @@ int knn_dist2(int N, const float* xyz, float* out, void* ws, size_t ws_bytes, cu
   const int nb = cdiv(N, KNN_BOX);
   knn_bbox_kernel<<<1, 1024, 0, st>>>(N, xyz, k.mm); count_launch();
   knn_morton_kernel<<<cdiv(N, 256), 256, 0, st>>>(N, xyz, k.mm, k.ka, k.va); count_launch();
-  int sel = sort_pairs(k.ka, k.kb, k.va, k.vb, N, nullptr, 30, k.sort, k.sort_bytes, st);
+  int sel = sort_pairs(k.ka, k.kb, k.va, k.vb, N, nullptr, 0, 30, k.sort, k.sort_bytes, st);
   if (sel < 0) return sel;
   const uint32_t* order = sel ? k.vb : k.va;
   knn_box_kernel<<<nb, KNN_BOX, 0, st>>>(N, xyz, order, k.boxes, k.pts); count_launch();

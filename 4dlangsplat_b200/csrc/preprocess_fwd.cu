@@ -89,7 +89,8 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
                       const float* __restrict__ shs, const float* __restrict__ cov3D_precomp,
                       const float* __restrict__ colors_precomp, const float* __restrict__ lang, ViewParams vp,
                       int* __restrict__ radii, float4* __restrict__ rec, uint32_t* __restrict__ tiles_touched,
-                      uint8_t* __restrict__ clamped, int prefiltered) {
+                      uint8_t* __restrict__ clamped, uint64_t* __restrict__ depth_keys,
+                      uint32_t* __restrict__ depth_vals, int prefiltered) {
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   if (threadIdx.x < 16) s_view[threadIdx.x] = vp.view[threadIdx.x];
   else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = vp.proj[threadIdx.x - 16];
@@ -100,6 +101,7 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
 
   int out_radius = 0;
   uint32_t out_tiles = 0;
+  uint32_t out_depth_bits = 0xffffffffu;  // culled Gaussians sort behind every visible one (depth > 0.2 => sign bit 0)
   do {
     const float3 p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
     // in_frustum (auxiliary.h:139-164): only the near-plane test is live.
@@ -164,9 +166,12 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
     r[3] = make_float4(l[2], l[3], l[4], l[5]);
     out_radius = my_radius;
     out_tiles = (rect_max.y - rect_min.y) * (rect_max.x - rect_min.x);
+    out_depth_bits = __float_as_uint(p_view.z);
   } while (0);
   radii[idx] = out_radius;
   tiles_touched[idx] = out_tiles;
+  depth_keys[idx] = out_depth_bits;  // input of the P-element depth sort (api.cu)
+  depth_vals[idx] = idx;
 }
 
 // markVisible / checkFrustum (rasterizer_impl.cu:54-66)
@@ -180,11 +185,12 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
 }
 
 cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, float4* rec, uint32_t* tiles_touched,
-                                  uint8_t* clamped, cudaStream_t st) {
+                                  uint8_t* clamped, uint64_t* depth_keys, uint32_t* depth_vals, cudaStream_t st) {
   if (a->P == 0) return cudaSuccess;
   preprocess_fwd_kernel<<<cdiv(a->P, 256), 256, 0, st>>>(
       a->P, a->D, a->M, a->F, a->means3D, a->scales, a->rotations, a->opacities, a->shs, a->cov3D_precomp,
-      a->colors_precomp, a->language_feature, vp, a->radii, rec, tiles_touched, clamped, a->prefiltered); count_launch();
+      a->colors_precomp, a->language_feature, vp, a->radii, rec, tiles_touched, clamped, depth_keys, depth_vals,
+      a->prefiltered); count_launch();
   return cudaGetLastError();
 }
 

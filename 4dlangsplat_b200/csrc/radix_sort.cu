@@ -1,4 +1,4 @@
-// radix_sort.cu -- stable LSD "onesweep" radix sort of (u64 key, u32 value) pairs on key bits [0, end_bit).
+// radix_sort.cu -- stable LSD "onesweep" radix sort of (u64 key, u32 value) pairs on key bits [begin_bit, end_bit).
 //
 // Replaces cub::DeviceRadixSort::SortPairs as called at rasterizer_impl.cu:307-312 on the (tile << 32 | depth bits)
 // keys.  Written from the published onesweep scheme (one upfront multi-pass histogram, then ONE kernel per 8-bit
@@ -74,7 +74,7 @@ __device__ __forceinline__ uint32_t rs_block_excl(uint32_t v, uint32_t* s_warp) 
 // Upfront histogram of every pass's digit (reads the keys once).
 __global__ void __launch_bounds__(RS_THREADS)
 rs_histogram_kernel(const uint64_t* __restrict__ keys, long long n_max, const uint32_t* __restrict__ n_dev, int passes,
-                    int end_bit, uint32_t* __restrict__ global_hist) {
+                    int begin_bit, int end_bit, uint32_t* __restrict__ global_hist) {
   __shared__ uint32_t s_hist[RS_MAX_PASSES][RS_BINS];
   const long long n = n_dev ? min((long long)n_dev[0], n_max) : n_max;
   const long long base = (long long)blockIdx.x * RS_TILE;
@@ -90,7 +90,7 @@ rs_histogram_kernel(const uint64_t* __restrict__ keys, long long n_max, const ui
     const unsigned act = __ballot_sync(FULL, valid);
     if (valid) {
       for (int p = 0; p < passes; ++p) {
-        const int shift = p * 8;
+        const int shift = begin_bit + p * 8;
         const uint32_t mask = (1u << min(8, end_bit - shift)) - 1;
         const uint32_t d = (uint32_t)(key >> shift) & mask;
         const unsigned peers = __match_any_sync(act, d);
@@ -257,9 +257,10 @@ size_t sort_scratch_bytes(long long n_max) { return rs_carve(nullptr, n_max < 1 
 
 // returns selector (0: result in a, 1: result in b) or a negative FDLS error
 int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
-               const uint32_t* n_dev, int end_bit, void* scratch, size_t scratch_bytes, cudaStream_t st) {
-  if (end_bit < 1 || end_bit > 64) return FDLS_EINVAL;
-  const int passes = (end_bit + 7) / 8;
+               const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes,
+               cudaStream_t st) {
+  if (begin_bit < 0 || end_bit <= begin_bit || end_bit > 64) return FDLS_EINVAL;
+  const int passes = (end_bit - begin_bit + 7) / 8;
   if (n_max <= 0) return passes & 1;
   RsScratch sc = rs_carve(scratch, n_max, passes);
   if (scratch_bytes < sc.total_bytes) return FDLS_EWORKSPACE;
@@ -272,13 +273,14 @@ int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* v
   }
   if (cudaMemsetAsync(scratch, 0, sc.header_bytes, st) != cudaSuccess) return FDLS_ECUDA;
   const int tiles = cdiv(n_max, RS_TILE);
-  rs_histogram_kernel<<<tiles, RS_THREADS, 0, st>>>(keys_a, n_max, n_dev, passes, end_bit, sc.global_hist); count_launch();
+  rs_histogram_kernel<<<tiles, RS_THREADS, 0, st>>>(keys_a, n_max, n_dev, passes, begin_bit, end_bit,
+                                                     sc.global_hist); count_launch();
   uint64_t* kin = keys_a;
   uint64_t* kout = keys_b;
   uint32_t* vin = vals_a;
   uint32_t* vout = vals_b;
   for (int p = 0; p < passes; ++p) {
-    const int shift = p * 8;
+    const int shift = begin_bit + p * 8;
     const int bits = end_bit - shift < 8 ? end_bit - shift : 8;
     rs_onesweep_kernel<<<tiles, RS_THREADS, sizeof(RsSmem), st>>>(
         kin, kout, vin, vout, n_max, n_dev, shift, bits, sc.global_hist + p * RS_BINS,

@@ -83,8 +83,10 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   float* __restrict__ grad_rec) {
   __shared__ float4 s_rec[2][4][RB_THREADS];
   __shared__ uint32_t s_id[2][RB_THREADS];
+  __shared__ uint32_t s_strips[2][RB_THREADS];  // strip_summary().y of each staged Gaussian
 
   const int tid = threadIdx.x, lane = tid & 31;
+  const uint32_t strip_bit = 1u << (tid >> 5);
   const uint32_t tile = blockIdx.x;
   const uint32_t tx = tile % gx, ty = tile / gx;
   const uint2 pix = {tx * TILE + (tid & (TILE - 1)), ty * TILE + (tid >> 4)};
@@ -150,9 +152,15 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     } else {
       rb_cp_async_wait<0>();
     }
+    {
+      const float4 r0 = s_rec[buf][0][tid], r1 = s_rec[buf][1][tid];
+      s_strips[buf][tid] = __float_as_uint(
+          strip_summary(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, (float)(tx * TILE), (float)(ty * TILE)).y);
+    }
     __syncthreads();
     const int cnt = min(RB_THREADS, M - i * RB_THREADS);
     for (int j = 0; j < cnt; j++) {
+      if (!(s_strips[buf][j] & strip_bit)) continue;  // warp-uniform skip, see common.cuh
       const int q = M - 1 - (i * RB_THREADS + j);  // == the reference's `contributor` after its decrement
       const float4 a = s_rec[buf][0][j];           // x, y, conic.x, conic.y
       const float4 b = s_rec[buf][1][j];           // conic.z, opacity, depth, r

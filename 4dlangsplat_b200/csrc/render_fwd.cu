@@ -37,7 +37,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   float* __restrict__ out_color, float* __restrict__ out_lang, float* __restrict__ out_depth) {
   // [buf][slot 0..3][thread]: conflict-free cp.async writes, broadcast reads
   __shared__ float4 s_rec[2][4][RF_THREADS];
-  __shared__ float s_thr[2][RF_THREADS];
+  __shared__ float2 s_aux[2][RF_THREADS];  // strip_summary() of each staged Gaussian
   __shared__ uint32_t s_max;
 
   const int tid = threadIdx.x;
@@ -48,6 +48,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const float2 pixf = {(float)pix.x, (float)pix.y};
   const bool inside = pix.x < (uint32_t)W && pix.y < (uint32_t)H;
   bool done = !inside;
+  const uint32_t strip_bit = 1u << (tid >> 5);
 
   const uint2 range = ranges[tile];
   int toDo = range.y - range.x;
@@ -81,22 +82,23 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     } else {
       cp_async_wait<0>();
     }
-    {  // conservative skip threshold for my own staged record: alpha < 1/255 is certain when power < thr
-      const float op = s_rec[buf][1][tid].y;  // own cp.async data is visible to the issuing thread after wait
-      // op*exp(power) < 1/255  <=>  power < -log(255*op); 0.01 of slack covers expf/logf rounding by orders of magnitude
-      s_thr[buf][tid] = -__logf(255.0f * op) - 0.01f;
+    {  // my own staged record (own cp.async data is visible to the issuing thread after the wait)
+      const float4 r0 = s_rec[buf][0][tid], r1 = s_rec[buf][1][tid];
+      s_aux[buf][tid] = strip_summary(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, (float)(tx * TILE), (float)(ty * TILE));
     }
     __syncthreads();
 
     const int cnt = min(RF_THREADS, toDo);
     for (int j = 0; !done && j < cnt; j++) {
       contributor++;
+      const float2 aux = s_aux[buf][j];
+      if (!(__float_as_uint(aux.y) & strip_bit)) continue;  // warp-uniform: no pixel of this strip can reach 1/255
       const float4 a = s_rec[buf][0][j];  // x, y, conic.x, conic.y
       const float4 b = s_rec[buf][1][j];  // conic.z, opacity, depth, r
       const float2 d = {a.x - pixf.x, a.y - pixf.y};
       const float power = -0.5f * (a.z * d.x * d.x + b.x * d.y * d.y) - a.w * d.x * d.y;
       if (power > 0.0f) continue;
-      if (power < s_thr[buf][j]) continue;  // certainly alpha < 1/255 (pre-test; exact test below)
+      if (power < aux.x) continue;  // certainly alpha < 1/255 (pre-test; exact test below)
       const float alpha = min(0.99f, b.y * exp(power));
       if (alpha < 1.0f / 255.0f) continue;
       const float test_T = T * (1 - alpha);

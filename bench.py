@@ -27,7 +27,7 @@ for _p in (ROOT, os.path.join(ROOT, "oracle")):
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
-FRAMES_PER_STEP = 10
+FRAMES_PER_STEP = int(os.environ.get('FDLS_BENCH_FRAMES_PER_STEP', '100'))  # one step = the config's 100-timestamp sweep
 N_TIMESTAMPS = 100
 N_PARAM_SETS = 3  # static per-Gaussian parameters are cycled over 3 copies (3 x 71 MB > 126 MB L2)
 

@@ -54,10 +54,12 @@ typedef struct FdlsLayout {
   /* geom */
   size_t rec;           /* float[16] per Gaussian: x,y, conic a,b,c, opacity, depth, r,g,b, lang[6] */
   size_t tiles_touched; /* u32[P] */
-  size_t point_offsets; /* u32[P] inclusive scan of tiles_touched */
+  size_t point_offsets; /* u32[P] inclusive scan of tiles_touched taken in DEPTH order (see depth_order) */
   size_t clamped;       /* u8[P]: bit c set if colour channel c was clamped (forward.cu:66-69) */
   size_t num_rendered;  /* u32[4]: [0]=R (device copy), [1]=overflow flag, [2..3] reserved */
   size_t scan_scratch;
+  size_t depth_order;   /* u32[P]: Gaussian indices sorted (stably) by depth bits; culled ones last */
+  size_t depth_scratch; /* scratch of that P-element sort */
   /* img */
   size_t final_T;   /* f32[H*W]  (reference "accum_alpha") */
   size_t n_contrib; /* u32[H*W] */
@@ -181,14 +183,15 @@ int fdls_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, 
 size_t fdls_knn_workspace_bytes(int32_t N);
 int fdls_knn_dist2(int32_t N, const float* xyz, float* out_dist2, void* ws, size_t ws_bytes, void* stream);
 
-/* Stable LSD radix sort of (u64 key, u32 value) pairs on key bits [0, end_bit); exported for the parity tests
+/* Stable LSD radix sort of (u64 key, u32 value) pairs on key bits [begin_bit, end_bit); exported for the parity tests
  * (replaces cub::DeviceRadixSort::SortPairs, rasterizer_impl.cu:307-312).  Double-buffered like cub::DoubleBuffer:
  * input in (keys_a, vals_a); returns 0 if the sorted result is in the `a` buffers, 1 if in the `b` buffers
  * (= number of 8-bit passes modulo 2), negative on error.  n_dev may be null (then n = n_max); otherwise the
  * element count is min(*n_dev, n_max), read on the device. */
 size_t fdls_sort_scratch_bytes(int64_t n_max);
 int fdls_sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, int64_t n_max,
-                    const uint32_t* n_dev, int end_bit, void* scratch, size_t scratch_bytes, void* stream);
+                    const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes,
+                    void* stream);
 
 #ifdef __cplusplus
 }

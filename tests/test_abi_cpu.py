@@ -61,7 +61,7 @@ def test_null_and_bad_arguments_are_rejected_without_touching_the_gpu(fdls):
     assert lib.fdls_forward(C.byref(a), None) == -4  # F > FDLS_MAX_LANG_CHANNELS
     b = fdls._lib.FdlsBwdArgs()
     assert lib.fdls_backward(C.byref(b), None) == -1
-    assert lib.fdls_sort_pairs(None, None, None, None, 10, None, 32, None, 0, None) == -1
+    assert lib.fdls_sort_pairs(None, None, None, None, 10, None, 0, 32, None, 0, None) == -1
     assert lib.fdls_knn_dist2(5, None, None, None, 0, None) == -1
 
 
