@@ -20,7 +20,8 @@ size_t scan_scratch_bytes(int P);
 cudaError_t launch_scan(int P, const uint32_t* tiles_touched, const uint32_t* order, uint32_t* offsets,
                         uint32_t* block_sums, uint32_t* num_rendered, long long capacity, cudaStream_t st);
 cudaError_t launch_duplicate(int P, const float4* rec, const uint32_t* order, const uint32_t* offsets, const int* radii,
-                             uint64_t* keys, uint32_t* vals, int gx, int gy, long long capacity, cudaStream_t st);
+                             uint64_t* keys, uint32_t* vals, int gx, int gy, long long capacity, uint32_t* global_hist,
+                             int passes, cudaStream_t st);
 cudaError_t launch_tile_ranges(const uint32_t* num_rendered, long long n_grid, long long capacity, const uint64_t* keys,
                                uint2* ranges, int tiles, cudaStream_t st);
 // radix_sort.cu
@@ -28,6 +29,11 @@ size_t sort_scratch_bytes(long long n_max);
 int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
                const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes,
                cudaStream_t st);
+int sort_prepare(long long n_max, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, cudaStream_t st);
+uint32_t* sort_hist(void* scratch);
+int sort_run(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
+             const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, bool have_hist,
+             cudaStream_t st);
 // render_fwd.cu / render_bwd.cu / preprocess_bwd.cu
 cudaError_t launch_render_fwd(int F, const uint2* ranges, const uint32_t* point_list, const float4* rec, int W, int H,
                               int gx, int gy, const float* bg, float* final_T, uint32_t* n_contrib, uint32_t* tile_max,
@@ -220,13 +226,16 @@ FDLS_API int fdls_bin_and_render(const FdlsFwdArgs* a, void* stream) {
     uint64_t* k_out = (uint64_t*)(b + ((passes & 1) ? L.keys : L.keys_alt));
     uint32_t* v_in = (uint32_t*)(b + ((passes & 1) ? L.vals_alt : L.vals));
     uint32_t* v_out = (uint32_t*)(b + ((passes & 1) ? L.vals : L.vals_alt));
+    void* sscr = b + L.sort_scratch;
+    const size_t sscr_bytes = S.binning_bytes - L.sort_scratch;
+    rc = sort_prepare(n_grid, 32, end_bit, sscr, sscr_bytes, st);
+    if (rc < 0) return rc;
     if (launch_duplicate(a->P, (const float4*)(g + L.rec), (const uint32_t*)(g + L.depth_order),
-                         (const uint32_t*)(g + L.point_offsets), a->radii, k_in, v_in, gx, gy, a->capacity,
-                         st) != cudaSuccess)
+                         (const uint32_t*)(g + L.point_offsets), a->radii, k_in, v_in, gx, gy,
+                         n_grid < a->capacity ? n_grid : a->capacity, sort_hist(sscr), passes, st) != cudaSuccess)
       return FDLS_ECUDA;
     rec(a->stage_events, 3, st);
-    rc = sort_pairs(k_in, k_out, v_in, v_out, n_grid, nr, 32, end_bit, b + L.sort_scratch,
-                    S.binning_bytes - L.sort_scratch, st);
+    rc = sort_run(k_in, k_out, v_in, v_out, n_grid, nr, 32, end_bit, sscr, sscr_bytes, true, st);
     if (rc < 0) return rc;
     rec(a->stage_events, 4, st);
     point_list = (const uint32_t*)(b + L.vals);

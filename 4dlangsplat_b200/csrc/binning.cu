@@ -128,13 +128,34 @@ scan_apply_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __rest
 
 // rasterizer_impl.cu:70-111, warp-cooperative.  Thread `pos` handles the pos-th Gaussian in DEPTH order
 // (order[pos]); within a Gaussian the tiles are emitted y-major, x-minor like the reference.  Because instances
-// leave this kernel already depth-sorted, the following stable sort only has to look at the tile bits.
+// leave this kernel already depth-sorted, the following stable sort only has to look at the tile bits -- and since the
+// tile ids are produced right here, the kernel also accumulates the sort's per-pass digit histograms (shared-memory
+// counters, warp-aggregated with match.any), which removes the sort's own histogram pass over the keys.
+constexpr int DUP_MAX_PASSES = 3;  // tile ids up to 24 bits
+
+__device__ __forceinline__ void dup_count(uint32_t (*s_hist)[256], int passes, bool valid, uint32_t tile, uint32_t lt) {
+#pragma unroll
+  for (int p = 0; p < DUP_MAX_PASSES; ++p) {
+    if (p < passes) {
+      const uint32_t d = valid ? ((tile >> (8 * p)) & 255u) : 0xffffffffu;
+      const unsigned peers = __match_any_sync(0xffffffffu, d);
+      if (valid && (peers & lt) == 0) atomicAdd(&s_hist[p][d], __popc(peers));
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256)
 duplicate_keys_kernel(int P, const float4* __restrict__ rec, const uint32_t* __restrict__ order,
                       const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
-                      uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, int gx, int gy, long long capacity) {
+                      uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, int gx, int gy, long long capacity,
+                      uint32_t* __restrict__ global_hist, int passes) {
+  __shared__ uint32_t s_hist[DUP_MAX_PASSES][256];
+  for (int i = threadIdx.x; i < DUP_MAX_PASSES * 256; i += blockDim.x) (&s_hist[0][0])[i] = 0;
+  __syncthreads();
   const int pos = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
+  uint32_t lt;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(lt));
   const int idx = pos < P ? (int)order[pos] : 0;
   int radius = pos < P ? radii[idx] : 0;
   uint32_t off = 0, depth_bits = 0, count = 0;
@@ -147,16 +168,26 @@ duplicate_keys_kernel(int P, const float4* __restrict__ rec, const uint32_t* __r
     count = (rmax.x - rmin.x) * (rmax.y - rmin.y);
   }
   constexpr uint32_t SMALL = 4;
-  if (count > 0 && count <= SMALL) {
-    uint32_t o = off;
-    for (uint32_t y = rmin.y; y < rmax.y; y++)
-      for (uint32_t x = rmin.x; x < rmax.x; x++) {
+  {  // Gaussians touching <= SMALL tiles: each lane emits its own (uniform trip count keeps the warp converged)
+    const bool mine = count > 0 && count <= SMALL;
+    const uint32_t w = rmax.x - rmin.x;
+#pragma unroll
+    for (uint32_t k = 0; k < SMALL; ++k) {
+      const bool valid = mine && k < count;
+      uint32_t tile = 0;
+      if (valid) {
+        const uint32_t y = rmin.y + k / w, x = rmin.x + k % w;
+        tile = y * gx + x;
+        const uint32_t o = off + k;
         if ((long long)o < capacity) {
-          keys[o] = ((uint64_t)(y * gx + x) << 32) | depth_bits;
+          keys[o] = ((uint64_t)tile << 32) | depth_bits;
           vals[o] = idx;
+        } else {
+          tile = 0xffffffffu;
         }
-        o++;
       }
+      dup_count(s_hist, passes, valid && tile != 0xffffffffu, tile, lt);
+    }
   }
   uint32_t big = __ballot_sync(0xffffffffu, count > SMALL);
   while (big) {
@@ -169,14 +200,28 @@ duplicate_keys_kernel(int P, const float4* __restrict__ rec, const uint32_t* __r
     const uint32_t b_w = __shfl_sync(0xffffffffu, rmax.x - rmin.x, src);
     const uint32_t b_depth = __shfl_sync(0xffffffffu, depth_bits, src);
     const uint32_t b_idx = __shfl_sync(0xffffffffu, (uint32_t)idx, src);
-    for (uint32_t i = lane; i < b_cnt; i += 32) {
-      const uint32_t y = b_y0 + i / b_w, x = b_x0 + i % b_w;
-      const uint32_t o = b_off + i;
-      if ((long long)o < capacity) {
-        keys[o] = ((uint64_t)(y * gx + x) << 32) | b_depth;
-        vals[o] = b_idx;
+    for (uint32_t base = 0; base < b_cnt; base += 32) {
+      const uint32_t i = base + lane;
+      bool valid = i < b_cnt;
+      uint32_t tile = 0;
+      if (valid) {
+        const uint32_t y = b_y0 + i / b_w, x = b_x0 + i % b_w;
+        tile = y * gx + x;
+        const uint32_t o = b_off + i;
+        if ((long long)o < capacity) {
+          keys[o] = ((uint64_t)tile << 32) | b_depth;
+          vals[o] = b_idx;
+        } else {
+          valid = false;
+        }
       }
+      dup_count(s_hist, passes, valid, tile, lt);
     }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < passes * 256; i += blockDim.x) {
+    const uint32_t c = (&s_hist[0][0])[i];
+    if (c) atomicAdd(&global_hist[i], c);
   }
 }
 
@@ -213,9 +258,11 @@ cudaError_t launch_scan(int P, const uint32_t* tiles_touched, const uint32_t* or
 
 cudaError_t launch_duplicate(int P, const float4* rec, const uint32_t* order, const uint32_t* offsets,
                              const int* radii, uint64_t* keys, uint32_t* vals, int gx, int gy, long long capacity,
-                             cudaStream_t st) {
+                             uint32_t* global_hist, int passes, cudaStream_t st) {
   if (P == 0) return cudaSuccess;
-  duplicate_keys_kernel<<<cdiv(P, 256), 256, 0, st>>>(P, rec, order, offsets, radii, keys, vals, gx, gy, capacity); count_launch();
+  if (passes > DUP_MAX_PASSES) return cudaErrorInvalidValue;
+  duplicate_keys_kernel<<<cdiv(P, 256), 256, 0, st>>>(P, rec, order, offsets, radii, keys, vals, gx, gy, capacity,
+                                                      global_hist, passes); count_launch();
   return cudaGetLastError();
 }
 

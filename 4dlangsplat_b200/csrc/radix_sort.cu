@@ -2,29 +2,35 @@
 //
 // Replaces cub::DeviceRadixSort::SortPairs as called at rasterizer_impl.cu:307-312 on the (tile << 32 | depth bits)
 // keys.  Written from the published onesweep scheme (one upfront multi-pass histogram, then ONE kernel per 8-bit
-// digit that ranks a 4096-key tile in shared memory and resolves its global offsets by decoupled look-back over the
+// digit that ranks a tile of keys in shared memory and resolves its global offsets by decoupled look-back over the
 // per-tile digit counts of the preceding tiles), sized for B200:
-//   * 256 threads x 16 keys per CTA, ~57 KB dynamic shared memory -> 3 CTAs/SM, grid >> 148 SMs;
+//   * 256 threads x IPT keys per CTA; IPT is chosen from the problem size so that even the 300k-element depth sort
+//     fills the 148 SMs (IPT=4 -> 1024-key tiles) while the multi-million-instance sort amortises its per-CTA scan
+//     and look-back (IPT=8);
+//   * one shared exchange buffer is used twice (keys, then values) and values are loaded only after ranking, which
+//     keeps the CTA at <= 64 registers/thread and ~25 KB of shared memory -> 4-5 CTAs per SM;
 //   * the element count is read from DEVICE memory (no host sync on num_rendered); CTAs past the end exit;
 //   * tiles are handed out by an atomic ticket so a CTA only ever waits on CTAs that already started;
-//   * keys are exchanged through shared memory so the scatter writes runs of equal digits contiguously.
+//   * a caller that generates the keys itself (duplicate_keys_kernel) can accumulate the digit histograms on the fly
+//     and skip the histogram pass (sort_prepare / sort_hist / sort_run).
 // Stability: items are ranked in (warp, item, lane) order == global index order; equal digits keep that order.
 #include "common.cuh"
 
 namespace fdls {
 
 constexpr int RS_THREADS = 256;
-constexpr int RS_IPT = 16;
-constexpr int RS_TILE = RS_THREADS * RS_IPT;  // 4096
 constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr int RS_BINS = 256;
 constexpr int RS_MAX_PASSES = 8;
 constexpr uint32_t FLAG_AGG = 1u << 30, FLAG_PREFIX = 2u << 30, FLAG_MASK = 3u << 30, VAL_MASK = ~FLAG_MASK;
 constexpr unsigned FULL = 0xffffffffu;
 
+template <int IPT>
 struct RsSmem {
-  uint64_t keys[RS_TILE];
-  uint32_t vals[RS_TILE];
+  union {
+    uint64_t keys[RS_THREADS * IPT];
+    uint32_t vals[RS_THREADS * IPT];
+  } x;
   uint32_t warp_hist[RS_WARPS][RS_BINS + 8];
   uint32_t digit_start[RS_BINS];
   uint32_t global_base[RS_BINS];
@@ -75,15 +81,16 @@ __device__ __forceinline__ uint32_t rs_block_excl(uint32_t v, uint32_t* s_warp) 
 __global__ void __launch_bounds__(RS_THREADS)
 rs_histogram_kernel(const uint64_t* __restrict__ keys, long long n_max, const uint32_t* __restrict__ n_dev, int passes,
                     int begin_bit, int end_bit, uint32_t* __restrict__ global_hist) {
+  constexpr int HT = RS_THREADS * 8;
   __shared__ uint32_t s_hist[RS_MAX_PASSES][RS_BINS];
   const long long n = n_dev ? min((long long)n_dev[0], n_max) : n_max;
-  const long long base = (long long)blockIdx.x * RS_TILE;
+  const long long base = (long long)blockIdx.x * HT;
   if (base >= n) return;
   for (int i = threadIdx.x; i < passes * RS_BINS; i += RS_THREADS) (&s_hist[0][0])[i] = 0;
   __syncthreads();
   const uint32_t lt = lanemask_lt();
 #pragma unroll 4
-  for (int i = 0; i < RS_IPT; ++i) {
+  for (int i = 0; i < 8; ++i) {
     const long long k = base + i * RS_THREADS + threadIdx.x;
     const bool valid = k < n;
     const uint64_t key = valid ? keys[k] : 0;
@@ -105,56 +112,54 @@ rs_histogram_kernel(const uint64_t* __restrict__ keys, long long n_max, const ui
   }
 }
 
+template <int IPT>
 __global__ void __launch_bounds__(RS_THREADS)
 rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_out,
                    const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out, long long n_max,
                    const uint32_t* __restrict__ n_dev, int shift, int bits, const uint32_t* __restrict__ global_hist,
                    uint32_t* __restrict__ tile_state, uint32_t* __restrict__ ticket, uint32_t* __restrict__ error_flag) {
+  constexpr int TILE_KEYS = RS_THREADS * IPT;
   extern __shared__ __align__(16) unsigned char rs_smem_raw[];
-  RsSmem& s = *reinterpret_cast<RsSmem*>(rs_smem_raw);
+  RsSmem<IPT>& s = *reinterpret_cast<RsSmem<IPT>*>(rs_smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s.tile = atomicAdd(ticket, 1u);
   for (int i = tid; i < RS_WARPS * (RS_BINS + 8); i += RS_THREADS) (&s.warp_hist[0][0])[i] = 0;
   __syncthreads();
   const uint32_t tile = s.tile;
   const long long n = n_dev ? min((long long)n_dev[0], n_max) : n_max;
-  const long long tile_base = (long long)tile * RS_TILE;
+  const long long tile_base = (long long)tile * TILE_KEYS;
   if (tile_base >= n) return;
-  const int valid_count = (int)min((long long)RS_TILE, n - tile_base);
+  const int valid_count = (int)min((long long)TILE_KEYS, n - tile_base);
   const uint32_t mask = (1u << bits) - 1;
 
-  // ---- load (warp-striped) and rank
-  uint64_t key[RS_IPT];
-  uint32_t val[RS_IPT];
-  uint32_t rank[RS_IPT];
-  const int warp_base = warp * 32 * RS_IPT;
+  // ---- load keys (warp-striped) and compute every item's peer set up front (independent match.any's)
+  uint64_t key[IPT];
+  unsigned peers[IPT];
+  uint16_t rank[IPT];
+  const int warp_base = warp * 32 * IPT;
 #pragma unroll
-  for (int i = 0; i < RS_IPT; ++i) {
+  for (int i = 0; i < IPT; ++i) {
     const int li = warp_base + i * 32 + lane;
-    if (li < valid_count) {
-      key[i] = keys_in[tile_base + li];
-      val[i] = vals_in[tile_base + li];
-    } else {
-      key[i] = ~0ull;
-      val[i] = 0;
-    }
+    key[i] = (li < valid_count) ? keys_in[tile_base + li] : ~0ull;
   }
+#pragma unroll
+  for (int i = 0; i < IPT; ++i) {
+    const int li = warp_base + i * 32 + lane;
+    const uint32_t d = (li < valid_count) ? ((uint32_t)(key[i] >> shift) & mask) : RS_BINS;  // bin 256 = padding
+    peers[i] = __match_any_sync(FULL, d);
+  }
+  // ---- rank inside the warp: running per-digit counters live in this warp's private shared histogram
   const uint32_t lt = lanemask_lt();
   uint32_t* wh = s.warp_hist[warp];
 #pragma unroll
-  for (int i = 0; i < RS_IPT; ++i) {
+  for (int i = 0; i < IPT; ++i) {
     const int li = warp_base + i * 32 + lane;
-    const uint32_t d = (li < valid_count) ? ((uint32_t)(key[i] >> shift) & mask) : RS_BINS;  // bin 256 = padding
-    const unsigned peers = __match_any_sync(FULL, d);
-    const int leader = __ffs(peers) - 1;
-    uint32_t old = 0;
-    if (lane == leader) {
-      old = wh[d];
-      wh[d] = old + __popc(peers);
-    }
-    old = __shfl_sync(FULL, old, leader);
-    rank[i] = old + __popc(peers & lt);
+    const uint32_t d = (li < valid_count) ? ((uint32_t)(key[i] >> shift) & mask) : RS_BINS;
+    const uint32_t old = wh[d];  // every lane of a peer group reads the same counter (broadcast) ...
     __syncwarp();
+    if ((peers[i] & lt) == 0) wh[d] = old + __popc(peers[i]);  // ... then its leader bumps it
+    __syncwarp();
+    rank[i] = (uint16_t)(old + __popc(peers[i] & lt));
   }
   __syncthreads();
 
@@ -169,11 +174,7 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ 
   }
   // ---- publish the CTA's digit count, then look back for the exclusive prefix over preceding tiles
   uint32_t* my_state = tile_state + (size_t)tile * RS_BINS + d;
-  if (tile == 0) {
-    st_relaxed(my_state, FLAG_PREFIX | count);
-  } else {
-    st_relaxed(my_state, FLAG_AGG | count);
-  }
+  st_relaxed(my_state, (tile == 0 ? FLAG_PREFIX : FLAG_AGG) | count);
   uint32_t excl = 0;
   if (tile > 0) {
     long long t = (long long)tile - 1;
@@ -202,39 +203,59 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ 
   s.global_base[d] = ghist_excl + excl - local_start;
   __syncthreads();
 
-  // ---- exchange through shared memory so equal digits become contiguous
+  // ---- keys: exchange through shared memory so equal digits become contiguous, then scatter
+  uint16_t pos[IPT];
+  uint32_t val[IPT];
 #pragma unroll
-  for (int i = 0; i < RS_IPT; ++i) {
+  for (int i = 0; i < IPT; ++i) {
     const int li = warp_base + i * 32 + lane;
+    pos[i] = 0;
+    val[i] = 0;
     if (li < valid_count) {
       const uint32_t dg = (uint32_t)(key[i] >> shift) & mask;
-      const uint32_t pos = s.digit_start[dg] + wh[dg] + rank[i];
-      s.keys[pos] = key[i];
-      s.vals[pos] = val[i];
+      pos[i] = (uint16_t)(s.digit_start[dg] + wh[dg] + rank[i]);
+      s.x.keys[pos[i]] = key[i];
+      val[i] = vals_in[tile_base + li];  // in flight while the keys are scattered
     }
   }
   __syncthreads();
+  uint32_t dst[IPT];
 #pragma unroll
-  for (int i = 0; i < RS_IPT; ++i) {
+  for (int i = 0; i < IPT; ++i) {
     const int p = i * RS_THREADS + tid;
+    dst[i] = 0;
     if (p < valid_count) {
-      const uint64_t k = s.keys[p];
+      const uint64_t k = s.x.keys[p];
       const uint32_t dg = (uint32_t)(k >> shift) & mask;
-      const uint32_t dst = s.global_base[dg] + p;
-      keys_out[dst] = k;
-      vals_out[dst] = s.vals[p];
+      dst[i] = s.global_base[dg] + p;
+      keys_out[dst[i]] = k;
     }
+  }
+  __syncthreads();
+  // ---- values: same exchange buffer, same positions
+#pragma unroll
+  for (int i = 0; i < IPT; ++i) {
+    const int li = warp_base + i * 32 + lane;
+    if (li < valid_count) s.x.vals[pos[i]] = val[i];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < IPT; ++i) {
+    const int p = i * RS_THREADS + tid;
+    if (p < valid_count) vals_out[dst[i]] = s.x.vals[p];
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
 struct RsScratch {
   uint32_t* global_hist;  // [RS_MAX_PASSES][256]
   uint32_t* tickets;      // [RS_MAX_PASSES]
   uint32_t* error_flag;   // [1]
   uint32_t* tile_state;   // [passes][tiles][256]
-  size_t header_bytes;    // bytes to zero before each sort = everything
   size_t total_bytes;
 };
+
+static int rs_ipt(long long n_max) { return n_max <= (1 << 20) ? 4 : 8; }
 
 static RsScratch rs_carve(void* scratch, long long n_max, int passes) {
   RsScratch r;
@@ -246,50 +267,81 @@ static RsScratch rs_carve(void* scratch, long long n_max, int passes) {
   r.error_flag = (uint32_t*)p;
   p += 16 * sizeof(uint32_t);
   r.tile_state = (uint32_t*)p;
-  const size_t tiles = (size_t)cdiv(n_max, RS_TILE);
+  const size_t tiles = (size_t)cdiv(n_max, RS_THREADS * rs_ipt(n_max));
   p += (size_t)passes * tiles * RS_BINS * sizeof(uint32_t);
   r.total_bytes = align_up((size_t)(p - (char*)scratch));
-  r.header_bytes = r.total_bytes;
   return r;
 }
 
 size_t sort_scratch_bytes(long long n_max) { return rs_carve(nullptr, n_max < 1 ? 1 : n_max, RS_MAX_PASSES).total_bytes; }
 
-// returns selector (0: result in a, 1: result in b) or a negative FDLS error
-int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
-               const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes,
-               cudaStream_t st) {
+// Zero the scratch (histograms, tickets, tile states).  Must precede sort_run and any external histogram accumulation.
+int sort_prepare(long long n_max, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+  if (begin_bit < 0 || end_bit <= begin_bit || end_bit > 64) return FDLS_EINVAL;
+  if (n_max <= 0) return FDLS_OK;
+  const int passes = (end_bit - begin_bit + 7) / 8;
+  RsScratch sc = rs_carve(scratch, n_max, passes);
+  if (scratch_bytes < sc.total_bytes) return FDLS_EWORKSPACE;
+  return cudaMemsetAsync(scratch, 0, sc.total_bytes, st) == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
+}
+
+// [pass][256] digit counters inside the scratch (for callers that build the histogram while generating the keys)
+uint32_t* sort_hist(void* scratch) { return (uint32_t*)scratch; }
+
+template <int IPT>
+static int rs_launch_passes(uint64_t* kin, uint64_t* kout, uint32_t* vin, uint32_t* vout, long long n_max,
+                            const uint32_t* n_dev, int begin_bit, int end_bit, int passes, RsScratch& sc,
+                            cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(rs_onesweep_kernel<IPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)sizeof(RsSmem<IPT>)) != cudaSuccess)
+      return FDLS_ECUDA;
+    attr_set = true;
+  }
+  const int tiles = cdiv(n_max, RS_THREADS * IPT);
+  for (int p = 0; p < passes; ++p) {
+    const int shift = begin_bit + p * 8;
+    const int bits = end_bit - shift < 8 ? end_bit - shift : 8;
+    rs_onesweep_kernel<IPT><<<tiles, RS_THREADS, sizeof(RsSmem<IPT>), st>>>(
+        kin, kout, vin, vout, n_max, n_dev, shift, bits, sc.global_hist + p * RS_BINS,
+        sc.tile_state + (size_t)p * tiles * RS_BINS, sc.tickets + p, sc.error_flag);
+    count_launch();
+    uint64_t* tk = kin; kin = kout; kout = tk;
+    uint32_t* tv = vin; vin = vout; vout = tv;
+  }
+  return FDLS_OK;
+}
+
+// returns selector (0: result in a, 1: result in b) or a negative FDLS error.  have_hist: the caller already
+// accumulated the per-pass digit histograms into sort_hist(scratch) after sort_prepare().
+int sort_run(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
+             const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, bool have_hist,
+             cudaStream_t st) {
   if (begin_bit < 0 || end_bit <= begin_bit || end_bit > 64) return FDLS_EINVAL;
   const int passes = (end_bit - begin_bit + 7) / 8;
   if (n_max <= 0) return passes & 1;
   RsScratch sc = rs_carve(scratch, n_max, passes);
   if (scratch_bytes < sc.total_bytes) return FDLS_EWORKSPACE;
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(rs_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem)) !=
-        cudaSuccess)
-      return FDLS_ECUDA;
-    attr_set = true;
+  if (!have_hist) {
+    rs_histogram_kernel<<<cdiv(n_max, RS_THREADS * 8), RS_THREADS, 0, st>>>(keys_a, n_max, n_dev, passes, begin_bit,
+                                                                           end_bit, sc.global_hist);
+    count_launch();
   }
-  if (cudaMemsetAsync(scratch, 0, sc.header_bytes, st) != cudaSuccess) return FDLS_ECUDA;
-  const int tiles = cdiv(n_max, RS_TILE);
-  rs_histogram_kernel<<<tiles, RS_THREADS, 0, st>>>(keys_a, n_max, n_dev, passes, begin_bit, end_bit,
-                                                     sc.global_hist); count_launch();
-  uint64_t* kin = keys_a;
-  uint64_t* kout = keys_b;
-  uint32_t* vin = vals_a;
-  uint32_t* vout = vals_b;
-  for (int p = 0; p < passes; ++p) {
-    const int shift = begin_bit + p * 8;
-    const int bits = end_bit - shift < 8 ? end_bit - shift : 8;
-    rs_onesweep_kernel<<<tiles, RS_THREADS, sizeof(RsSmem), st>>>(
-        kin, kout, vin, vout, n_max, n_dev, shift, bits, sc.global_hist + p * RS_BINS,
-        sc.tile_state + (size_t)p * tiles * RS_BINS, sc.tickets + p, sc.error_flag); count_launch();
-    uint64_t* tk = kin; kin = kout; kout = tk;
-    uint32_t* tv = vin; vin = vout; vout = tv;
-  }
+  int rc = rs_ipt(n_max) == 4
+               ? rs_launch_passes<4>(keys_a, keys_b, vals_a, vals_b, n_max, n_dev, begin_bit, end_bit, passes, sc, st)
+               : rs_launch_passes<8>(keys_a, keys_b, vals_a, vals_b, n_max, n_dev, begin_bit, end_bit, passes, sc, st);
+  if (rc < 0) return rc;
   if (cudaGetLastError() != cudaSuccess) return FDLS_ECUDA;
   return passes & 1;
+}
+
+int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
+               const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes,
+               cudaStream_t st) {
+  int rc = sort_prepare(n_max, begin_bit, end_bit, scratch, scratch_bytes, st);
+  if (rc < 0) return rc;
+  return sort_run(keys_a, keys_b, vals_a, vals_b, n_max, n_dev, begin_bit, end_bit, scratch, scratch_bytes, false, st);
 }
 
 }  // namespace fdls

@@ -183,7 +183,7 @@ def test_sort_pairs_stable(fdls, n, end_bit):
     ka, kb, va, vb = keys.clone(), torch.empty_like(keys), vals.clone(), torch.empty_like(vals)
     sb = lib.fdls_sort_scratch_bytes(n)
     scratch = torch.empty(sb, dtype=torch.uint8, device="cuda")
-    sel = lib.fdls_sort_pairs(ka.data_ptr(), kb.data_ptr(), va.data_ptr(), vb.data_ptr(), n, None, end_bit,
+    sel = lib.fdls_sort_pairs(ka.data_ptr(), kb.data_ptr(), va.data_ptr(), vb.data_ptr(), n, None, 0, end_bit,
                               scratch.data_ptr(), sb, C.c_void_p(torch.cuda.current_stream().cuda_stream))
     torch.cuda.synchronize()
     assert sel in (0, 1)
@@ -206,7 +206,7 @@ def test_sort_pairs_device_count(fdls):
     n_dev = torch.tensor([n], dtype=torch.int32, device="cuda")
     sb = lib.fdls_sort_scratch_bytes(n_max)
     scratch = torch.empty(sb, dtype=torch.uint8, device="cuda")
-    sel = lib.fdls_sort_pairs(ka.data_ptr(), kb.data_ptr(), va.data_ptr(), vb.data_ptr(), n_max, n_dev.data_ptr(), 40,
+    sel = lib.fdls_sort_pairs(ka.data_ptr(), kb.data_ptr(), va.data_ptr(), vb.data_ptr(), n_max, n_dev.data_ptr(), 0, 40,
                               scratch.data_ptr(), sb, C.c_void_p(torch.cuda.current_stream().cuda_stream))
     torch.cuda.synchronize()
     ko, vo = (kb, vb) if sel else (ka, va)
@@ -224,3 +224,54 @@ def test_knn_dist2(fdls, n):
     d, _ = cKDTree(pts.astype(np.float64)).query(pts.astype(np.float64), k=4)
     want = (d[:, 1:4] ** 2).mean(1)
     np.testing.assert_allclose(got, want, rtol=1e-4, atol=1e-12)
+
+
+@pytest.mark.parametrize("name", ["tiny", "small"])
+def test_backward_accuracy_vs_float64(synth, name):
+    """Who is right when this build and the reference disagree in the 4th digit?  Recompute the backward in float64
+    (CPU oracle) on the REFERENCE's own forward state and check that this build's gradients are as close to it as the
+    reference's are (the reference sums with float atomics in arbitrary order, this build with warp-tree sums)."""
+    import oracle as orc
+    from types import SimpleNamespace
+    _need_ref(3)
+    s = synth.scene(name)
+    dcol, dlang, ddepth = synth.upstream_grads(s, depth=True)
+    ref = refcuda.Ref(3)
+    r = ref.forward(s)
+    gr = ref.backward(dcol, dlang, ddepth)
+    o = helpers.run_forward(s)
+    g = helpers.run_backward(s, o, dcol, dlang, ddepth)
+    f64 = lambda t: np.ascontiguousarray(t.detach().cpu().numpy().astype(np.float64))
+    a64 = lambda a: np.ascontiguousarray(np.asarray(a, np.float64))
+    st = SimpleNamespace(P=s.P, W=s.W, H=s.H, F=s.F, M=s.shs.shape[1], D=s.sh_degree, dtype=np.float64,
+                         include_feature=True)
+    st.inputs = SimpleNamespace(means3D=a64(s.means3D), opacities=a64(s.opacities).reshape(-1), view=a64(s.viewmatrix).reshape(-1),
+                                proj=a64(s.projmatrix).reshape(-1), campos=a64(s.campos).reshape(-1), bg=a64(s.bg),
+                                shs=a64(s.shs), colors_precomp=None, language_feature=a64(s.language_feature),
+                                scales=a64(s.scales), rotations=a64(s.rotations), cov3D_precomp=None,
+                                tanfovx=s.tanfovx, tanfovy=s.tanfovy, scale_modifier=s.scale_modifier)
+    vis = (r.radii > 0).cpu().numpy()
+    clean = lambda t: np.where(vis.reshape(-1, *([1] * (t.ndim - 1))), f64(t), 0.0)
+    st.radii = r.radii.cpu().numpy().astype(np.int32)
+    st.means2D, st.depths, st.cov3D = clean(r.means2D), clean(r.depths), clean(r.cov3D)
+    st.conic_opacity, st.feat = clean(r.conic_opacity), clean(r.rgb)
+    st.clamped = np.ascontiguousarray((r.clamped != 0).cpu().numpy().astype(np.uint8) * vis[:, None])
+    st.ranges = np.ascontiguousarray(r.ranges.cpu().numpy().astype(np.uint32))
+    st.point_list = np.ascontiguousarray(r.point_list.cpu().numpy().astype(np.uint32))
+    st.final_T, st.n_contrib = f64(r.final_T), np.ascontiguousarray(r.n_contrib.cpu().numpy().astype(np.uint32))
+    truth = orc.backward(st, a64(dcol), a64(dlang), a64(ddepth))
+    report = []
+    for nm, mine, theirs, tr in (("means2D", g.means2D, gr.means2D, truth.means2D), ("colors", g.colors, gr.colors, truth.colors),
+                                 ("lang", g.lang, gr.lang, truth.language_feature), ("opacity", g.opacity, gr.opacity, truth.opacities),
+                                 ("means3D", g.means3D, gr.means3D, truth.means3D), ("cov3D", g.cov3D, gr.cov3D, truth.cov3D),
+                                 ("sh", g.sh, gr.sh, truth.sh), ("scales", g.scales, gr.scales, truth.scales),
+                                 ("rots", g.rots, gr.rots, truth.rotations)):
+        tr = np.asarray(tr, np.float64).reshape(-1)
+        e_mine = np.abs(f64(mine).reshape(-1) - tr)
+        e_ref = np.abs(f64(theirs).reshape(-1) - tr)
+        gmax = np.abs(tr).max()
+        report.append("%s: max err mine %.3g / ref %.3g, mean err mine %.3g / ref %.3g (max |truth| %.3g)" % (
+            nm, e_mine.max(), e_ref.max(), e_mine.mean(), e_ref.mean(), gmax))
+        assert e_mine.max() <= 2.0 * e_ref.max() + 2e-6 * gmax, report[-1]
+        assert e_mine.mean() <= 2.0 * e_ref.mean() + 1e-7 * gmax, report[-1]
+    print("\n".join(report))
