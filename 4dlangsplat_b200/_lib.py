@@ -25,7 +25,7 @@ class FdlsLayout(C.Structure):
     _fields_ = [(n, C.c_size_t) for n in (
         "rec", "tiles_touched", "point_offsets", "clamped", "num_rendered", "scan_scratch",
         "depth_order", "depth_scratch",
-        "final_T", "n_contrib", "ranges", "tile_max_contrib",
+        "final_T", "n_contrib", "ranges", "tile_max_contrib", "tile_start", "tile_cursor",
         "keys_alt", "keys", "vals_alt", "vals", "sort_scratch")]
 
 
@@ -45,6 +45,7 @@ class FdlsFwdArgs(C.Structure):
         ("num_rendered_host", C.c_void_p),
         ("num_rendered_hint", C.c_int64),
         ("stage_events", C.POINTER(C.c_void_p)),
+        ("binning_algo", C.c_int32),
     ]
 
 

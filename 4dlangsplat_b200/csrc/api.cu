@@ -34,6 +34,15 @@ uint32_t* sort_hist(void* scratch);
 int sort_run(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
              const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, bool have_hist,
              cudaStream_t st);
+// binning_bucket.cu
+cudaError_t launch_tile_count(int P, const float4* rec, const int* radii, int gx, int gy, uint32_t* counters,
+                              cudaStream_t st);
+cudaError_t launch_tile_scan(int T, uint32_t* counters, uint32_t* tile_start, uint2* ranges, uint32_t* num_rendered,
+                             long long capacity, cudaStream_t st);
+cudaError_t launch_tile_scatter_sort(int P, const float4* rec, const int* radii, int gx, int gy, uint32_t* counters,
+                                     const uint32_t* tile_start, const uint32_t* num_rendered, long long capacity,
+                                     uint64_t* seg, uint64_t* keys_out, uint32_t* point_list, void** events,
+                                     cudaStream_t st);
 // render_fwd.cu / render_bwd.cu / preprocess_bwd.cu
 cudaError_t launch_render_fwd(int F, const uint2* ranges, const uint32_t* point_list, const float4* rec, int W, int H,
                               int gx, int gy, const float* bg, float* final_T, uint32_t* n_contrib, uint32_t* tile_max,
@@ -80,6 +89,8 @@ static void compute_layout(int P, int W, int H, long long capacity, FdlsLayout* 
   L->n_contrib = o;        o += align_up(HW * 4);
   L->ranges = o;           o += align_up(tiles * 8);
   L->tile_max_contrib = o; o += align_up(tiles * 4);
+  L->tile_start = o;       o += align_up((tiles + 1) * 4);
+  L->tile_cursor = o;      o += align_up(tiles * 4);
   S->img_bytes = o;
   o = 0;
   L->vals = o;         o += align_up(cap * 4);  // first: the backward finds point_list without knowing capacity
@@ -178,10 +189,27 @@ FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
   uint32_t* dv_b = (uint32_t*)(g + L.depth_scratch + 2 * align_up(Pz * 8));
   char* dscr = g + L.depth_scratch + 2 * align_up(Pz * 8) + align_up(Pz * 4);
   uint32_t* order = (uint32_t*)(g + L.depth_order);
+  const bool bucket = a->binning_algo == 0;
   if (launch_preprocess_fwd(a, vp, (float4*)(g + L.rec), (uint32_t*)(g + L.tiles_touched), (uint8_t*)(g + L.clamped),
-                            dk_a, order, st) != cudaSuccess)
+                            bucket ? nullptr : dk_a, order, st) != cudaSuccess)
     return FDLS_ECUDA;
   rec(a->stage_events, 1, st);
+  if (bucket) {
+    // K1 + K2 of binning_bucket.cu: per-tile instance counts -> tile starts (== ranges) and R
+    char* im = (char*)a->img_ws;
+    const int gx = cdiv(a->W, TILE), gy = cdiv(a->H, TILE);
+    if (launch_tile_count(a->P, (const float4*)(g + L.rec), a->radii, gx, gy, (uint32_t*)(im + L.tile_cursor), st) !=
+        cudaSuccess)
+      return FDLS_ECUDA;
+    if (launch_tile_scan(gx * gy, (uint32_t*)(im + L.tile_cursor), (uint32_t*)(im + L.tile_start),
+                         (uint2*)(im + L.ranges), nr, a->capacity, st) != cudaSuccess)
+      return FDLS_ECUDA;
+    rec(a->stage_events, 2, st);
+    if (a->num_rendered_host &&
+        cudaMemcpyAsync(a->num_rendered_host, nr, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st) != cudaSuccess)
+      return FDLS_ECUDA;
+    return FDLS_OK;
+  }
   // (1) order the GAUSSIANS by depth bits (stable, P elements) ...
   int sel = sort_pairs(dk_a, dk_b, order, dv_b, a->P, nullptr, 0, 32, dscr, sort_scratch_bytes((long long)Pz), st);
   if (sel < 0) return sel;
@@ -216,7 +244,18 @@ FDLS_API int fdls_bin_and_render(const FdlsFwdArgs* a, void* stream) {
   if (a->num_rendered_hint >= 0 && a->num_rendered_hint < n_grid) n_grid = a->num_rendered_hint;
   uint2* ranges = (uint2*)(im + L.ranges);
   const uint32_t* point_list = nullptr;
-  if (n_grid > 0) {
+  if (a->binning_algo == 0) {
+    if (n_grid > 0) {
+      // K3 + K4 of binning_bucket.cu (ranges were written by K2 in stage 1)
+      if (launch_tile_scatter_sort(a->P, (const float4*)(g + L.rec), a->radii, gx, gy, (uint32_t*)(im + L.tile_cursor),
+                                   (const uint32_t*)(im + L.tile_start), nr, n_grid < a->capacity ? n_grid : a->capacity,
+                                   (uint64_t*)(b + L.keys_alt), (uint64_t*)(b + L.keys), (uint32_t*)(b + L.vals),
+                                   a->stage_events, st) != cudaSuccess)
+        return FDLS_ECUDA;
+      point_list = (const uint32_t*)(b + L.vals);
+    }
+    rec(a->stage_events, 4, st);
+  } else if (n_grid > 0) {
     // Instances were emitted in depth order, so a STABLE sort on the tile bits alone yields exactly the order of the
     // reference's sort on bits [0, 32+bit) (rasterizer_impl.cu:304-312): 2 passes over R instead of 6.
     const int end_bit = 32 + (int)higher_msb((uint32_t)(gx * gy));

@@ -170,8 +170,10 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
   } while (0);
   radii[idx] = out_radius;
   tiles_touched[idx] = out_tiles;
-  depth_keys[idx] = out_depth_bits;  // input of the P-element depth sort (api.cu)
-  depth_vals[idx] = idx;
+  if (depth_keys != nullptr) {  // input of the P-element depth sort (onesweep binning only, api.cu)
+    depth_keys[idx] = out_depth_bits;
+    depth_vals[idx] = idx;
+  }
 }
 
 // markVisible / checkFrustum (rasterizer_impl.cu:54-66)

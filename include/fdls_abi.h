@@ -65,6 +65,8 @@ typedef struct FdlsLayout {
   size_t n_contrib; /* u32[H*W] */
   size_t ranges;    /* uint2[tiles] */
   size_t tile_max_contrib; /* u32[tiles]: max n_contrib over the tile's pixels (lets backward skip the tail) */
+  size_t tile_start;       /* u32[tiles+1]: exclusive scan of the per-tile instance counts (binning_algo 0) */
+  size_t tile_cursor;      /* u32[tiles]: per-tile counters / scatter cursors (binning_algo 0) */
   /* binning */
   size_t keys_alt; /* u64[capacity] ping-pong partner of `keys` */
   size_t keys;     /* u64[capacity] sorted keys after the forward (reference: point_list_keys) */
@@ -113,6 +115,9 @@ typedef struct FdlsFwdArgs {
   /* optional: array of FDLS_FWD_EVENTS cudaEvent_t handles recorded on the stream between stages
    * [0] start, [1] preprocess, [2] scan, [3] duplicate, [4] sort, [5] tile ranges, [6] compositor; null = off */
   void** stage_events;
+  /* binning algorithm: 0 = tile-bucketed count/scan/scatter + per-tile shared-memory sort (default),
+   * 1 = key duplication + onesweep LSD radix sort (the reference's structure).  Results are identical. */
+  int32_t binning_algo;
 } FdlsFwdArgs;
 #define FDLS_FWD_EVENTS 7
 

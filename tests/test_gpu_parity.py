@@ -44,9 +44,11 @@ def _assert_close(a, b, rtol, what, atol_frac=1e-6):
 CASES = [("tiny", 3, (1, 1, 1)), ("tiny", 6, (0, 0, 0)), ("small", 3, (1, 1, 1)), ("small", 6, (1, 1, 1))]
 
 
+@pytest.mark.parametrize("algo", ["bucket", "onesweep"])
 @pytest.mark.parametrize("name,F,bg", CASES)
-def test_forward_bit_exact_stages(synth, name, F, bg):
+def test_forward_bit_exact_stages(synth, monkeypatch, name, F, bg, algo):
     _need_ref(F)
+    monkeypatch.setenv("FDLS_BINNING", algo)
     s = synth.scene(name, F=F, bg=bg)
     ref = refcuda.Ref(F)
     r = ref.forward(s)
@@ -55,12 +57,13 @@ def test_forward_bit_exact_stages(synth, name, F, bg):
     _assert_same(o.radii, r.radii, "radii")
     vis = (r.radii > 0)
     _assert_same(o.tiles_touched, r.tiles_touched, "tiles_touched")
-    # point_offsets: this build scans the tile counts in DEPTH order, so only the total is comparable
-    assert int(o.point_offsets[-1]) == int(r.point_offsets[-1]) == r.R
-    order = o.depth_order.long()
-    assert torch.equal(torch.sort(order).values, torch.arange(s.P, device="cuda"))  # a permutation ...
-    dkey = torch.where(r.radii > 0, r.depths.view(torch.int32).long(), torch.full_like(order, 0xffffffff))
-    assert bool((dkey[order][1:] >= dkey[order][:-1]).all())  # ... sorted by depth bits
+    if algo == "onesweep":
+        # point_offsets: that path scans the tile counts in DEPTH order, so only the total is comparable
+        assert int(o.point_offsets[-1]) == int(r.point_offsets[-1]) == r.R
+        order = o.depth_order.long()
+        assert torch.equal(torch.sort(order).values, torch.arange(s.P, device="cuda"))  # a permutation ...
+        dkey = torch.where(r.radii > 0, r.depths.view(torch.int32).long(), torch.full_like(order, 0xffffffff))
+        assert bool((dkey[order][1:] >= dkey[order][:-1]).all())  # ... sorted by depth bits
     _assert_same(o.depths[vis], r.depths[vis], "depths")
     _assert_same(o.means2D[vis], r.means2D[vis], "means2D")
     _assert_same(o.conic_opacity[vis], r.conic_opacity[vis], "conic_opacity")
@@ -100,6 +103,26 @@ def test_backward_matches_reference(synth, name, F, bg, depth_grad):
                      ("cov3D", g.cov3D, gr.cov3D), ("sh", g.sh, gr.sh), ("scales", g.scales, gr.scales),
                      ("rots", g.rots, gr.rots)):
         _assert_grad(a, b, "dL_d" + nm)
+
+
+@pytest.mark.parametrize("algo", ["bucket", "onesweep"])
+@pytest.mark.parametrize("P", [30_000, 120_000])
+def test_long_tile_segments(synth, monkeypatch, algo, P):
+    """Tiles holding far more than 4096 instances (the shared-memory sort's run length): exercises the run-merge path
+    of the bucketed binning (one and several merge levels) and multi-round compositing."""
+    _need_ref(3)
+    monkeypatch.setenv("FDLS_BINNING", algo)
+    s = synth.scene("tiny", P=P)  # 64x48 image = 12 tiles
+    r = refcuda.Ref(3).forward(s)
+    o = helpers.run_forward(s)
+    per_tile = (r.ranges[:, 1] - r.ranges[:, 0]).max().item()
+    assert per_tile > (4096 if P < 100_000 else 3 * 4096), per_tile
+    assert o.R == r.R
+    _assert_same(o.keys, r.keys, "sorted keys")
+    _assert_same(o.point_list, r.point_list, "sorted values")
+    _assert_same(o.ranges, r.ranges, "tile ranges")
+    _assert_same(o.n_contrib, r.n_contrib, "n_contrib")
+    _assert_close(o.color, r.color, IMG_RTOL, "color")
 
 
 def test_no_feature_and_precomputed_inputs(synth):
