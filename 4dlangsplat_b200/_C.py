@@ -101,7 +101,7 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
     a.geom_ws, a.geom_bytes, a.img_ws, a.img_bytes = geom.data_ptr(), sizes.geom_bytes, img.data_ptr(), sizes.img_bytes
     a.num_rendered_host = st["pinned"].data_ptr()
     a.num_rendered_hint = -1
-    a.binning_algo = 1 if os.environ.get("FDLS_BINNING", "bucket") == "onesweep" else 0
+    a.binning_algo = 1 if os.environ.get("FDLS_BINNING", "partition") == "onesweep" else 0
     if profile["fwd"] is not None:
         a.stage_events = profile["fwd"]
     stream = _stream()

@@ -34,15 +34,16 @@ uint32_t* sort_hist(void* scratch);
 int sort_run(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
              const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, bool have_hist,
              cudaStream_t st);
-// binning_bucket.cu
-cudaError_t launch_tile_count(int P, const float4* rec, const int* radii, int gx, int gy, uint32_t* counters,
-                              cudaStream_t st);
-cudaError_t launch_tile_scan(int T, uint32_t* counters, uint32_t* tile_start, uint2* ranges, uint32_t* num_rendered,
-                             long long capacity, cudaStream_t st);
-cudaError_t launch_tile_scatter_sort(int P, const float4* rec, const int* radii, int gx, int gy, uint32_t* counters,
-                                     const uint32_t* tile_start, const uint32_t* num_rendered, long long capacity,
-                                     uint64_t* seg, uint64_t* keys_out, uint32_t* point_list, void** events,
-                                     cudaStream_t st);
+// binning_partition.cu
+bool partition_supported(int T);
+size_t partition_table_bytes(int P, int T);
+cudaError_t launch_partition_count(int P, int gx, int gy, const uint32_t* order, const int* radii, const float4* rec,
+                                   uint32_t* table, uint32_t* tile_total, uint32_t* tile_start, uint2* ranges,
+                                   uint32_t* num_rendered, long long capacity, cudaStream_t st);
+cudaError_t launch_partition_scatter(int P, int gx, int gy, const uint32_t* order, const int* radii, const float4* rec,
+                                     const uint32_t* table, const uint32_t* tile_total, uint32_t* tile_start,
+                                     uint2* ranges, uint32_t* num_rendered, uint32_t* point_list, uint64_t* keys,
+                                     long long capacity, cudaStream_t st);
 // render_fwd.cu / render_bwd.cu / preprocess_bwd.cu
 cudaError_t launch_render_fwd(int F, const uint2* ranges, const uint32_t* point_list, const float4* rec, int W, int H,
                               int gx, int gy, const float* bg, float* final_T, uint32_t* n_contrib, uint32_t* tile_max,
@@ -83,6 +84,7 @@ static void compute_layout(int P, int W, int H, long long capacity, FdlsLayout* 
   L->scan_scratch = o;  o += scan_scratch_bytes((int)Pz);
   L->depth_order = o;   o += align_up(Pz * 4);
   L->depth_scratch = o; o += align_up(Pz * 8) * 2 + align_up(Pz * 4) + sort_scratch_bytes((long long)Pz);
+  L->part_table = o;    o += partition_supported((int)tiles) ? partition_table_bytes((int)Pz, (int)tiles) : 256;
   S->geom_bytes = o;
   o = 0;
   L->final_T = o;          o += align_up(HW * 4);
@@ -189,20 +191,23 @@ FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
   uint32_t* dv_b = (uint32_t*)(g + L.depth_scratch + 2 * align_up(Pz * 8));
   char* dscr = g + L.depth_scratch + 2 * align_up(Pz * 8) + align_up(Pz * 4);
   uint32_t* order = (uint32_t*)(g + L.depth_order);
-  const bool bucket = a->binning_algo == 0;
+  const int gx1 = cdiv(a->W, TILE), gy1 = cdiv(a->H, TILE);
+  const bool partition = a->binning_algo == 0 && partition_supported(gx1 * gy1);
   if (launch_preprocess_fwd(a, vp, (float4*)(g + L.rec), (uint32_t*)(g + L.tiles_touched), (uint8_t*)(g + L.clamped),
-                            bucket ? nullptr : dk_a, order, st) != cudaSuccess)
+                            dk_a, order, st) != cudaSuccess)
     return FDLS_ECUDA;
   rec(a->stage_events, 1, st);
-  if (bucket) {
-    // K1 + K2 of binning_bucket.cu: per-tile instance counts -> tile starts (== ranges) and R
+  // (1) order the GAUSSIANS by depth bits (stable, P elements) ...
+  int sel = sort_pairs(dk_a, dk_b, order, dv_b, a->P, nullptr, 0, 32, dscr, sort_scratch_bytes((long long)Pz), st);
+  if (sel < 0) return sel;
+  if (sel != 0) return FDLS_ECUDA;  // 4 passes: result is back in the `a` buffers by construction
+  if (partition) {
+    // (2a) binning_partition.cu kernels A, S1, S2: per-tile instance counts -> tile starts, ranges, R
     char* im = (char*)a->img_ws;
-    const int gx = cdiv(a->W, TILE), gy = cdiv(a->H, TILE);
-    if (launch_tile_count(a->P, (const float4*)(g + L.rec), a->radii, gx, gy, (uint32_t*)(im + L.tile_cursor), st) !=
-        cudaSuccess)
-      return FDLS_ECUDA;
-    if (launch_tile_scan(gx * gy, (uint32_t*)(im + L.tile_cursor), (uint32_t*)(im + L.tile_start),
-                         (uint2*)(im + L.ranges), nr, a->capacity, st) != cudaSuccess)
+    if (launch_partition_count(a->P, gx1, gy1, order, a->radii, (const float4*)(g + L.rec),
+                               (uint32_t*)(g + L.part_table), (uint32_t*)(im + L.tile_cursor),
+                               (uint32_t*)(im + L.tile_start), (uint2*)(im + L.ranges), nr, a->capacity,
+                               st) != cudaSuccess)
       return FDLS_ECUDA;
     rec(a->stage_events, 2, st);
     if (a->num_rendered_host &&
@@ -210,10 +215,6 @@ FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
       return FDLS_ECUDA;
     return FDLS_OK;
   }
-  // (1) order the GAUSSIANS by depth bits (stable, P elements) ...
-  int sel = sort_pairs(dk_a, dk_b, order, dv_b, a->P, nullptr, 0, 32, dscr, sort_scratch_bytes((long long)Pz), st);
-  if (sel < 0) return sel;
-  if (sel != 0) return FDLS_ECUDA;  // 4 passes: result is back in the `a` buffers by construction
   // (2) ... and scan the tile counts in that order, so instances are emitted depth-sorted
   if (launch_scan(a->P, (uint32_t*)(g + L.tiles_touched), order, (uint32_t*)(g + L.point_offsets),
                   (uint32_t*)(g + L.scan_scratch), nr, a->capacity, st) != cudaSuccess)
@@ -244,16 +245,20 @@ FDLS_API int fdls_bin_and_render(const FdlsFwdArgs* a, void* stream) {
   if (a->num_rendered_hint >= 0 && a->num_rendered_hint < n_grid) n_grid = a->num_rendered_hint;
   uint2* ranges = (uint2*)(im + L.ranges);
   const uint32_t* point_list = nullptr;
-  if (a->binning_algo == 0) {
+  if (a->binning_algo == 0 && partition_supported(gx * gy)) {
     if (n_grid > 0) {
-      // K3 + K4 of binning_bucket.cu (ranges were written by K2 in stage 1)
-      if (launch_tile_scatter_sort(a->P, (const float4*)(g + L.rec), a->radii, gx, gy, (uint32_t*)(im + L.tile_cursor),
-                                   (const uint32_t*)(im + L.tile_start), nr, n_grid < a->capacity ? n_grid : a->capacity,
-                                   (uint64_t*)(b + L.keys_alt), (uint64_t*)(b + L.keys), (uint32_t*)(b + L.vals),
-                                   a->stage_events, st) != cudaSuccess)
+      // (2b) binning_partition.cu kernel B: every instance goes straight to its final slot
+      if (launch_partition_scatter(a->P, gx, gy, (const uint32_t*)(g + L.depth_order), a->radii,
+                                   (const float4*)(g + L.rec), (const uint32_t*)(g + L.part_table),
+                                   (const uint32_t*)(im + L.tile_cursor), (uint32_t*)(im + L.tile_start), ranges, nr,
+                                   (uint32_t*)(b + L.vals), (uint64_t*)(b + L.keys),
+                                   n_grid < a->capacity ? n_grid : a->capacity, st) != cudaSuccess)
         return FDLS_ECUDA;
       point_list = (const uint32_t*)(b + L.vals);
+    } else {
+      if (cudaMemsetAsync(ranges, 0, (size_t)gx * gy * sizeof(uint2), st) != cudaSuccess) return FDLS_ECUDA;
     }
+    rec(a->stage_events, 3, st);
     rec(a->stage_events, 4, st);
   } else if (n_grid > 0) {
     // Instances were emitted in depth order, so a STABLE sort on the tile bits alone yields exactly the order of the

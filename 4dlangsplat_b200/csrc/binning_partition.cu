@@ -1,0 +1,276 @@
+// binning_partition.cu -- default binning: ONE stable partition pass by tile over depth-ordered Gaussians.
+// Replaces duplicateWithKeys + cub::DeviceRadixSort::SortPairs + identifyTileRanges
+// (rasterizer_impl.cu:70-138, :293-318) without ever materialising unsorted keys.
+//
+// The reference sorts R (tile<<32|depth) keys with a 6-pass LSD radix sort.  The same order is obtained by
+//   (1) sorting the P GAUSSIANS by depth bits once (stable onesweep over P elements, radix_sort.cu; R/P ~ 10), and
+//   (2) a stable multi-way partition of the depth-ordered instance stream by tile id -- a single radix pass whose
+//       "digit" is the whole tile id (T <= 10240 bins), done here.
+// Ties in depth keep ascending Gaussian index through (1)'s stability, exactly like the reference's stable sort, so
+// sorted keys / values / ranges are bit-identical.
+//
+// Kernels (A and B walk the depth-ordered Gaussians warp-cooperatively: one Gaussian at a time per warp, its tiles
+// spread over the 32 lanes; all ranking happens in per-warp shared-memory counters -- no global atomics):
+//   A  part_count    per CTA chunk: instances per tile                         -> table[cta][tile]
+//   S1 part_colscan  exclusive scan of table over CTAs (per tile), tile totals -> table (in place), tile_total
+//   S2 part_tilescan exclusive scan over tiles                                 -> tile_start, ranges, R
+//   B  part_scatter  re-walk: rank = tile_start + table[cta][tile] + warp prefix + running count; write point_list
+//                    (and the reference-format key) straight to its final slot.
+// HBM traffic: ~12 B written per instance (4 B id + 8 B key) + O(CTAs*T) table; nothing is read back per instance.
+#include "common.cuh"
+
+namespace fdls {
+
+constexpr int PT_THREADS = 256;
+constexpr int PT_WARPS = PT_THREADS / 32;
+constexpr int PT_MAX_TILES = 10240;  // 8 warps x 10240 x 2 B + 10240 x 4 B = 200 KB of shared memory
+
+__host__ __device__ inline int pt_chunk(int P) {  // Gaussians per CTA: keep <= ~1200 CTAs, multiple of 256
+  int ch = 512;
+  while ((long long)ch * 1200 < P) ch *= 2;
+  return ch;
+}
+
+// u16 counters packed two per 32-bit word; returns the previous value of counter t
+__device__ __forceinline__ uint32_t cnt_inc(uint32_t* w, uint32_t t) {
+  const uint32_t old = atomicAdd(&w[t >> 1], (t & 1u) ? 0x10000u : 1u);
+  return (t & 1u) ? (old >> 16) : (old & 0xffffu);
+}
+__device__ __forceinline__ uint32_t cnt_get(const uint32_t* w, uint32_t t) {
+  const uint32_t v = w[t >> 1];
+  return (t & 1u) ? (v >> 16) : (v & 0xffffu);
+}
+
+// Walk this warp's slice [g_begin, g_end) of the depth-ordered Gaussian list, one Gaussian at a time in order.
+template <bool SCATTER>
+__device__ __forceinline__ void walk(int g_begin, int g_end, int P, const uint32_t* __restrict__ order,
+                                     const int* __restrict__ radii, const float4* __restrict__ rec, int gx, int gy,
+                                     uint32_t* wcnt, const uint32_t* blockbase, uint32_t* __restrict__ point_list,
+                                     uint64_t* __restrict__ keys, long long capacity, int lane) {
+  for (int g0 = g_begin; g0 < g_end; g0 += 32) {
+    const int pos = g0 + lane;
+    uint32_t idx = 0, count = 0, depth_bits = 0;
+    uint2 rmin = {0, 0}, rmax = {0, 0};
+    if (pos < g_end && pos < P) {
+      idx = order[pos];
+      const int radius = radii[idx];
+      if (radius > 0) {
+        const float4 r0 = rec[(size_t)idx * 4];
+        if (SCATTER) depth_bits = __float_as_uint(rec[(size_t)idx * 4 + 1].z);
+        get_rect(r0.x, r0.y, radius, gx, gy, rmin, rmax);
+        count = (rmax.x - rmin.x) * (rmax.y - rmin.y);
+      }
+    }
+    uint32_t todo = __ballot_sync(0xffffffffu, count > 0);
+    while (todo) {
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const uint32_t b_cnt = __shfl_sync(0xffffffffu, count, src);
+      const uint32_t b_x0 = __shfl_sync(0xffffffffu, rmin.x, src);
+      const uint32_t b_y0 = __shfl_sync(0xffffffffu, rmin.y, src);
+      const uint32_t b_w = __shfl_sync(0xffffffffu, rmax.x - rmin.x, src);
+      uint32_t b_depth = 0, b_idx = 0;
+      if (SCATTER) {
+        b_depth = __shfl_sync(0xffffffffu, depth_bits, src);
+        b_idx = __shfl_sync(0xffffffffu, idx, src);
+      }
+      for (uint32_t i = lane; i < b_cnt; i += 32) {
+        const uint32_t row = i / b_w;
+        const uint32_t t = (b_y0 + row) * gx + b_x0 + (i - row * b_w);
+        const uint32_t old = cnt_inc(wcnt, t);
+        if (SCATTER) {
+          const long long slot = (long long)blockbase[t] + old;
+          if (slot < capacity) {
+            point_list[slot] = b_idx;
+            keys[slot] = ((uint64_t)t << 32) | b_depth;
+          }
+        }
+      }
+      __syncwarp();
+    }
+  }
+}
+
+__global__ void __launch_bounds__(PT_THREADS)
+part_count_kernel(int P, int T, int chunk, const uint32_t* __restrict__ order, const int* __restrict__ radii,
+                  const float4* __restrict__ rec, int gx, int gy, uint32_t* __restrict__ table) {
+  extern __shared__ uint32_t pt_smem[];
+  const int words = (T + 1) / 2;  // per-warp counter words
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < PT_WARPS * words; i += PT_THREADS) pt_smem[i] = 0;
+  __syncthreads();
+  const int per_warp = chunk / PT_WARPS;
+  const int g_begin = blockIdx.x * chunk + warp * per_warp;
+  walk<false>(g_begin, min(g_begin + per_warp, P), P, order, radii, rec, gx, gy, pt_smem + warp * words, nullptr,
+              nullptr, nullptr, 0, lane);
+  __syncthreads();
+  uint32_t* row = table + (size_t)blockIdx.x * T;
+  for (int t = tid; t < T; t += PT_THREADS) {
+    uint32_t c = 0;
+#pragma unroll
+    for (int w = 0; w < PT_WARPS; ++w) c += cnt_get(pt_smem + w * words, t);
+    row[t] = c;
+  }
+}
+
+// per tile: exclusive scan over the CTAs (table is [ctas][T], coalesced along t); tile_total[t] = column sum
+__global__ void __launch_bounds__(256)
+part_colscan_kernel(int T, int ctas, uint32_t* __restrict__ table, uint32_t* __restrict__ tile_total) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= T) return;
+  uint32_t run = 0;
+  int b = 0;
+  for (; b + 8 <= ctas; b += 8) {
+    uint32_t v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = table[(size_t)(b + k) * T + t];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      table[(size_t)(b + k) * T + t] = run;
+      run += v[k];
+    }
+  }
+  for (; b < ctas; ++b) {
+    const uint32_t v = table[(size_t)b * T + t];
+    table[(size_t)b * T + t] = run;
+    run += v;
+  }
+  tile_total[t] = run;
+}
+
+__global__ void __launch_bounds__(PT_THREADS)
+part_scatter_kernel(int P, int T, int chunk, const uint32_t* __restrict__ order, const int* __restrict__ radii,
+                    const float4* __restrict__ rec, int gx, int gy, const uint32_t* __restrict__ table,
+                    const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ point_list,
+                    uint64_t* __restrict__ keys, long long capacity) {
+  extern __shared__ uint32_t pt_smem[];
+  const int words = (T + 1) / 2;
+  uint32_t* blockbase = pt_smem + PT_WARPS * words;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < PT_WARPS * words; i += PT_THREADS) pt_smem[i] = 0;
+  __syncthreads();
+  const int per_warp = chunk / PT_WARPS;
+  const int g_begin = blockIdx.x * chunk + warp * per_warp;
+  const int g_end = min(g_begin + per_warp, P);
+  // walk 1: per-warp tile counts (same as kernel A)
+  walk<false>(g_begin, g_end, P, order, radii, rec, gx, gy, pt_smem + warp * words, nullptr, nullptr, nullptr, 0, lane);
+  __syncthreads();
+  // counts -> exclusive prefix across the warps of this CTA (in place); global base of the CTA per tile
+  const uint32_t* row = table + (size_t)blockIdx.x * T;
+  for (int w2 = tid; w2 < words; w2 += PT_THREADS) {  // two tiles per word; the two u16 lanes scan independently
+    uint32_t run = 0;
+#pragma unroll
+    for (int w = 0; w < PT_WARPS; ++w) {
+      const uint32_t c = pt_smem[w * words + w2];
+      pt_smem[w * words + w2] = run;
+      run += c;  // no carry between halves: a CTA emits < 65536 instances per tile (chunk <= 65535 Gaussians)
+    }
+    const int t0 = 2 * w2;
+    blockbase[t0] = tile_start[t0] + row[t0];
+    if (t0 + 1 < T) blockbase[t0 + 1] = tile_start[t0 + 1] + row[t0 + 1];
+  }
+  __syncthreads();
+  // walk 2: the running counters now start at each warp's prefix -> final slots
+  walk<true>(g_begin, g_end, P, order, radii, rec, gx, gy, pt_smem + warp * words, blockbase, point_list, keys,
+             capacity, lane);
+}
+
+// tile_scan_kernel lives in binning_scan below: exclusive scan over tile totals -> tile_start, ranges, R
+__global__ void __launch_bounds__(1024)
+part_tilescan_kernel(int T, const uint32_t* __restrict__ tile_total, uint32_t* __restrict__ tile_start,
+                     uint2* __restrict__ ranges, uint32_t* __restrict__ num_rendered, long long capacity) {
+  __shared__ uint32_t s_warp[33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t carry = 0;
+  for (int base = 0; base < T; base += 1024) {
+    const int t = base + threadIdx.x;
+    const uint32_t c = t < T ? tile_total[t] : 0;
+    uint32_t incl = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += v;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      const uint32_t w = s_warp[lane];
+      uint32_t wi = w;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, wi, d);
+        if (lane >= d) wi += v;
+      }
+      s_warp[lane] = wi - w;
+      if (lane == 31) s_warp[32] = wi;
+    }
+    __syncthreads();
+    const uint32_t start = carry + s_warp[warp] + incl - c;
+    if (t < T) {
+      tile_start[t] = start;
+      // the reference leaves empty tiles at (0,0) (cudaMemset, rasterizer_impl.cu:314); clip to the workspace so that
+      // the compositor never walks past it after a capacity overflow (the caller then re-runs with a larger one)
+      const long long lo = min((long long)start, capacity), hi = min((long long)start + c, capacity);
+      ranges[t] = hi > lo ? make_uint2((uint32_t)lo, (uint32_t)hi) : make_uint2(0u, 0u);
+    }
+    carry += s_warp[32];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    tile_start[T] = carry;
+    num_rendered[0] = carry;
+    num_rendered[1] = ((long long)carry > capacity) ? 1u : 0u;
+  }
+}
+
+bool partition_supported(int T) { return T <= PT_MAX_TILES; }
+int partition_ctas(int P) { return cdiv(P < 1 ? 1 : P, pt_chunk(P)); }
+size_t partition_table_bytes(int P, int T) { return align_up((size_t)partition_ctas(P) * T * sizeof(uint32_t)); }
+
+static size_t pt_smem_bytes(int T, bool scatter) {
+  const size_t words = (size_t)(T + 1) / 2;
+  return (PT_WARPS * words + (scatter ? (size_t)T + 1 : 0)) * sizeof(uint32_t);
+}
+
+cudaError_t launch_partition_count(int P, int gx, int gy, const uint32_t* order, const int* radii, const float4* rec,
+                                   uint32_t* table, uint32_t* tile_total, uint32_t* tile_start, uint2* ranges,
+                                   uint32_t* num_rendered, long long capacity, cudaStream_t st) {
+  const int T = gx * gy, chunk = pt_chunk(P), ctas = partition_ctas(P);
+  static size_t attr_a = 0;
+  const size_t sa = pt_smem_bytes(T, false);
+  if (sa > attr_a) {
+    cudaError_t e = cudaFuncSetAttribute(part_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa);
+    if (e != cudaSuccess) return e;
+    attr_a = sa;
+  }
+  part_count_kernel<<<ctas, PT_THREADS, sa, st>>>(P, T, chunk, order, radii, rec, gx, gy, table);
+  count_launch();
+  part_colscan_kernel<<<cdiv(T, 256), 256, 0, st>>>(T, ctas, table, tile_total);
+  count_launch();
+  part_tilescan_kernel<<<1, 1024, 0, st>>>(T, tile_total, tile_start, ranges, num_rendered, capacity);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_partition_scatter(int P, int gx, int gy, const uint32_t* order, const int* radii, const float4* rec,
+                                     const uint32_t* table, const uint32_t* tile_total, uint32_t* tile_start,
+                                     uint2* ranges, uint32_t* num_rendered, uint32_t* point_list, uint64_t* keys,
+                                     long long capacity, cudaStream_t st) {
+  const int T = gx * gy, chunk = pt_chunk(P), ctas = partition_ctas(P);
+  static size_t attr_b = 0;
+  const size_t sb = pt_smem_bytes(T, true);
+  if (sb > attr_b) {
+    cudaError_t e = cudaFuncSetAttribute(part_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb);
+    if (e != cudaSuccess) return e;
+    attr_b = sb;
+  }
+  // ranges depend on the capacity of THIS call's workspace (clipping): recompute them (one tiny CTA)
+  part_tilescan_kernel<<<1, 1024, 0, st>>>(T, tile_total, tile_start, ranges, num_rendered, capacity);
+  count_launch();
+  part_scatter_kernel<<<ctas, PT_THREADS, sb, st>>>(P, T, chunk, order, radii, rec, gx, gy, table, tile_start,
+                                                    point_list, keys, capacity);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace fdls

@@ -44,7 +44,7 @@ def _assert_close(a, b, rtol, what, atol_frac=1e-6):
 CASES = [("tiny", 3, (1, 1, 1)), ("tiny", 6, (0, 0, 0)), ("small", 3, (1, 1, 1)), ("small", 6, (1, 1, 1))]
 
 
-@pytest.mark.parametrize("algo", ["bucket", "onesweep"])
+@pytest.mark.parametrize("algo", ["partition", "onesweep"])
 @pytest.mark.parametrize("name,F,bg", CASES)
 def test_forward_bit_exact_stages(synth, monkeypatch, name, F, bg, algo):
     _need_ref(F)
@@ -105,11 +105,11 @@ def test_backward_matches_reference(synth, name, F, bg, depth_grad):
         _assert_grad(a, b, "dL_d" + nm)
 
 
-@pytest.mark.parametrize("algo", ["bucket", "onesweep"])
+@pytest.mark.parametrize("algo", ["partition", "onesweep"])
 @pytest.mark.parametrize("P", [30_000, 120_000])
 def test_long_tile_segments(synth, monkeypatch, algo, P):
     """Tiles holding far more than 4096 instances (the shared-memory sort's run length): exercises the run-merge path
-    of the bucketed binning (one and several merge levels) and multi-round compositing."""
+    of the partition binning (one and several merge levels) and multi-round compositing."""
     _need_ref(3)
     monkeypatch.setenv("FDLS_BINNING", algo)
     s = synth.scene("tiny", P=P)  # 64x48 image = 12 tiles
