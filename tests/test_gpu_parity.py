@@ -106,7 +106,7 @@ def test_backward_matches_reference(synth, name, F, bg, depth_grad):
 
 
 @pytest.mark.parametrize("algo", ["partition", "onesweep"])
-@pytest.mark.parametrize("P", [30_000, 120_000])
+@pytest.mark.parametrize("P", [60_000, 150_000])
 def test_long_tile_segments(synth, monkeypatch, algo, P):
     """Tiles holding far more than 4096 instances (the shared-memory sort's run length): exercises the run-merge path
     of the partition binning (one and several merge levels) and multi-round compositing."""
