@@ -113,29 +113,31 @@ part_count_kernel(int P, int T, int chunk, const uint32_t* __restrict__ order, c
   }
 }
 
-// per tile: exclusive scan over the CTAs (table is [ctas][T], coalesced along t); tile_total[t] = column sum
-__global__ void __launch_bounds__(256)
+// per tile: exclusive scan over the CTAs (table is [ctas][T], coalesced along t); tile_total[t] = column sum.
+// CTA = 32 tiles x 32 row groups: each thread sums its slice of rows, the 32 slice sums of a tile are scanned through
+// shared memory, then the slice is rewritten as running prefixes (second read served by L1/L2).
+__global__ void __launch_bounds__(1024)
 part_colscan_kernel(int T, int ctas, uint32_t* __restrict__ table, uint32_t* __restrict__ tile_total) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= T) return;
+  __shared__ uint32_t s_sum[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int t = blockIdx.x * 32 + tx;
+  const int per = (ctas + 31) / 32;
+  const int r0 = ty * per, r1 = min(r0 + per, ctas);
+  uint32_t sum = 0;
+  if (t < T)
+    for (int r = r0; r < r1; ++r) sum += table[(size_t)r * T + t];
+  s_sum[ty][tx] = sum;
+  __syncthreads();
   uint32_t run = 0;
-  int b = 0;
-  for (; b + 8 <= ctas; b += 8) {
-    uint32_t v[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) v[k] = table[(size_t)(b + k) * T + t];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      table[(size_t)(b + k) * T + t] = run;
-      run += v[k];
+  for (int k = 0; k < ty; ++k) run += s_sum[k][tx];
+  if (t < T) {
+    for (int r = r0; r < r1; ++r) {
+      const uint32_t v = table[(size_t)r * T + t];
+      table[(size_t)r * T + t] = run;
+      run += v;
     }
+    if (ty == 31) tile_total[t] = run;  // the last slice ends at the column total (empty slices pass `run` through)
   }
-  for (; b < ctas; ++b) {
-    const uint32_t v = table[(size_t)b * T + t];
-    table[(size_t)b * T + t] = run;
-    run += v;
-  }
-  tile_total[t] = run;
 }
 
 __global__ void __launch_bounds__(PT_THREADS)
@@ -245,7 +247,7 @@ cudaError_t launch_partition_count(int P, int gx, int gy, const uint32_t* order,
   }
   part_count_kernel<<<ctas, PT_THREADS, sa, st>>>(P, T, chunk, order, radii, rec, gx, gy, table);
   count_launch();
-  part_colscan_kernel<<<cdiv(T, 256), 256, 0, st>>>(T, ctas, table, tile_total);
+  part_colscan_kernel<<<cdiv(T, 32), 1024, 0, st>>>(T, ctas, table, tile_total);
   count_launch();
   part_tilescan_kernel<<<1, 1024, 0, st>>>(T, tile_total, tile_start, ranges, num_rendered, capacity);
   count_launch();

@@ -84,9 +84,12 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   __shared__ float4 s_rec[2][4][RB_THREADS];
   __shared__ uint32_t s_id[2][RB_THREADS];
   __shared__ uint32_t s_strips[2][RB_THREADS];  // strip_summary().y of each staged Gaussian
+  __shared__ uint8_t s_list[RB_THREADS / 32][RB_THREADS];
 
   const int tid = threadIdx.x, lane = tid & 31;
-  const uint32_t strip_bit = 1u << (tid >> 5);
+  const int warp = tid >> 5;
+  const uint32_t strip_bit = 1u << warp;
+  const uint32_t lt_mask = (1u << lane) - 1u;
   const uint32_t tile = blockIdx.x;
   const uint32_t tx = tile % gx, ty = tile / gx;
   const uint2 pix = {tx * TILE + (tid & (TILE - 1)), ty * TILE + (tid >> 4)};
@@ -159,8 +162,19 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     }
     __syncthreads();
     const int cnt = min(RB_THREADS, M - i * RB_THREADS);
-    for (int j = 0; j < cnt; j++) {
-      if (!(s_strips[buf][j] & strip_bit)) continue;  // warp-uniform skip, see common.cuh
+    // per-warp compaction of the batch to the Gaussians that can reach this warp's strip (see render_fwd.cu)
+    int n_hit = 0;
+#pragma unroll
+    for (int k = 0; k < RB_THREADS / 32; ++k) {
+      const int jj = k * 32 + lane;
+      const bool hit = jj < cnt && (s_strips[buf][jj] & strip_bit);
+      const uint32_t m = __ballot_sync(RB_FULL, hit);
+      if (hit) s_list[warp][n_hit + __popc(m & lt_mask)] = (uint8_t)jj;
+      n_hit += __popc(m);
+    }
+    __syncwarp();
+    for (int h = 0; h < n_hit; h++) {
+      const int j = s_list[warp][h];
       const int q = M - 1 - (i * RB_THREADS + j);  // == the reference's `contributor` after its decrement
       const float4 a = s_rec[buf][0][j];           // x, y, conic.x, conic.y
       const float4 b = s_rec[buf][1][j];           // conic.z, opacity, depth, r

@@ -10,6 +10,9 @@
 //    double-buffered 2 x 16 KB shared-memory ring, so the gather of batch i+1 overlaps the blend of batch i.
 //    The reference instead gathers colour / language / depth from GLOBAL memory per contributing (pixel, Gaussian)
 //    pair (forward.cu:362-369).
+//  * each warp owns a 16x2-pixel strip; the staging thread computes a conservative strip mask per Gaussian and every
+//    warp compacts the batch to the Gaussians that can touch its strip before blending (most of a tile's list misses
+//    any given strip, and skipping them one by one was the dominant instruction cost).
 //  * a conservative log-domain pre-test skips the expf for pairs whose alpha is certainly below 1/255; the exact
 //    reference test still decides every pair near the threshold, so results do not change.
 //  * F is a template parameter dispatched at run time (the reference needs a rebuild per F: setup.py:18,32).
@@ -38,6 +41,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   // [buf][slot 0..3][thread]: conflict-free cp.async writes, broadcast reads
   __shared__ float4 s_rec[2][4][RF_THREADS];
   __shared__ float2 s_aux[2][RF_THREADS];  // strip_summary() of each staged Gaussian
+  __shared__ uint8_t s_list[RF_THREADS / 32][RF_THREADS];  // per-warp compacted indices into the staged batch
   __shared__ uint32_t s_max;
 
   const int tid = threadIdx.x;
@@ -48,7 +52,9 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const float2 pixf = {(float)pix.x, (float)pix.y};
   const bool inside = pix.x < (uint32_t)W && pix.y < (uint32_t)H;
   bool done = !inside;
-  const uint32_t strip_bit = 1u << (tid >> 5);
+  const int lane = tid & 31, warp = tid >> 5;
+  const uint32_t strip_bit = 1u << warp;
+  const uint32_t lt_mask = (1u << lane) - 1u;
 
   const uint2 range = ranges[tile];
   int toDo = range.y - range.x;
@@ -68,7 +74,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   };
 
   float T = 1.0f;
-  uint32_t contributor = 0, last_contributor = 0;
+  uint32_t last_contributor = 0;
   float C[3] = {0, 0, 0};
   float D = 0;
   float Fa[F > 0 ? F : 1] = {0};
@@ -89,16 +95,31 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     __syncthreads();
 
     const int cnt = min(RF_THREADS, toDo);
-    for (int j = 0; !done && j < cnt; j++) {
-      contributor++;
-      const float2 aux = s_aux[buf][j];
-      if (!(__float_as_uint(aux.y) & strip_bit)) continue;  // warp-uniform: no pixel of this strip can reach 1/255
+    // Per-warp compaction: the indices of the staged Gaussians that can reach this warp's 16x2 strip are gathered
+    // (in order) into a private list, so the blend loop never iterates over a Gaussian the whole warp would skip.
+    // `contributor` is the 1-based position in the tile's range, exactly the reference's running counter.
+    int n_hit = 0;
+    if (!__all_sync(0xffffffffu, done)) {
+#pragma unroll
+      for (int k = 0; k < RF_THREADS / 32; ++k) {
+        const int j = k * 32 + lane;
+        const bool hit = j < cnt && (__float_as_uint(s_aux[buf][j].y) & strip_bit);
+        const uint32_t m = __ballot_sync(0xffffffffu, hit);
+        if (hit) s_list[warp][n_hit + __popc(m & lt_mask)] = (uint8_t)j;
+        n_hit += __popc(m);
+      }
+      __syncwarp();
+    }
+    const uint32_t base = (uint32_t)i * RF_THREADS;
+    for (int q = 0; !done && q < n_hit; q++) {
+      const int j = s_list[warp][q];
+      const float thr = s_aux[buf][j].x;
       const float4 a = s_rec[buf][0][j];  // x, y, conic.x, conic.y
       const float4 b = s_rec[buf][1][j];  // conic.z, opacity, depth, r
       const float2 d = {a.x - pixf.x, a.y - pixf.y};
       const float power = -0.5f * (a.z * d.x * d.x + b.x * d.y * d.y) - a.w * d.x * d.y;
       if (power > 0.0f) continue;
-      if (power < aux.x) continue;  // certainly alpha < 1/255 (pre-test; exact test below)
+      if (power < thr) continue;  // certainly alpha < 1/255 (pre-test; exact test below)
       const float alpha = min(0.99f, b.y * exp(power));
       if (alpha < 1.0f / 255.0f) continue;
       const float test_T = T * (1 - alpha);
@@ -118,7 +139,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       }
       D += b.z * alpha * T;
       T = test_T;
-      last_contributor = contributor;
+      last_contributor = base + j + 1;
     }
     // also fences the shared ring before the next prefetch overwrites buffer `buf`
     if (__syncthreads_count(done) == RF_THREADS) break;
