@@ -12,6 +12,7 @@ Instance-count handling (the reference blocks on a D2H copy of num_rendered, ras
     If R overflowed the guess, stage 2 is simply re-run with the right size.  Results are identical in both modes.
 """
 import ctypes as C
+import functools
 import os
 
 import torch
@@ -45,9 +46,21 @@ def _prep(t, name):
         return t
     if not t.is_cuda:
         raise RuntimeError("%s must be a CUDA tensor (this build has no CPU path)" % name)
-    if t.dtype != torch.float32:
-        t = t.float()
-    return t.contiguous()
+    if t.dtype is torch.float32 and t.is_contiguous():  # the usual case: no new tensor object
+        return t
+    return t.float().contiguous()
+
+
+@functools.lru_cache(maxsize=4096)
+def _sizes(P, W, H, capacity):
+    """(geom_bytes, img_bytes, binning_bytes) for this shape; cached (one ctypes round trip per new shape)."""
+    s = _lib.workspace_sizes(P, W, H, capacity)
+    return s.geom_bytes, s.img_bytes, s.binning_bytes
+
+
+def _round_capacity(n):
+    """Capacity guesses are rounded up to 64 Ki instances so consecutive frames reuse the same allocator block."""
+    return (int(n) + 0xffff) & ~0xffff
 
 
 def _stream():
@@ -81,9 +94,9 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
     # rasterize_points.cu:72-78: a (1,) tensor stands in for the feature image when include_feature is false
     out_lang = torch.empty((F, H, W), **f32) if include_feature else torch.zeros((1,), **f32)
     radii = torch.empty((P,), dtype=torch.int32, device=dev)
-    sizes = _lib.workspace_sizes(P, W, H, 0)
-    geom = torch.empty(sizes.geom_bytes, dtype=torch.uint8, device=dev)
-    img = torch.empty(sizes.img_bytes, dtype=torch.uint8, device=dev)
+    geom_bytes, img_bytes, _ = _sizes(P, W, H, 0)
+    geom = torch.empty(geom_bytes, dtype=torch.uint8, device=dev)
+    img = torch.empty(img_bytes, dtype=torch.uint8, device=dev)
     if P == 0:  # rasterize_points.cu:91: kernels skipped, images are the fill values
         out_color.zero_(); out_depth.zero_(); out_lang.zero_()
         return 0, out_color, out_lang, out_depth, radii, geom, torch.empty(0, dtype=torch.uint8, device=dev), img
@@ -98,7 +111,7 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
     a.cov3D_precomp, a.viewmatrix, a.projmatrix, a.campos = _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos)
     a.out_color, a.out_depth, a.radii = out_color.data_ptr(), out_depth.data_ptr(), radii.data_ptr()
     a.out_language = out_lang.data_ptr() if include_feature else None
-    a.geom_ws, a.geom_bytes, a.img_ws, a.img_bytes = geom.data_ptr(), sizes.geom_bytes, img.data_ptr(), sizes.img_bytes
+    a.geom_ws, a.geom_bytes, a.img_ws, a.img_bytes = geom.data_ptr(), geom_bytes, img.data_ptr(), img_bytes
     a.num_rendered_host = st["pinned"].data_ptr()
     a.num_rendered_hint = -1
     a.binning_algo = 1 if os.environ.get("FDLS_BINNING", "partition") == "onesweep" else 0
@@ -107,7 +120,7 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
     stream = _stream()
 
     def run_stage2(capacity, hint):
-        bs = _lib.workspace_sizes(P, W, H, capacity).binning_bytes if capacity > 0 else 0
+        bs = _sizes(P, W, H, capacity)[2] if capacity > 0 else 0
         binning = torch.empty(bs, dtype=torch.uint8, device=dev)
         a.binning_ws, a.binning_bytes, a.capacity = (binning.data_ptr() if bs else None), bs, capacity
         a.num_rendered_hint = hint
@@ -117,10 +130,12 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
     speculative = os.environ.get("FDLS_SPECULATIVE", "1") != "0" and st["last_R"] is not None and not debug
     a.capacity = 0
     if speculative:
-        capacity = int(st["last_R"] * 1.25) + 4096
+        capacity = _round_capacity(st["last_R"] * 1.25 + 4096)
         a.capacity = capacity
         _lib.check(lib.fdls_preprocess(C.byref(a), stream), "fdls_preprocess")
-        ev = torch.cuda.Event()
+        ev = st.get("event")
+        if ev is None:
+            ev = st["event"] = torch.cuda.Event()
         ev.record()
         binning = run_stage2(capacity, -1)
         ev.synchronize()

@@ -125,8 +125,11 @@ class Workload:
         base, amp_d, phase_d = t(s.means3D), t(amp), t(phase)
         # this rank's shard of the sweep: timestamps rank, rank+world, ...
         self.times = [((i * world + rank) % N_TIMESTAMPS) / (N_TIMESTAMPS - 1.0) for i in range(N_TIMESTAMPS)]
-        self.means = [base + amp_d * torch.sin(2 * np.pi * tt + phase_d) for tt in self.times]
-        self.means_host = [m.cpu().pin_memory() for m in self.means]
+        tt = torch.tensor(self.times, device=dev, dtype=torch.float32).view(-1, 1, 1)
+        all_means = base[None] + amp_d[None] * torch.sin(2 * np.pi * tt + phase_d[None])  # (timestamps, P, 3)
+        self.means = list(all_means.unbind(0))
+        host = all_means.cpu().pin_memory()
+        self.means_host = list(host.unbind(0))
         self.sets = []
         for k in range(N_PARAM_SETS):
             self.sets.append(dict(scales=t(s.scales).clone(), rots=t(s.rotations).clone(), opac=t(s.opacities).clone(),
@@ -287,6 +290,174 @@ def run_reference(wl, steps, warmup, world):
                 h2d=h2d * FRAMES_PER_STEP, d2h=d2h * FRAMES_PER_STEP)
 
 
+TRAIN_VIEWS = 4  # BASELINE.json configs[2]: HyperNeRF-shaped training step, batch of 4 views
+
+
+class TrainWorkload:
+    """cfg3: B views of the cfg2-shaped scene (cameras 4 degrees apart), sharded round-robin over ranks."""
+
+    def __init__(self, name, rank, world, n_views=TRAIN_VIEWS):
+        synth = importlib.import_module("4dlangsplat_b200.synth")
+        fdist = importlib.import_module("4dlangsplat_b200.dist")
+        base = {"cfg3": "cfg2", "cfg5": "cfg5"}.get(name, name)
+        self.name, self.n_views = name, n_views
+        self.mine = fdist.shard_views(n_views, rank, world)
+        t = lambda a: torch.as_tensor(np.ascontiguousarray(a), device="cuda")
+        self.s = s = synth.scene(base)
+        self.views = {}
+        for v in self.mine:
+            sv = synth.scene(base, view_index=v, n_views=n_views)
+            dcol, dlang, _ = synth.upstream_grads(sv, n_views=n_views, seed=7 + v)
+            self.views[v] = dict(view=t(sv.viewmatrix), proj=t(sv.projmatrix), campos=t(sv.campos), dcol=t(dcol), dlang=t(dlang))
+        self.bg = t(s.bg)
+        self.params = dict(means3D=t(s.means3D), shs=t(s.shs), lang=t(s.language_feature), opac=t(s.opacities),
+                           scales=t(s.scales), rots=t(s.rotations))
+        self.cam_host, self.means_host, self.static_bytes = [], [], 0
+
+
+def run_train_ours(wl, steps, warmup, world):
+    fd = importlib.import_module("4dlangsplat_b200")
+    fdist = importlib.import_module("4dlangsplat_b200.dist")
+    lib = fd._lib.load()
+    dgr, s = fd.diff_gaussian_rasterization, wl.s
+    p = {k: v.clone().requires_grad_(True) for k, v in wl.params.items()}
+    means2D = torch.zeros_like(p["means3D"], requires_grad=True)
+    leaves = list(p.values()) + [means2D]
+    bucket = fdist.GradBucket(leaves)
+    Rs = []
+
+    def render(v):
+        c = wl.views[v]
+        rs = dgr.GaussianRasterizationSettings(s.H, s.W, s.tanfovx, s.tanfovy, wl.bg, 1.0, c["view"], c["proj"],
+                                               s.sh_degree, c["campos"], False, False, True)
+        return dgr.GaussianRasterizer(rs)(means3D=p["means3D"], means2D=means2D, opacities=p["opac"], shs=p["shs"],
+                                          language_feature_precomp=p["lang"], scales=p["scales"], rotations=p["rots"])
+
+    def loss_of(v, out):  # d(loss)/d(image) = the masked-L1-like sign pattern of synth.upstream_grads
+        c = wl.views[v]
+        return ((out[0] * c["dcol"]).sum() + (out[1] * c["dlang"]).sum()) * wl.n_views
+
+    def step():
+        for t in leaves:
+            t.grad = None
+        loss, nbytes = fdist.sharded_step(render, loss_of, wl.n_views, bucket)
+        return loss, nbytes
+
+    for _ in range(warmup):
+        step()
+    barrier(world)
+    launches0 = lib.fdls_kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        loss, nbytes = step()
+    e1.record()
+    barrier(world)
+    launches = lib.fdls_kernel_launches() - launches0
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    # stage split of one more (untimed) iteration, for the roofline line
+    fwd_ev, bwd_ev = EventPool(fd._lib.FDLS_FWD_EVENTS, 1), EventPool(fd._lib.FDLS_BWD_EVENTS, 1)
+    fd._C.profile["fwd"], fd._C.profile["bwd"] = fwd_ev.arrays[0], bwd_ev.arrays[0]
+    for t in leaves:
+        t.grad = None
+    if wl.mine:
+        v = wl.mine[0]
+        loss_of(v, render(v)).backward()
+    fd._C.profile["fwd"] = fd._C.profile["bwd"] = None
+    torch.cuda.synchronize()
+    st = fd._C._dev_state(torch.device("cuda", torch.cuda.current_device()))
+    R = st["last_R"] or 0
+    # e2e: same step, camera + upstream image gradients arrive from pinned host memory, the loss is read back
+    host = {v: {k: x.cpu().pin_memory() for k, x in c.items()} for v, c in wl.views.items()}
+    h2d = sum(x.numel() * 4 for c in host.values() for x in c.values())
+
+    def e2e_step():
+        for v, c in host.items():
+            wl.views[v] = {k: x.to("cuda", non_blocking=True) for k, x in c.items()}
+        loss, _ = step()
+        return float(loss)  # D2H read of the loss
+
+    for _ in range(max(1, warmup)):
+        e2e_step()
+    barrier(world)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    barrier(world)
+    e2e_s = max_over_ranks(t1 - t0, world)
+    V = int((torch.as_tensor(0)).item())
+    return dict(ms=ms, n_frames=steps, stage_ms=fwd_ev.stage_ms(1), bwd_stage_ms=bwd_ev.stage_ms(1), R=float(R), V=V,
+                launches=int(launches), e2e_s=e2e_s, h2d=h2d, d2h=4, allreduce_bytes=nbytes)
+
+
+def run_train_reference(wl, steps, warmup, world):
+    """The unmodified reference CUDA rasterizer, forward + backward over all B views on ONE GPU, with the fills its
+    torch glue performs (rasterize_points.cu:70-78,169-192)."""
+    import refcuda
+    from types import SimpleNamespace
+    s = wl.s
+    ref = refcuda.Ref(s.F)
+    P, M = s.P, s.shs.shape[1]
+    f32 = dict(dtype=torch.float32, device="cuda")
+    p = wl.params
+    color, lang, depth = torch.empty((3, s.H, s.W), **f32), torch.empty((s.F, s.H, s.W), **f32), torch.empty((1, s.H, s.W), **f32)
+    radii = torch.empty(P, dtype=torch.int32, device="cuda")
+    ddepth = torch.zeros((1, s.H, s.W), **f32)
+    acc = None
+
+    def step():
+        nonlocal acc
+        acc = None
+        for v in wl.mine:
+            c = wl.views[v]
+            color.zero_(); lang.zero_(); depth.zero_(); radii.zero_()
+            R = ref.forward_raw(P, s.sh_degree, M, s.W, s.H, wl.bg, p["means3D"], p["shs"], p["lang"], p["opac"],
+                                p["scales"], p["rots"], c["view"], c["proj"], c["campos"], s.tanfovx, s.tanfovy, color,
+                                lang, depth, radii)
+            z = lambda *shape: torch.zeros(shape, **f32)
+            g = SimpleNamespace(means2D=z(P, 3), conic=z(P, 4), opacity=z(P, 1), colors=z(P, 3), lang=z(P, s.F),
+                                depths=z(P), means3D=z(P, 3), cov3D=z(P, 6), sh=z(P, M, 3), scales=z(P, 3), rots=z(P, 4))
+            ref.backward_raw(P, s.sh_degree, M, R, s.W, s.H, wl.bg, p["means3D"], p["shs"], p["lang"], p["scales"],
+                             p["rots"], c["view"], c["proj"], c["campos"], s.tanfovx, s.tanfovy, radii, c["dcol"],
+                             c["dlang"], ddepth, g)
+            # autograd accumulates the views' gradients (train.py:339)
+            cur = [g.means3D, g.means2D, g.sh, g.lang, g.opacity, g.scales, g.rots]
+            acc = cur if acc is None else [a.add_(b) for a, b in zip(acc, cur)]
+        return R
+
+    for _ in range(warmup):
+        step()
+    barrier(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        R = step()
+    e1.record()
+    barrier(world)
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    host = {v: {k: x.cpu().pin_memory() for k, x in c.items()} for v, c in wl.views.items()}
+    h2d = sum(x.numel() * 4 for c in host.values() for x in c.values())
+
+    def e2e_step():
+        for v, c in host.items():
+            wl.views[v] = {k: x.to("cuda", non_blocking=True) for k, x in c.items()}
+        step()
+        return float(acc[0][0, 0])
+
+    for _ in range(max(1, warmup)):
+        e2e_step()
+    barrier(world)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    e2e_s = max_over_ranks(t1 - t0, world)
+    return dict(ms=ms, n_frames=steps, stage_ms=None, R=float(R), V=0, launches=0, e2e_s=e2e_s, h2d=h2d, d2h=4)
+
+
 def cpu_baseline(wl, frames=1):
     """CPU restatement (oracle/raster_oracle.cpp, OpenMP over all host cores) of the same forward on a bounded sample."""
     import oracle as orc
@@ -309,6 +480,57 @@ def stage_bytes(P, V, R, HW, T, F):
             "tile_ranges": 8 * R + 8 * T, "render": (44 + 4 * F) * R + (24 + 4 * F) * HW}
 
 
+def main_train(a, rank, world, local, warmup):
+    """BASELINE.json configs[2]: training step (rasterizer fwd+bwd) over a batch of views sharded over the ranks,
+    per-Gaussian gradients all-reduced once per iteration.  The batch is fixed => strong scaling."""
+    name = a.workload if a.workload != "cfg2" else "cfg3"
+    wl = TrainWorkload(name, rank, world)
+    s = wl.s
+    sampler = ClockSampler(local)
+    sampler.start()
+    r = (run_train_ours if a.impl == "ours" else run_train_reference)(wl, a.steps, warmup, world)
+    clocks = sampler.result()
+    value = a.steps / (r["ms"] * 1e-3)
+    line = {
+        "metric": "train_iters_per_s", "value": round(value, 3), "unit": "iters/s", "n_gpus": world, "steps": a.steps,
+        "warmup": warmup, "ms_per_step": round(r["ms"] / a.steps, 4), "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "%s: %d Gaussians, %dx%d, F=%d, rasterizer forward+backward, batch of %d views "
+                               "(deformation network out of scope, SURVEY 8f N1)" % (name, s.P, s.W, s.H, s.F, wl.n_views),
+                   "views_per_rank": len(wl.mine), "instances_per_view": round(r["R"]),
+                   "sharding": "views round-robin over ranks; one flat fp32 all-reduce of the leaf gradients per step",
+                   "l2": "per-view working set (records 19 MB + instance lists + 5 images) is re-streamed for every view; "
+                         "4 views x (SH 58 MB + gradient outputs 90 MB) exceed the 126 MB L2 between reuses"},
+        "clocks": clocks,
+        "e2e": {"value": round(a.steps / r["e2e_s"], 3), "unit": "iters/s", "h2d_bytes_per_step": r["h2d"],
+                "d2h_bytes_per_step": r["d2h"]},
+        "gpu_launches": r["launches"],
+    }
+    if a.impl == "ours":
+        pk, pk_kind = peaks()
+        HW = s.W * s.H
+        bwd = [float(x) for x in r["bwd_stage_ms"]]  # zero-fill, compositor bwd, preprocess bwd
+        bytes_rb = (44 + 4 * s.F) * r["R"] + (24 + 4 * s.F) * HW + (48 + 4 * s.F) * s.P
+        ach = bytes_rb / (bwd[1] * 1e-3) / 1e9 if bwd[1] > 0 else 0.0
+        line["roofline"] = {"bound": "hbm", "kernel": "render_bwd", "achieved": round(ach, 1), "peak": pk["hbm_gbs"],
+                            "unit": "GB/s", "frac": round(ach / pk["hbm_gbs"], 4), "traffic": None,
+                            "peak_source": pk_kind, "algorithmic_bytes_per_launch": int(bytes_rb),
+                            "avg_launch_ms": round(bwd[1], 4)}
+        names = ["preprocess", "scan", "duplicate", "sort", "tile_ranges", "render"]
+        line["stages_ms"] = dict(zip(names, [round(float(x), 4) for x in r["stage_ms"]]))
+        line["stages_ms"].update({"bwd_zero": round(bwd[0], 4), "render_bwd": round(bwd[1], 4), "preprocess_bwd": round(bwd[2], 4)})
+        line["allreduce_bytes_per_step"] = r["allreduce_bytes"]
+    else:
+        line["impl"] = "reference"
+        line["cpu_baseline"] = {"value": line["value"], "unit": "iters/s", "cores": 1, "kind": "reference",
+                                "sample": "reference CUDA rasterizer fwd+bwd (oracle/_ref) on one B200, all %d views" % wl.n_views}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -317,11 +539,20 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--mode", default="render", choices=["render", "train"],
+                    help="render: forward sweep (headline, cfg2); train: fwd+bwd over a batch of 4 views (cfg3)")
     a = ap.parse_args()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    if a.impl == "reference" and int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        # the reference has no multi-GPU path: rank 0 alone runs its single-GPU loop, the other ranks exit without work
+        if int(os.environ.get("RANK", "0")) != 0:
+            return
+        os.environ["WORLD_SIZE"], os.environ["LOCAL_RANK"] = "1", "0"
     rank, world, local = dist_setup(a.gpus)
     warmup = max(3, a.warmup)
+    if a.mode == "train" or a.workload in ("cfg3",):
+        return main_train(a, rank, world, local, warmup)
     wl = Workload(a.workload, rank, world)
     s = wl.s
     sampler = ClockSampler(local)
