@@ -35,7 +35,7 @@ int sort_run(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* val
              const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, bool have_hist,
              cudaStream_t st);
 // binning_partition.cu
-bool partition_supported(int T);
+bool partition_supported(int gx, int gy);
 size_t partition_table_bytes(int P, int T);
 cudaError_t launch_partition_count(int P, int gx, int gy, const uint32_t* order, const int* radii, const float4* rec,
                                    uint32_t* table, uint32_t* tile_total, uint32_t* tile_start, uint2* ranges,
@@ -84,7 +84,7 @@ static void compute_layout(int P, int W, int H, long long capacity, FdlsLayout* 
   L->scan_scratch = o;  o += scan_scratch_bytes((int)Pz);
   L->depth_order = o;   o += align_up(Pz * 4);
   L->depth_scratch = o; o += align_up(Pz * 8) * 2 + align_up(Pz * 4) + sort_scratch_bytes((long long)Pz);
-  L->part_table = o;    o += partition_supported((int)tiles) ? partition_table_bytes((int)Pz, (int)tiles) : 256;
+  L->part_table = o;    o += partition_supported(gx, gy) ? partition_table_bytes((int)Pz, (int)tiles) : 256;
   S->geom_bytes = o;
   o = 0;
   L->final_T = o;          o += align_up(HW * 4);
@@ -192,7 +192,7 @@ FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
   char* dscr = g + L.depth_scratch + 2 * align_up(Pz * 8) + align_up(Pz * 4);
   uint32_t* order = (uint32_t*)(g + L.depth_order);
   const int gx1 = cdiv(a->W, TILE), gy1 = cdiv(a->H, TILE);
-  const bool partition = a->binning_algo == 0 && partition_supported(gx1 * gy1);
+  const bool partition = a->binning_algo == 0 && partition_supported(gx1, gy1);
   if (launch_preprocess_fwd(a, vp, (float4*)(g + L.rec), (uint32_t*)(g + L.tiles_touched), (uint8_t*)(g + L.clamped),
                             dk_a, order, st) != cudaSuccess)
     return FDLS_ECUDA;
@@ -245,7 +245,7 @@ FDLS_API int fdls_bin_and_render(const FdlsFwdArgs* a, void* stream) {
   if (a->num_rendered_hint >= 0 && a->num_rendered_hint < n_grid) n_grid = a->num_rendered_hint;
   uint2* ranges = (uint2*)(im + L.ranges);
   const uint32_t* point_list = nullptr;
-  if (a->binning_algo == 0 && partition_supported(gx * gy)) {
+  if (a->binning_algo == 0 && partition_supported(gx, gy)) {
     if (n_grid > 0) {
       // (2b) binning_partition.cu kernel B: every instance goes straight to its final slot
       if (launch_partition_scatter(a->P, gx, gy, (const uint32_t*)(g + L.depth_order), a->radii,

@@ -10,7 +10,9 @@
 // sorted keys / values / ranges are bit-identical.
 //
 // Kernels (A and B walk the depth-ordered Gaussians warp-cooperatively: one Gaussian at a time per warp, its tiles
-// spread over the 32 lanes; all ranking happens in per-warp shared-memory counters -- no global atomics):
+// spread over the 32 lanes; all ranking happens in per-warp shared-memory counters -- no global atomics).
+// (A variant that flattens the instances of 32 Gaussians over the lanes and ranks with match.any was measured 2.4x
+// SLOWER on B200 -- match.any serialises over distinct values -- and was dropped.)
 //   A  part_count    per CTA chunk: instances per tile                         -> table[cta][tile]
 //   S1 part_colscan  exclusive scan of table over CTAs (per tile), tile totals -> table (in place), tile_total
 //   S2 part_tilescan exclusive scan over tiles                                 -> tile_start, ranges, R
@@ -225,7 +227,7 @@ part_tilescan_kernel(int T, const uint32_t* __restrict__ tile_total, uint32_t* _
   }
 }
 
-bool partition_supported(int T) { return T <= PT_MAX_TILES; }
+bool partition_supported(int gx, int gy) { return gx < 1024 && gy < 1024 && gx * gy <= PT_MAX_TILES; }
 int partition_ctas(int P) { return cdiv(P < 1 ? 1 : P, pt_chunk(P)); }
 size_t partition_table_bytes(int P, int T) { return align_up((size_t)partition_ctas(P) * T * sizeof(uint32_t)); }
 
