@@ -13,7 +13,8 @@ static inline void rec(void** ev, int i, cudaStream_t st) {
 }
 // preprocess_fwd.cu
 cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, float4* rec, uint32_t* tiles_touched,
-                                  uint8_t* clamped, uint64_t* depth_keys, uint32_t* depth_vals, cudaStream_t st);
+                                  uint8_t* clamped, uint64_t* depth_keys, uint32_t* depth_vals, uint32_t* depth_hist,
+                                  cudaStream_t st);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 // binning.cu
 size_t scan_scratch_bytes(int P);
@@ -43,7 +44,7 @@ cudaError_t launch_partition_count(int P, int gx, int gy, const uint32_t* order,
 cudaError_t launch_partition_scatter(int P, int gx, int gy, const uint32_t* order, const int* radii, const float4* rec,
                                      const uint32_t* table, const uint32_t* tile_total, uint32_t* tile_start,
                                      uint2* ranges, uint32_t* num_rendered, uint32_t* point_list, uint64_t* keys,
-                                     long long capacity, cudaStream_t st);
+                                     long long capacity, bool rescan, cudaStream_t st);
 // render_fwd.cu / render_bwd.cu / preprocess_bwd.cu
 cudaError_t launch_render_fwd(int F, const uint2* ranges, const uint32_t* point_list, const float4* rec, int W, int H,
                               int gx, int gy, const float* bg, float* final_T, uint32_t* n_contrib, uint32_t* tile_max,
@@ -193,12 +194,16 @@ FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
   uint32_t* order = (uint32_t*)(g + L.depth_order);
   const int gx1 = cdiv(a->W, TILE), gy1 = cdiv(a->H, TILE);
   const bool partition = a->binning_algo == 0 && partition_supported(gx1, gy1);
+  // the depth sort's digit histograms are accumulated by the preprocess kernel itself (no separate pass over the keys)
+  const size_t dscr_bytes = sort_scratch_bytes((long long)Pz);
+  rc = sort_prepare(a->P, 0, 32, dscr, dscr_bytes, st);
+  if (rc < 0) return rc;
   if (launch_preprocess_fwd(a, vp, (float4*)(g + L.rec), (uint32_t*)(g + L.tiles_touched), (uint8_t*)(g + L.clamped),
-                            dk_a, order, st) != cudaSuccess)
+                            dk_a, order, a->P > 0 ? sort_hist(dscr) : nullptr, st) != cudaSuccess)
     return FDLS_ECUDA;
   rec(a->stage_events, 1, st);
   // (1) order the GAUSSIANS by depth bits (stable, P elements) ...
-  int sel = sort_pairs(dk_a, dk_b, order, dv_b, a->P, nullptr, 0, 32, dscr, sort_scratch_bytes((long long)Pz), st);
+  int sel = sort_run(dk_a, dk_b, order, dv_b, a->P, nullptr, 0, 32, dscr, dscr_bytes, true, st);
   if (sel < 0) return sel;
   if (sel != 0) return FDLS_ECUDA;  // 4 passes: result is back in the `a` buffers by construction
   if (partition) {
@@ -252,7 +257,8 @@ FDLS_API int fdls_bin_and_render(const FdlsFwdArgs* a, void* stream) {
                                    (const float4*)(g + L.rec), (const uint32_t*)(g + L.part_table),
                                    (const uint32_t*)(im + L.tile_cursor), (uint32_t*)(im + L.tile_start), ranges, nr,
                                    (uint32_t*)(b + L.vals), (uint64_t*)(b + L.keys),
-                                   n_grid < a->capacity ? n_grid : a->capacity, st) != cudaSuccess)
+                                   n_grid < a->capacity ? n_grid : a->capacity, /*rescan=*/a->num_rendered_hint >= 0,
+                                   st) != cudaSuccess)
         return FDLS_ECUDA;
       point_list = (const uint32_t*)(b + L.vals);
     } else {

@@ -259,7 +259,7 @@ cudaError_t launch_partition_count(int P, int gx, int gy, const uint32_t* order,
 cudaError_t launch_partition_scatter(int P, int gx, int gy, const uint32_t* order, const int* radii, const float4* rec,
                                      const uint32_t* table, const uint32_t* tile_total, uint32_t* tile_start,
                                      uint2* ranges, uint32_t* num_rendered, uint32_t* point_list, uint64_t* keys,
-                                     long long capacity, cudaStream_t st) {
+                                     long long capacity, bool rescan, cudaStream_t st) {
   const int T = gx * gy, chunk = pt_chunk(P), ctas = partition_ctas(P);
   static size_t attr_b = 0;
   const size_t sb = pt_smem_bytes(T, true);
@@ -269,8 +269,10 @@ cudaError_t launch_partition_scatter(int P, int gx, int gy, const uint32_t* orde
     attr_b = sb;
   }
   // ranges depend on the capacity of THIS call's workspace (clipping): recompute them (one tiny CTA)
-  part_tilescan_kernel<<<1, 1024, 0, st>>>(T, tile_total, tile_start, ranges, num_rendered, capacity);
-  count_launch();
+  if (rescan) {
+    part_tilescan_kernel<<<1, 1024, 0, st>>>(T, tile_total, tile_start, ranges, num_rendered, capacity);
+    count_launch();
+  }
   part_scatter_kernel<<<ctas, PT_THREADS, sb, st>>>(P, T, chunk, order, radii, rec, gx, gy, table, tile_start,
                                                     point_list, keys, capacity);
   count_launch();

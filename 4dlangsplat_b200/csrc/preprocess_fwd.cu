@@ -90,19 +90,53 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
                       const float* __restrict__ colors_precomp, const float* __restrict__ lang, ViewParams vp,
                       int* __restrict__ radii, float4* __restrict__ rec, uint32_t* __restrict__ tiles_touched,
                       uint8_t* __restrict__ clamped, uint64_t* __restrict__ depth_keys,
-                      uint32_t* __restrict__ depth_vals, int prefiltered) {
+                      uint32_t* __restrict__ depth_vals, int prefiltered, uint32_t sh_magic,
+                      uint32_t* __restrict__ depth_hist) {
+  extern __shared__ float s_sh[];  // [256][3M+1] when SH are staged (sh_magic != 0), else empty
   __shared__ float s_view[16], s_proj[16], s_cam[3];
+  __shared__ uint32_t s_hist[4][256];  // digit histograms of the depth keys, for the depth sort that follows
+  if (depth_hist != nullptr)
+    for (int i = threadIdx.x; i < 1024; i += 256) (&s_hist[0][0])[i] = 0;
   if (threadIdx.x < 16) s_view[threadIdx.x] = vp.view[threadIdx.x];
   else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = vp.proj[threadIdx.x - 16];
   else if (threadIdx.x < 35) s_cam[threadIdx.x - 32] = vp.campos[threadIdx.x - 32];
   __syncthreads();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
+  const int sh_stride = 3 * M + 1;
+  if (sh_magic != 0) {
+    // Coalesced staging of this warp's 32 x (M,3) SH block: the direct per-thread reads are 192-byte strided
+    // (forward.cu:20-71 reads sh[idx*max_coeffs + i]) and waste most of every sector; here each warp streams its
+    // contiguous 32*3M floats with 16-byte loads and re-reads them conflict-free (row stride 3M+1 words).
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g0 = blockIdx.x * 256 + warp * 32;
+    if (g0 < P) {
+      const int n_fl = min(32, P - g0) * 3 * M;
+      const float* src = shs + (size_t)g0 * 3 * M;
+      float* dst = s_sh + warp * 32 * sh_stride;
+      for (int e0 = 4 * lane; e0 < n_fl; e0 += 128) {
+        float v[4];
+        if (e0 + 3 < n_fl) {
+          const float4 q = *reinterpret_cast<const float4*>(src + e0);
+          v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) v[k] = e0 + k < n_fl ? src[e0 + k] : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint32_t e = e0 + k;
+          const uint32_t g = __umulhi(e, sh_magic);  // e / (3M)
+          if ((int)e < n_fl) dst[g * sh_stride + (e - g * 3 * M)] = v[k];
+        }
+      }
+    }
+    __syncwarp();
+  }
 
   int out_radius = 0;
   uint32_t out_tiles = 0;
   uint32_t out_depth_bits = 0xffffffffu;  // culled Gaussians sort behind every visible one (depth > 0.2 => sign bit 0)
-  do {
+  if (idx < P) do {
     const float3 p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
     // in_frustum (auxiliary.h:139-164): only the near-plane test is live.
     const float3 p_view = xform4x3(p_orig, s_view);
@@ -149,7 +183,8 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
       V3 cam = {s_cam[0], s_cam[1], s_cam[2]};
       V3 dir = pos - cam;
       dir = dir / sqrt(dot3(dir, dir));
-      rgb = sh_to_rgb(D, shs + (size_t)idx * M * 3, dir, cl);
+      rgb = sh_magic != 0 ? sh_to_rgb(D, s_sh + threadIdx.x * sh_stride, dir, cl)
+                          : sh_to_rgb(D, shs + (size_t)idx * M * 3, dir, cl);
     } else {
       rgb = {colors_precomp[3 * idx], colors_precomp[3 * idx + 1], colors_precomp[3 * idx + 2]};
     }
@@ -168,11 +203,25 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
     out_tiles = (rect_max.y - rect_min.y) * (rect_max.x - rect_min.x);
     out_depth_bits = __float_as_uint(p_view.z);
   } while (0);
-  radii[idx] = out_radius;
-  tiles_touched[idx] = out_tiles;
-  if (depth_keys != nullptr) {  // input of the P-element depth sort (onesweep binning only, api.cu)
-    depth_keys[idx] = out_depth_bits;
-    depth_vals[idx] = idx;
+  if (idx < P) {
+    radii[idx] = out_radius;
+    tiles_touched[idx] = out_tiles;
+    if (depth_keys != nullptr) {  // input of the P-element depth sort (api.cu)
+      depth_keys[idx] = out_depth_bits;
+      depth_vals[idx] = idx;
+    }
+  }
+  if (depth_hist != nullptr) {  // replaces the sort's own histogram pass over the keys (radix_sort.cu)
+    __syncthreads();
+    if (idx < P) {
+#pragma unroll
+      for (int p = 0; p < 4; ++p) atomicAdd(&s_hist[p][(out_depth_bits >> (8 * p)) & 255u], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 1024; i += 256) {
+      const uint32_t c = (&s_hist[0][0])[i];
+      if (c) atomicAdd(&depth_hist[i], c);
+    }
   }
 }
 
@@ -187,12 +236,23 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
 }
 
 cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, float4* rec, uint32_t* tiles_touched,
-                                  uint8_t* clamped, uint64_t* depth_keys, uint32_t* depth_vals, cudaStream_t st) {
+                                  uint8_t* clamped, uint64_t* depth_keys, uint32_t* depth_vals, uint32_t* depth_hist,
+                                  cudaStream_t st) {
   if (a->P == 0) return cudaSuccess;
-  preprocess_fwd_kernel<<<cdiv(a->P, 256), 256, 0, st>>>(
+  // SH staging needs 256*(3M+1) floats of shared memory; M <= 16 (degree 3) -> 50 KB
+  const bool stage = a->shs != nullptr && a->colors_precomp == nullptr && a->M >= 1 && a->M <= 16;
+  const size_t smem = stage ? (size_t)256 * (3 * a->M + 1) * sizeof(float) : 0;
+  const uint32_t magic = stage ? (uint32_t)(0xffffffffu / (uint32_t)(3 * a->M) + 1u) : 0u;
+  static size_t attr = 0;
+  if (smem > attr) {
+    cudaError_t e = cudaFuncSetAttribute(preprocess_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    attr = smem;
+  }
+  preprocess_fwd_kernel<<<cdiv(a->P, 256), 256, smem, st>>>(
       a->P, a->D, a->M, a->F, a->means3D, a->scales, a->rotations, a->opacities, a->shs, a->cov3D_precomp,
       a->colors_precomp, a->language_feature, vp, a->radii, rec, tiles_touched, clamped, depth_keys, depth_vals,
-      a->prefiltered); count_launch();
+      a->prefiltered, magic, depth_hist); count_launch();
   return cudaGetLastError();
 }
 

@@ -52,6 +52,19 @@ __device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v) {
   asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// Lanes holding the same 9-bit digit (bin 256 = padding).  Nine ballots: a fixed ~30-instruction cost, where the
+// hardware match.any serialises over the distinct values in the warp (measured slower on B200 for 8-bit digits).
+__device__ __forceinline__ uint32_t rs_match9(uint32_t d) {
+  uint32_t peers = FULL;
+#pragma unroll
+  for (int b = 0; b < 9; ++b) {
+    const bool bit = (d >> b) & 1u;
+    const uint32_t bal = __ballot_sync(FULL, bit);
+    peers &= bit ? bal : ~bal;
+  }
+  return peers;
+}
+
 __device__ __forceinline__ uint32_t rs_warp_incl(uint32_t v, int lane) {
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
@@ -100,8 +113,7 @@ rs_histogram_kernel(const uint64_t* __restrict__ keys, long long n_max, const ui
         const int shift = begin_bit + p * 8;
         const uint32_t mask = (1u << min(8, end_bit - shift)) - 1;
         const uint32_t d = (uint32_t)(key >> shift) & mask;
-        const unsigned peers = __match_any_sync(act, d);
-        if ((peers & lt) == 0) atomicAdd(&s_hist[p][d], __popc(peers));
+        atomicAdd(&s_hist[p][d], 1u);
       }
     }
   }
@@ -146,7 +158,7 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ 
   for (int i = 0; i < IPT; ++i) {
     const int li = warp_base + i * 32 + lane;
     const uint32_t d = (li < valid_count) ? ((uint32_t)(key[i] >> shift) & mask) : RS_BINS;  // bin 256 = padding
-    peers[i] = __match_any_sync(FULL, d);
+    peers[i] = rs_match9(d);
   }
   // ---- rank inside the warp: running per-digit counters live in this warp's private shared histogram
   const uint32_t lt = lanemask_lt();

@@ -111,7 +111,9 @@ typedef struct FdlsFwdArgs {
   int64_t capacity; /* instances the binning workspace was sized for */
   /* optional pinned-host uint32[2]: asynchronously receives {R, overflow}; valid after the stream reaches that point */
   uint32_t* num_rendered_host;
-  /* host-known instance count for grid sizing in fdls_bin_and_render; <0 = unknown, size grids by capacity */
+  /* host-known instance count for grid sizing in fdls_bin_and_render; <0 = unknown, size grids by capacity.
+   * <0 also states that `capacity` is the one fdls_preprocess ran with (its clipped tile ranges are reused);
+   * pass the exact R (>= 0) whenever stage 2 runs with a different capacity than stage 1. */
   int64_t num_rendered_hint;
   /* optional: array of FDLS_FWD_EVENTS cudaEvent_t handles recorded on the stream between stages
    * [0] start, [1] preprocess, [2] scan, [3] duplicate, [4] sort, [5] tile ranges, [6] compositor; null = off */
