@@ -298,3 +298,53 @@ def test_backward_accuracy_vs_float64(synth, name):
         assert e_mine.max() <= 4.0 * e_ref.max() + 1e-5 * gmax, report[-1]  # 1e-5 of the scale: 10x inside the 1e-4 contract
         assert e_mine.mean() <= 2.0 * e_ref.mean() + 1e-7 * gmax, report[-1]
     print("\n".join(report))
+
+
+@pytest.mark.parametrize("name", ["cfg1", "cfg2", "cfg2_f6", "cfg4", "cfg5"])
+def test_full_size_configs_bit_exact(synth, name):
+    """BASELINE.json's full-size shapes (100k/800x800, 300k/536x960 F=3 and F=6, 600k/1352x1014, 3M/1920x1080 F=6):
+    forward against the reference CUDA build on the same B200 -- R, sorted values, tile ranges and contributor counts
+    bit-exact, images 1e-5 -- plus size-independent properties of the binning (every tile's list is sorted by depth
+    bits then Gaussian index; ranges tile the instance list without gaps)."""
+    s = synth.scene(name)
+    _need_ref(s.F)
+    r = refcuda.Ref(s.F).forward(s)
+    o = helpers.run_forward(s)
+    assert o.R == r.R
+    _assert_same(o.radii, r.radii, "radii")
+    _assert_same(o.point_list, r.point_list, "sorted values")
+    _assert_same(o.keys, r.keys, "sorted keys")
+    _assert_same(o.ranges, r.ranges, "tile ranges")
+    _assert_same(o.n_contrib, r.n_contrib, "n_contrib")
+    _assert_same(o.final_T, r.final_T, "final_T")
+    _assert_close(o.color, r.color, IMG_RTOL, "color")
+    _assert_close(o.lang, r.lang, IMG_RTOL, "language feature")
+    _assert_close(o.depth, r.depth, IMG_RTOL, "depth")
+    # properties that hold at any size
+    k = o.keys
+    assert bool((k[1:] >= k[:-1]).all()), "keys not sorted"
+    same = k[1:] == k[:-1]
+    pl = o.point_list.long()
+    assert bool((pl[1:][same] > pl[:-1][same]).all()), "ties not in ascending Gaussian index (stability)"
+    rg = o.ranges.long()
+    nonempty = rg[:, 1] > rg[:, 0]
+    assert int((rg[nonempty, 1] - rg[nonempty, 0]).sum()) == o.R
+    tiles = (k >> 32)
+    starts = rg[nonempty, 0]
+    assert bool((tiles[starts] == torch.nonzero(nonempty).flatten()).all())
+
+
+@pytest.mark.parametrize("name", ["cfg2", "cfg5"])
+def test_full_size_backward(synth, name):
+    s = synth.scene(name)
+    _need_ref(s.F)
+    dcol, dlang, ddepth = synth.upstream_grads(s)
+    ref = refcuda.Ref(s.F)
+    ref.forward(s)
+    gr = ref.backward(dcol, dlang, ddepth)
+    o = helpers.run_forward(s)
+    g = helpers.run_backward(s, o, dcol, dlang, ddepth)
+    for nm, a, b in (("means2D", g.means2D, gr.means2D), ("colors", g.colors, gr.colors), ("lang", g.lang, gr.lang),
+                     ("opacity", g.opacity, gr.opacity), ("means3D", g.means3D, gr.means3D), ("sh", g.sh, gr.sh),
+                     ("scales", g.scales, gr.scales), ("rots", g.rots, gr.rots)):
+        _assert_grad(a, b, "dL_d" + nm)
