@@ -24,9 +24,9 @@ class FdlsWorkspaceSizes(C.Structure):
 class FdlsLayout(C.Structure):
     _fields_ = [(n, C.c_size_t) for n in (
         "rec", "tiles_touched", "point_offsets", "clamped", "num_rendered", "scan_scratch",
-        "depth_order", "depth_scratch", "part_table",
+        "depth_order", "depth_scratch",
         "final_T", "n_contrib", "ranges", "tile_max_contrib", "tile_start", "tile_cursor",
-        "keys_alt", "keys", "vals_alt", "vals", "sort_scratch")]
+        "keys_alt", "keys", "vals_alt", "vals", "sort_scratch", "part_table")]
 
 
 class FdlsFwdArgs(C.Structure):

@@ -37,14 +37,11 @@ int sort_run(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* val
              cudaStream_t st);
 // binning_partition.cu
 bool partition_supported(int gx, int gy);
-size_t partition_table_bytes(int P, int T);
-cudaError_t launch_partition_count(int P, int gx, int gy, const uint32_t* order, const int* radii, const float4* rec,
-                                   uint32_t* table, uint32_t* tile_total, uint32_t* tile_start, uint2* ranges,
-                                   uint32_t* num_rendered, long long capacity, cudaStream_t st);
-cudaError_t launch_partition_scatter(int P, int gx, int gy, const uint32_t* order, const int* radii, const float4* rec,
-                                     const uint32_t* table, const uint32_t* tile_total, uint32_t* tile_start,
-                                     uint2* ranges, uint32_t* num_rendered, uint32_t* point_list, uint64_t* keys,
-                                     long long capacity, bool rescan, cudaStream_t st);
+size_t partition_table_bytes(long long capacity, int P, int T);
+cudaError_t launch_partition(int P, int gx, int gy, const uint32_t* order, const uint32_t* offsets, const int* radii,
+                             const float4* rec, uint32_t* table, uint32_t* tile_total, uint32_t* tile_start,
+                             uint2* ranges, uint32_t* num_rendered, uint32_t* point_list, uint64_t* keys,
+                             const uint32_t* depth_hist, long long capacity, cudaStream_t st);
 // render_fwd.cu / render_bwd.cu / preprocess_bwd.cu
 cudaError_t launch_render_fwd(int F, const uint2* ranges, const uint32_t* point_list, const float4* rec, int W, int H,
                               int gx, int gy, const float* bg, float* final_T, uint32_t* n_contrib, uint32_t* tile_max,
@@ -85,7 +82,6 @@ static void compute_layout(int P, int W, int H, long long capacity, FdlsLayout* 
   L->scan_scratch = o;  o += scan_scratch_bytes((int)Pz);
   L->depth_order = o;   o += align_up(Pz * 4);
   L->depth_scratch = o; o += align_up(Pz * 8) * 2 + align_up(Pz * 4) + sort_scratch_bytes((long long)Pz);
-  L->part_table = o;    o += partition_supported(gx, gy) ? partition_table_bytes((int)Pz, (int)tiles) : 256;
   S->geom_bytes = o;
   o = 0;
   L->final_T = o;          o += align_up(HW * 4);
@@ -101,6 +97,7 @@ static void compute_layout(int P, int W, int H, long long capacity, FdlsLayout* 
   L->keys = o;         o += align_up(cap * 8);
   L->keys_alt = o;     o += align_up(cap * 8);
   L->sort_scratch = o; o += sort_scratch_bytes((long long)cap);
+  L->part_table = o;   o += partition_supported(gx, gy) ? partition_table_bytes((long long)cap, (int)Pz, (int)tiles) : 256;
   S->binning_bytes = o;
 }
 
@@ -192,8 +189,6 @@ FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
   uint32_t* dv_b = (uint32_t*)(g + L.depth_scratch + 2 * align_up(Pz * 8));
   char* dscr = g + L.depth_scratch + 2 * align_up(Pz * 8) + align_up(Pz * 4);
   uint32_t* order = (uint32_t*)(g + L.depth_order);
-  const int gx1 = cdiv(a->W, TILE), gy1 = cdiv(a->H, TILE);
-  const bool partition = a->binning_algo == 0 && partition_supported(gx1, gy1);
   // the depth sort's digit histograms are accumulated by the preprocess kernel itself (no separate pass over the keys)
   const size_t dscr_bytes = sort_scratch_bytes((long long)Pz);
   rc = sort_prepare(a->P, 0, 32, dscr, dscr_bytes, st);
@@ -206,20 +201,6 @@ FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
   int sel = sort_run(dk_a, dk_b, order, dv_b, a->P, nullptr, 0, 32, dscr, dscr_bytes, true, st);
   if (sel < 0) return sel;
   if (sel != 0) return FDLS_ECUDA;  // 4 passes: result is back in the `a` buffers by construction
-  if (partition) {
-    // (2a) binning_partition.cu kernels A, S1, S2: per-tile instance counts -> tile starts, ranges, R
-    char* im = (char*)a->img_ws;
-    if (launch_partition_count(a->P, gx1, gy1, order, a->radii, (const float4*)(g + L.rec),
-                               (uint32_t*)(g + L.part_table), (uint32_t*)(im + L.tile_cursor),
-                               (uint32_t*)(im + L.tile_start), (uint2*)(im + L.ranges), nr, a->capacity,
-                               st) != cudaSuccess)
-      return FDLS_ECUDA;
-    rec(a->stage_events, 2, st);
-    if (a->num_rendered_host &&
-        cudaMemcpyAsync(a->num_rendered_host, nr, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st) != cudaSuccess)
-      return FDLS_ECUDA;
-    return FDLS_OK;
-  }
   // (2) ... and scan the tile counts in that order, so instances are emitted depth-sorted
   if (launch_scan(a->P, (uint32_t*)(g + L.tiles_touched), order, (uint32_t*)(g + L.point_offsets),
                   (uint32_t*)(g + L.scan_scratch), nr, a->capacity, st) != cudaSuccess)
@@ -252,13 +233,16 @@ FDLS_API int fdls_bin_and_render(const FdlsFwdArgs* a, void* stream) {
   const uint32_t* point_list = nullptr;
   if (a->binning_algo == 0 && partition_supported(gx, gy)) {
     if (n_grid > 0) {
-      // (2b) binning_partition.cu kernel B: every instance goes straight to its final slot
-      if (launch_partition_scatter(a->P, gx, gy, (const uint32_t*)(g + L.depth_order), a->radii,
-                                   (const float4*)(g + L.rec), (const uint32_t*)(g + L.part_table),
-                                   (const uint32_t*)(im + L.tile_cursor), (uint32_t*)(im + L.tile_start), ranges, nr,
-                                   (uint32_t*)(b + L.vals), (uint64_t*)(b + L.keys),
-                                   n_grid < a->capacity ? n_grid : a->capacity, /*rescan=*/a->num_rendered_hint >= 0,
-                                   st) != cudaSuccess)
+      // digit histograms of the depth sort (top-byte bin 0xff = culled Gaussians), still in the geometry workspace
+      const size_t Pz2 = (size_t)(a->P < 1 ? 1 : a->P);
+      const uint32_t* depth_hist =
+          sort_hist(g + L.depth_scratch + 2 * align_up(Pz2 * 8) + align_up(Pz2 * 4));
+      // binning_partition.cu: count / scans / scatter -- every instance goes straight to its final sorted slot
+      if (launch_partition(a->P, gx, gy, (const uint32_t*)(g + L.depth_order), (const uint32_t*)(g + L.point_offsets),
+                           a->radii, (const float4*)(g + L.rec), (uint32_t*)(b + L.part_table),
+                           (uint32_t*)(im + L.tile_cursor), (uint32_t*)(im + L.tile_start), ranges, nr,
+                           (uint32_t*)(b + L.vals), (uint64_t*)(b + L.keys), depth_hist, a->capacity,
+                           st) != cudaSuccess)
         return FDLS_ECUDA;
       point_list = (const uint32_t*)(b + L.vals);
     } else {

@@ -27,10 +27,39 @@ constexpr int PT_THREADS = 256;
 constexpr int PT_WARPS = PT_THREADS / 32;
 constexpr int PT_MAX_TILES = 10240;  // 8 warps x 10240 x 2 B + 10240 x 4 B = 200 KB of shared memory
 
-__host__ __device__ inline int pt_chunk(int P) {  // Gaussians per CTA: keep <= ~1200 CTAs, multiple of 256
-  int ch = 512;
-  while ((long long)ch * 1200 < P) ch *= 2;
-  return ch;
+// Work is split by COST (instances + a per-Gaussian overhead), not by Gaussian count: in depth order the near
+// (= large on screen) Gaussians come first, so equal Gaussian counts per CTA would leave the first CTAs with most of
+// the instances, and equal instance counts would leave the last CTAs with most of the (tiny) Gaussians.  CTA c owns
+// the cost span [c*I, (c+1)*I) of the depth-ordered stream (I = ceil(total / ctas), read on the device), warp w an
+// eighth of it; a Gaussian whose instances straddle a boundary is shared (its tiles are distinct, so any split
+// keeps the per-tile order).
+// ctas: enough CTAs for the u16 per-tile counters to be safe, and -- unless that bound needs more -- at most one
+// resident wave of the scatter kernel (148 SMs x the CTAs its shared memory allows), so no partial second wave trails behind.
+constexpr int PT_SMS = 148;                 // B200
+constexpr size_t PT_SMEM_PER_SM = 227 * 1024;
+static size_t pt_smem_bytes(int T, bool scatter) {
+  const size_t words = (size_t)(T + 1) / 2;
+  return (PT_WARPS * words + (scatter ? (size_t)T + 1 : 0)) * sizeof(uint32_t);
+}
+static int pt_ctas(long long capacity, int P, int T) {
+  // total cost <= capacity + PT_C * P (PT_C = 32, see below).  A CTA span of cost c holds at most c / 33 Gaussians,
+  // which must stay below 65536 (u16 per-tile counters): c <= 2e6.  Target: ~16K cost units per CTA.
+  const long long cost = capacity + 32LL * P;
+  long long lo = (cost + 1999999) / 2000000, g = (cost + 16383) / 16384;
+  if (lo < 1) lo = 1;
+  long long per_sm = (long long)(PT_SMEM_PER_SM / (pt_smem_bytes(T, true) + 1024));
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 8) per_sm = 8;
+  const long long wave = per_sm * PT_SMS;
+  // ... but never spans above 64K cost units: CTAs that run together then work on neighbouring stretches of the
+  // stream and their 4-byte stores into a tile's list share sectors in L2 (measured: 2.5x faster scatter at R = 185M
+  // than one wave of long spans, whose stores each dirty a sector of their own)
+  const long long fine = (cost + 65535) / 65536;
+  if (lo < fine) lo = fine;
+  const long long hi = lo > wave ? lo : wave;
+  if (g < lo) g = lo;
+  if (g > hi) g = hi;
+  return (int)g;
 }
 
 // u16 counters packed two per 32-bit word; returns the previous value of counter t
@@ -43,31 +72,71 @@ __device__ __forceinline__ uint32_t cnt_get(const uint32_t* w, uint32_t t) {
   return (t & 1u) ? (v >> 16) : (v & 0xffffu);
 }
 
-// Walk this warp's slice [g_begin, g_end) of the depth-ordered Gaussian list, one Gaussian at a time in order.
+// Cost model of the walk: a Gaussian costs its instance count plus PT_C (shuffles, loop set-up and one mostly idle
+// inner iteration ~ one full 32-lane iteration).  Spans are equal in COST: W_incl(p) = offsets[p] + PT_C * (p + 1)
+// over the V visible Gaussians, which come first in depth order (culled ones carry the key 0xffffffff).
+constexpr uint32_t PT_C = 32;
+__device__ __forceinline__ unsigned long long w_incl(const uint32_t* __restrict__ offsets, int p) {
+  return (unsigned long long)offsets[p] + (unsigned long long)PT_C * (uint32_t)(p + 1);
+}
+
+// smallest position p in [0, V) with W_incl(p) > ws (ws < W_incl(V-1)); 32-ary search, one probe per lane per round
+__device__ __forceinline__ int first_pos_above(const uint32_t* __restrict__ offsets, int V, unsigned long long ws,
+                                               int lane) {
+  int lo = 0, hi = V;
+  while (hi - lo > 32) {
+    const int step = (hi - lo + 31) / 32;
+    const int p = min(lo + (lane + 1) * step, hi) - 1;
+    const uint32_t m = __ballot_sync(0xffffffffu, w_incl(offsets, p) > ws);
+    const int k = __ffs(m) - 1;  // lane 31 probes hi-1, which is above `ws` by the invariant
+    hi = min(lo + (k + 1) * step, hi);
+    lo = lo + k * step;
+  }
+  const uint32_t m = __ballot_sync(0xffffffffu, lo + lane < hi && w_incl(offsets, lo + lane) > ws);
+  return lo + __ffs(m) - 1;
+}
+
+// Walk the cost span [ws, we) of the depth-ordered stream, one Gaussian at a time per warp, its tiles spread over the
+// 32 lanes.  Instance j of the Gaussian at position p sits at cost coordinate excl(p) + PT_C*p + PT_C + j.
+// (A variant that flattens the instances of 32 Gaussians over the lanes and ranks with match.any was measured 2.4x
+// SLOWER on B200 -- match.any serialises over distinct values -- and was dropped.)
 template <bool SCATTER>
-__device__ __forceinline__ void walk(int g_begin, int g_end, int P, const uint32_t* __restrict__ order,
+__device__ __forceinline__ void walk(unsigned long long ws, unsigned long long we, int V,
+                                     const uint32_t* __restrict__ order, const uint32_t* __restrict__ offsets,
                                      const int* __restrict__ radii, const float4* __restrict__ rec, int gx, int gy,
                                      uint32_t* wcnt, const uint32_t* blockbase, uint32_t* __restrict__ point_list,
                                      uint64_t* __restrict__ keys, long long capacity, int lane) {
-  for (int g0 = g_begin; g0 < g_end; g0 += 32) {
+  if (ws >= we) return;
+  for (int g0 = first_pos_above(offsets, V, ws, lane);; g0 += 32) {
     const int pos = g0 + lane;
-    uint32_t idx = 0, count = 0, depth_bits = 0;
+    uint32_t idx = 0, depth_bits = 0, j0 = 0, j1 = 0;
     uint2 rmin = {0, 0}, rmax = {0, 0};
-    if (pos < g_end && pos < P) {
+    bool past = pos >= V;
+    if (!past) {
       idx = order[pos];
+      const uint32_t incl = offsets[pos];
       const int radius = radii[idx];
+      uint32_t count = 0;
       if (radius > 0) {
         const float4 r0 = rec[(size_t)idx * 4];
         if (SCATTER) depth_bits = __float_as_uint(rec[(size_t)idx * 4 + 1].z);
         get_rect(r0.x, r0.y, radius, gx, gy, rmin, rmax);
         count = (rmax.x - rmin.x) * (rmax.y - rmin.y);
       }
+      const unsigned long long w0 = (unsigned long long)(incl - count) + (unsigned long long)PT_C * (uint32_t)pos + PT_C;
+      past = w0 - PT_C >= we;
+      if (!past) {  // clip the Gaussian's instances [0, count) to this span
+        j0 = ws > w0 ? (uint32_t)min((unsigned long long)count, ws - w0) : 0u;
+        j1 = we > w0 ? (uint32_t)min((unsigned long long)count, we - w0) : 0u;
+      }
     }
-    uint32_t todo = __ballot_sync(0xffffffffu, count > 0);
+    uint32_t todo = __ballot_sync(0xffffffffu, j1 > j0);
+    const bool last = __any_sync(0xffffffffu, past);
     while (todo) {
       const int src = __ffs(todo) - 1;
       todo &= todo - 1;
-      const uint32_t b_cnt = __shfl_sync(0xffffffffu, count, src);
+      const uint32_t b_j0 = __shfl_sync(0xffffffffu, j0, src);
+      const uint32_t b_j1 = __shfl_sync(0xffffffffu, j1, src);
       const uint32_t b_x0 = __shfl_sync(0xffffffffu, rmin.x, src);
       const uint32_t b_y0 = __shfl_sync(0xffffffffu, rmin.y, src);
       const uint32_t b_w = __shfl_sync(0xffffffffu, rmax.x - rmin.x, src);
@@ -76,7 +145,7 @@ __device__ __forceinline__ void walk(int g_begin, int g_end, int P, const uint32
         b_depth = __shfl_sync(0xffffffffu, depth_bits, src);
         b_idx = __shfl_sync(0xffffffffu, idx, src);
       }
-      for (uint32_t i = lane; i < b_cnt; i += 32) {
+      for (uint32_t i = b_j0 + lane; i < b_j1; i += 32) {
         const uint32_t row = i / b_w;
         const uint32_t t = (b_y0 + row) * gx + b_x0 + (i - row * b_w);
         const uint32_t old = cnt_inc(wcnt, t);
@@ -90,21 +159,40 @@ __device__ __forceinline__ void walk(int g_begin, int g_end, int P, const uint32
       }
       __syncwarp();
     }
+    if (last) break;
   }
 }
 
+// this warp's cost span; V = visible Gaussians = P - (depth keys whose top byte is 0xff, i.e. the culled ones)
+__device__ __forceinline__ void pt_span(const uint32_t* __restrict__ num_rendered, const uint32_t* __restrict__ depth_hist,
+                                        int P, int warp, unsigned long long& ws, unsigned long long& we, int& V) {
+  const uint32_t R = num_rendered[0];
+  V = P - (int)depth_hist[3 * 256 + 255];
+  const unsigned long long total = R ? (unsigned long long)R + (unsigned long long)PT_C * (uint32_t)V : 0ull;
+  const unsigned long long I = (total + gridDim.x - 1) / gridDim.x;
+  const unsigned long long Iw = (I + PT_WARPS - 1) / PT_WARPS;
+  const unsigned long long c0 = (unsigned long long)blockIdx.x * I;
+  ws = c0 + (unsigned long long)warp * Iw;
+  we = ws + Iw;
+  if (we > c0 + I) we = c0 + I;
+  if (we > total) we = total;
+  if (ws > total) ws = total;
+}
+
 __global__ void __launch_bounds__(PT_THREADS)
-part_count_kernel(int P, int T, int chunk, const uint32_t* __restrict__ order, const int* __restrict__ radii,
-                  const float4* __restrict__ rec, int gx, int gy, uint32_t* __restrict__ table) {
+part_count_kernel(int P, int T, const uint32_t* __restrict__ num_rendered,
+                  const uint32_t* __restrict__ depth_hist, const uint32_t* __restrict__ order,
+                  const uint32_t* __restrict__ offsets, const int* __restrict__ radii, const float4* __restrict__ rec,
+                  int gx, int gy, uint32_t* __restrict__ table) {
   extern __shared__ uint32_t pt_smem[];
   const int words = (T + 1) / 2;  // per-warp counter words
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (int i = tid; i < PT_WARPS * words; i += PT_THREADS) pt_smem[i] = 0;
   __syncthreads();
-  const int per_warp = chunk / PT_WARPS;
-  const int g_begin = blockIdx.x * chunk + warp * per_warp;
-  walk<false>(g_begin, min(g_begin + per_warp, P), P, order, radii, rec, gx, gy, pt_smem + warp * words, nullptr,
-              nullptr, nullptr, 0, lane);
+  unsigned long long ws, we;
+  int V;
+  pt_span(num_rendered, depth_hist, P, warp, ws, we, V);
+  walk<false>(ws, we, V, order, offsets, radii, rec, gx, gy, pt_smem + warp * words, nullptr, nullptr, nullptr, 0, lane);
   __syncthreads();
   uint32_t* row = table + (size_t)blockIdx.x * T;
   for (int t = tid; t < T; t += PT_THREADS) {
@@ -143,7 +231,9 @@ part_colscan_kernel(int T, int ctas, uint32_t* __restrict__ table, uint32_t* __r
 }
 
 __global__ void __launch_bounds__(PT_THREADS)
-part_scatter_kernel(int P, int T, int chunk, const uint32_t* __restrict__ order, const int* __restrict__ radii,
+part_scatter_kernel(int P, int T, const uint32_t* __restrict__ num_rendered,
+                    const uint32_t* __restrict__ depth_hist, const uint32_t* __restrict__ order,
+                    const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
                     const float4* __restrict__ rec, int gx, int gy, const uint32_t* __restrict__ table,
                     const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ point_list,
                     uint64_t* __restrict__ keys, long long capacity) {
@@ -153,11 +243,11 @@ part_scatter_kernel(int P, int T, int chunk, const uint32_t* __restrict__ order,
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (int i = tid; i < PT_WARPS * words; i += PT_THREADS) pt_smem[i] = 0;
   __syncthreads();
-  const int per_warp = chunk / PT_WARPS;
-  const int g_begin = blockIdx.x * chunk + warp * per_warp;
-  const int g_end = min(g_begin + per_warp, P);
+  unsigned long long ws, we;
+  int V;
+  pt_span(num_rendered, depth_hist, P, warp, ws, we, V);
   // walk 1: per-warp tile counts (same as kernel A)
-  walk<false>(g_begin, g_end, P, order, radii, rec, gx, gy, pt_smem + warp * words, nullptr, nullptr, nullptr, 0, lane);
+  walk<false>(ws, we, V, order, offsets, radii, rec, gx, gy, pt_smem + warp * words, nullptr, nullptr, nullptr, 0, lane);
   __syncthreads();
   // counts -> exclusive prefix across the warps of this CTA (in place); global base of the CTA per tile
   const uint32_t* row = table + (size_t)blockIdx.x * T;
@@ -167,7 +257,7 @@ part_scatter_kernel(int P, int T, int chunk, const uint32_t* __restrict__ order,
     for (int w = 0; w < PT_WARPS; ++w) {
       const uint32_t c = pt_smem[w * words + w2];
       pt_smem[w * words + w2] = run;
-      run += c;  // no carry between halves: a CTA emits < 65536 instances per tile (chunk <= 65535 Gaussians)
+      run += c;  // no carry between halves: a CTA span holds < 65536 Gaussians (pt_ctas), hence < 65536 per tile
     }
     const int t0 = 2 * w2;
     blockbase[t0] = tile_start[t0] + row[t0];
@@ -175,7 +265,7 @@ part_scatter_kernel(int P, int T, int chunk, const uint32_t* __restrict__ order,
   }
   __syncthreads();
   // walk 2: the running counters now start at each warp's prefix -> final slots
-  walk<true>(g_begin, g_end, P, order, radii, rec, gx, gy, pt_smem + warp * words, blockbase, point_list, keys,
+  walk<true>(ws, we, V, order, offsets, radii, rec, gx, gy, pt_smem + warp * words, blockbase, point_list, keys,
              capacity, lane);
 }
 
@@ -228,53 +318,37 @@ part_tilescan_kernel(int T, const uint32_t* __restrict__ tile_total, uint32_t* _
 }
 
 bool partition_supported(int gx, int gy) { return gx < 1024 && gy < 1024 && gx * gy <= PT_MAX_TILES; }
-int partition_ctas(int P) { return cdiv(P < 1 ? 1 : P, pt_chunk(P)); }
-size_t partition_table_bytes(int P, int T) { return align_up((size_t)partition_ctas(P) * T * sizeof(uint32_t)); }
-
-static size_t pt_smem_bytes(int T, bool scatter) {
-  const size_t words = (size_t)(T + 1) / 2;
-  return (PT_WARPS * words + (scatter ? (size_t)T + 1 : 0)) * sizeof(uint32_t);
+int partition_ctas(long long capacity, int P, int T) { return pt_ctas(capacity < 1 ? 1 : capacity, P < 1 ? 1 : P, T); }
+size_t partition_table_bytes(long long capacity, int P, int T) {
+  return align_up((size_t)partition_ctas(capacity, P, T) * T * sizeof(uint32_t));
 }
 
-cudaError_t launch_partition_count(int P, int gx, int gy, const uint32_t* order, const int* radii, const float4* rec,
-                                   uint32_t* table, uint32_t* tile_total, uint32_t* tile_start, uint2* ranges,
-                                   uint32_t* num_rendered, long long capacity, cudaStream_t st) {
-  const int T = gx * gy, chunk = pt_chunk(P), ctas = partition_ctas(P);
-  static size_t attr_a = 0;
-  const size_t sa = pt_smem_bytes(T, false);
+// count -> column scan -> tile scan -> scatter, all on `st`; R is read from num_rendered[0] on the device.
+cudaError_t launch_partition(int P, int gx, int gy, const uint32_t* order, const uint32_t* offsets, const int* radii,
+                             const float4* rec, uint32_t* table, uint32_t* tile_total, uint32_t* tile_start,
+                             uint2* ranges, uint32_t* num_rendered, uint32_t* point_list, uint64_t* keys,
+                             const uint32_t* depth_hist, long long capacity, cudaStream_t st) {
+  const int T = gx * gy, ctas = partition_ctas(capacity, P, T);
+  static size_t attr_a = 0, attr_b = 0;
+  const size_t sa = pt_smem_bytes(T, false), sb = pt_smem_bytes(T, true);
   if (sa > attr_a) {
     cudaError_t e = cudaFuncSetAttribute(part_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa);
     if (e != cudaSuccess) return e;
     attr_a = sa;
   }
-  part_count_kernel<<<ctas, PT_THREADS, sa, st>>>(P, T, chunk, order, radii, rec, gx, gy, table);
-  count_launch();
-  part_colscan_kernel<<<cdiv(T, 32), 1024, 0, st>>>(T, ctas, table, tile_total);
-  count_launch();
-  part_tilescan_kernel<<<1, 1024, 0, st>>>(T, tile_total, tile_start, ranges, num_rendered, capacity);
-  count_launch();
-  return cudaGetLastError();
-}
-
-cudaError_t launch_partition_scatter(int P, int gx, int gy, const uint32_t* order, const int* radii, const float4* rec,
-                                     const uint32_t* table, const uint32_t* tile_total, uint32_t* tile_start,
-                                     uint2* ranges, uint32_t* num_rendered, uint32_t* point_list, uint64_t* keys,
-                                     long long capacity, bool rescan, cudaStream_t st) {
-  const int T = gx * gy, chunk = pt_chunk(P), ctas = partition_ctas(P);
-  static size_t attr_b = 0;
-  const size_t sb = pt_smem_bytes(T, true);
   if (sb > attr_b) {
     cudaError_t e = cudaFuncSetAttribute(part_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb);
     if (e != cudaSuccess) return e;
     attr_b = sb;
   }
-  // ranges depend on the capacity of THIS call's workspace (clipping): recompute them (one tiny CTA)
-  if (rescan) {
-    part_tilescan_kernel<<<1, 1024, 0, st>>>(T, tile_total, tile_start, ranges, num_rendered, capacity);
-    count_launch();
-  }
-  part_scatter_kernel<<<ctas, PT_THREADS, sb, st>>>(P, T, chunk, order, radii, rec, gx, gy, table, tile_start,
-                                                    point_list, keys, capacity);
+  part_count_kernel<<<ctas, PT_THREADS, sa, st>>>(P, T, num_rendered, depth_hist, order, offsets, radii, rec, gx, gy, table);
+  count_launch();
+  part_colscan_kernel<<<cdiv(T, 32), 1024, 0, st>>>(T, ctas, table, tile_total);
+  count_launch();
+  part_tilescan_kernel<<<1, 1024, 0, st>>>(T, tile_total, tile_start, ranges, num_rendered, capacity);
+  count_launch();
+  part_scatter_kernel<<<ctas, PT_THREADS, sb, st>>>(P, T, num_rendered, depth_hist, order, offsets, radii, rec, gx, gy, table,
+                                                    tile_start, point_list, keys, capacity);
   count_launch();
   return cudaGetLastError();
 }

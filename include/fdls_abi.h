@@ -60,7 +60,6 @@ typedef struct FdlsLayout {
   size_t scan_scratch;
   size_t depth_order;   /* u32[P]: Gaussian indices sorted (stably) by depth bits; culled ones last */
   size_t depth_scratch; /* scratch of that P-element sort */
-  size_t part_table;    /* u32[ctas][tiles]: per-CTA per-tile instance counts / prefixes (binning_algo 0) */
   /* img */
   size_t final_T;   /* f32[H*W]  (reference "accum_alpha") */
   size_t n_contrib; /* u32[H*W] */
@@ -74,6 +73,7 @@ typedef struct FdlsLayout {
   size_t vals_alt; /* u32[capacity] */
   size_t vals;     /* u32[capacity] sorted Gaussian ids (reference: point_list) */
   size_t sort_scratch;
+  size_t part_table; /* u32[ctas(capacity)][tiles]: per-CTA per-tile instance counts / prefixes (binning_algo 0) */
 } FdlsLayout;
 
 typedef struct FdlsFwdArgs {
