@@ -22,6 +22,8 @@ from . import _lib
 _state = {}  # per-device: pinned R buffer, last R
 # bench.py hooks: ctypes arrays of cudaEvent_t handles (FDLS_FWD_EVENTS / FDLS_BWD_EVENTS entries) or None
 profile = {"fwd": None, "bwd": None}
+# parity tests set this: the partition binning then also writes the reference-format sorted keys (not needed to render)
+emit_keys = False
 
 
 def _dev_state(device):
@@ -119,6 +121,7 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
     a.num_rendered_host = st["pinned"].data_ptr()
     a.num_rendered_hint = -1
     a.binning_algo = 1 if os.environ.get("FDLS_BINNING", "partition") == "onesweep" else 0
+    a.emit_keys = int(bool(emit_keys or debug))
     if profile["fwd"] is not None:
         a.stage_events = profile["fwd"]
     stream = _stream()

@@ -46,6 +46,7 @@ class FdlsFwdArgs(C.Structure):
         ("num_rendered_hint", C.c_int64),
         ("stage_events", C.POINTER(C.c_void_p)),
         ("binning_algo", C.c_int32),
+        ("emit_keys", C.c_int32),
     ]
 
 

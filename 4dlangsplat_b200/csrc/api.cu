@@ -241,7 +241,8 @@ FDLS_API int fdls_bin_and_render(const FdlsFwdArgs* a, void* stream) {
       if (launch_partition(a->P, gx, gy, (const uint32_t*)(g + L.depth_order), (const uint32_t*)(g + L.point_offsets),
                            a->radii, (const float4*)(g + L.rec), (uint32_t*)(b + L.part_table),
                            (uint32_t*)(im + L.tile_cursor), (uint32_t*)(im + L.tile_start), ranges, nr,
-                           (uint32_t*)(b + L.vals), (uint64_t*)(b + L.keys), depth_hist, a->capacity,
+                           (uint32_t*)(b + L.vals), a->emit_keys ? (uint64_t*)(b + L.keys) : nullptr, depth_hist,
+                           a->capacity,
                            st) != cudaSuccess)
         return FDLS_ECUDA;
       point_list = (const uint32_t*)(b + L.vals);

@@ -119,7 +119,7 @@ __device__ __forceinline__ void walk(unsigned long long ws, unsigned long long w
       uint32_t count = 0;
       if (radius > 0) {
         const float4 r0 = rec[(size_t)idx * 4];
-        if (SCATTER) depth_bits = __float_as_uint(rec[(size_t)idx * 4 + 1].z);
+        if (SCATTER && keys != nullptr) depth_bits = __float_as_uint(rec[(size_t)idx * 4 + 1].z);
         get_rect(r0.x, r0.y, radius, gx, gy, rmin, rmax);
         count = (rmax.x - rmin.x) * (rmax.y - rmin.y);
       }
@@ -153,7 +153,7 @@ __device__ __forceinline__ void walk(unsigned long long ws, unsigned long long w
           const long long slot = (long long)blockbase[t] + old;
           if (slot < capacity) {
             point_list[slot] = b_idx;
-            keys[slot] = ((uint64_t)t << 32) | b_depth;
+            if (keys != nullptr) keys[slot] = ((uint64_t)t << 32) | b_depth;  // reference-format key, on request
           }
         }
       }

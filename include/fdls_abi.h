@@ -121,6 +121,10 @@ typedef struct FdlsFwdArgs {
   /* binning algorithm: 0 = tile-bucketed count/scan/scatter + per-tile shared-memory sort (default),
    * 1 = key duplication + onesweep LSD radix sort (the reference's structure).  Results are identical. */
   int32_t binning_algo;
+  /* binning_algo 0 never needs (tile|depth) keys: its scatter places every instance by rank.  Non-zero makes it ALSO
+   * write the reference-format sorted keys (point_list_keys, rasterizer_impl.cu:307-312) into the binning workspace,
+   * for parity checks; binning_algo 1 always produces them. */
+  int32_t emit_keys;
 } FdlsFwdArgs;
 #define FDLS_FWD_EVENTS 7
 

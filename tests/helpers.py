@@ -21,6 +21,7 @@ def to_dev(s, dev="cuda"):
 def run_forward(s, include_feature=True, colors_precomp=None, cov3D_precomp=None, dev="cuda"):
     """Returns outputs and decoded intermediates of the product forward (via 4dlangsplat_b200._C)."""
     fd = pkg()
+    fd._C.emit_keys = True  # also write the reference-format sorted keys, so they can be compared bit for bit
     d = to_dev(s, dev)
     E = torch.Tensor([])
     colors = E if colors_precomp is None else torch.as_tensor(colors_precomp, device=dev)
