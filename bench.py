@@ -158,6 +158,66 @@ class EventPool:
         return out / max(1, frames)
 
 
+class E2EPipe:
+    """Host<->device pipeline of the end-to-end arms (same for both): frame i+1's inputs are uploaded from pinned host
+    memory on a copy stream while frame i renders, and frame i's three images go back to pinned host memory on a
+    second copy stream while frame i+1 renders.  Every copy still happens inside the timed region."""
+
+    def __init__(self, wl):
+        self.wl = wl
+        s = wl.s
+        self.up, self.down = torch.cuda.Stream(), torch.cuda.Stream()
+        self.outs_host = [torch.empty((3, s.H, s.W)).pin_memory(), torch.empty((s.F, s.H, s.W)).pin_memory(),
+                          torch.empty((1, s.H, s.W)).pin_memory()]
+        self.h2d = sum(x.numel() * 4 for x in wl.cam_host) + wl.means_host[0].numel() * 4
+        self.d2h = sum(x.numel() * 4 for x in self.outs_host)
+        self.next = None
+        self.on_copied = None
+
+    def upload(self, i):
+        with torch.cuda.stream(self.up):
+            cam = [x.to("cuda", non_blocking=True) for x in self.wl.cam_host]
+            means = self.wl.means_host[i % N_TIMESTAMPS].to("cuda", non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self.up)
+        return cam, means, ev
+
+    def frame(self, i, render):
+        """render(i, means, cam) -> (color, lang, depth) enqueued on the current stream."""
+        main = torch.cuda.current_stream()
+        cam, means, ev = self.next if self.next is not None else self.upload(i)
+        self.next = self.upload(i + 1)
+        main.wait_event(ev)
+        outs = render(i, means, cam)
+        for t in cam + [means]:
+            t.record_stream(main)
+        done = torch.cuda.Event()
+        done.record(main)
+        self.down.wait_event(done)
+        with torch.cuda.stream(self.down):
+            for h, o in zip(self.outs_host, outs):
+                h.copy_(o, non_blocking=True)
+                o.record_stream(self.down)
+            copied = torch.cuda.Event()
+            copied.record(self.down)
+        if self.on_copied is not None:
+            self.on_copied(copied)
+        return copied
+
+    def run(self, steps, warmup, world, render):
+        for i in range(max(1, warmup) * FRAMES_PER_STEP):
+            self.frame(i, render)
+        barrier(world)
+        t0 = time.perf_counter()
+        for k in range(steps):
+            for f in range(FRAMES_PER_STEP):
+                self.frame(k * FRAMES_PER_STEP + f, render)
+            torch.cuda.synchronize()  # the step's images are on the host
+        t1 = time.perf_counter()
+        barrier(world)
+        return max_over_ranks(t1 - t0, world)
+
+
 def run_ours(wl, steps, warmup, world):
     fd = importlib.import_module("4dlangsplat_b200")
     lib = fd._lib.load()
@@ -196,37 +256,21 @@ def run_ours(wl, steps, warmup, world):
     V = int((radii > 0).sum())
 
     # ---- end-to-end arm through the public API with host buffers
-    rs_host = wl.cam_host
-    outs_host = [torch.empty((3, s.H, s.W)).pin_memory(), torch.empty((s.F, s.H, s.W)).pin_memory(),
-                 torch.empty((1, s.H, s.W)).pin_memory()]
-    h2d = sum(x.numel() * 4 for x in rs_host) + wl.means_host[0].numel() * 4
-    d2h = sum(x.numel() * 4 for x in outs_host)
+    pipe = E2EPipe(wl)
 
-    def e2e_frame(i):
+    def render(i, means, cam):
         p = wl.sets[i % N_PARAM_SETS]
-        view, proj, campos, bg = [x.to("cuda", non_blocking=True) for x in rs_host]
-        means = wl.means_host[i % N_TIMESTAMPS].to("cuda", non_blocking=True)
+        view, proj, campos, bg = cam
         settings = dgr.GaussianRasterizationSettings(s.H, s.W, s.tanfovx, s.tanfovy, bg, 1.0, view, proj, s.sh_degree,
                                                      campos, False, False, True)
         with torch.no_grad():
             color, lang, radii_, depth = dgr.GaussianRasterizer(settings)(
                 means3D=means, means2D=None, opacities=p["opac"], shs=p["shs"], language_feature_precomp=p["lang"],
                 scales=p["scales"], rotations=p["rots"])
-        outs_host[0].copy_(color, non_blocking=True)
-        outs_host[1].copy_(lang, non_blocking=True)
-        outs_host[2].copy_(depth, non_blocking=True)
+        return color, lang, depth
 
-    for i in range(max(1, warmup) * FRAMES_PER_STEP):
-        e2e_frame(i)
-    barrier(world)
-    t0 = time.perf_counter()
-    for k in range(steps):
-        for f in range(FRAMES_PER_STEP):
-            e2e_frame(k * FRAMES_PER_STEP + f)
-        torch.cuda.synchronize()  # the step's images are on the host
-    t1 = time.perf_counter()
-    barrier(world)
-    e2e_s = max_over_ranks(t1 - t0, world)
+    e2e_s = pipe.run(steps, warmup, world, render)
+    h2d, d2h = pipe.h2d, pipe.d2h  # per frame
     return dict(ms=ms, n_frames=n_frames, stage_ms=stage_ms, R=float(np.mean(Rs)), V=V, launches=int(launches),
                 e2e_s=e2e_s, h2d=h2d * FRAMES_PER_STEP, d2h=d2h * FRAMES_PER_STEP)
 
@@ -237,18 +281,25 @@ def run_reference(wl, steps, warmup, world):
     ref = refcuda.Ref(s.F)
     M = s.shs.shape[1]
     f32 = dict(dtype=torch.float32, device="cuda")
-    color, lang, depth = torch.empty((3, s.H, s.W), **f32), torch.empty((s.F, s.H, s.W), **f32), torch.empty((1, s.H, s.W), **f32)
+    # output ring: the reference's torch glue allocates fresh outputs every call (rasterize_points.cu:63-78); three
+    # preallocated sets stand in for that so a set can still be on its way to the host while the next frame renders
+    ring = [dict(color=torch.empty((3, s.H, s.W), **f32), lang=torch.empty((s.F, s.H, s.W), **f32),
+                 depth=torch.empty((1, s.H, s.W), **f32), copied=None) for _ in range(3)]
     radii = torch.empty(s.P, dtype=torch.int32, device="cuda")
     Rs = []
 
     def frame(i, means=None, cam=None):
         p = wl.sets[i % N_PARAM_SETS]
+        o = ring[i % 3]
+        if o["copied"] is not None:
+            torch.cuda.current_stream().wait_event(o["copied"])
         view, proj, campos, bg = cam if cam is not None else (wl.view, wl.proj, wl.campos, wl.bg)
         m = means if means is not None else wl.means[i % N_TIMESTAMPS]
         # the reference's torch glue fills its outputs before the kernels run (rasterize_points.cu:70-78)
-        color.zero_(); lang.zero_(); depth.zero_(); radii.zero_()
-        return ref.forward_raw(s.P, s.sh_degree, M, s.W, s.H, bg, m, p["shs"], p["lang"], p["opac"], p["scales"],
-                               p["rots"], view, proj, campos, s.tanfovx, s.tanfovy, color, lang, depth, radii)
+        o["color"].zero_(); o["lang"].zero_(); o["depth"].zero_(); radii.zero_()
+        R = ref.forward_raw(s.P, s.sh_degree, M, s.W, s.H, bg, m, p["shs"], p["lang"], p["opac"], p["scales"],
+                            p["rots"], view, proj, campos, s.tanfovx, s.tanfovy, o["color"], o["lang"], o["depth"], radii)
+        return R, o
 
     for i in range(warmup * FRAMES_PER_STEP):
         frame(i)
@@ -257,37 +308,24 @@ def run_reference(wl, steps, warmup, world):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(n_frames):
-        Rs.append(frame(i))
+        Rs.append(frame(i)[0])
     e1.record()
     barrier(world)
     ms = max_over_ranks(e0.elapsed_time(e1), world)
     V = int((radii > 0).sum())
-    outs_host = [torch.empty((3, s.H, s.W)).pin_memory(), torch.empty((s.F, s.H, s.W)).pin_memory(),
-                 torch.empty((1, s.H, s.W)).pin_memory()]
-    h2d = sum(x.numel() * 4 for x in wl.cam_host) + wl.means_host[0].numel() * 4
-    d2h = sum(x.numel() * 4 for x in outs_host)
+    pipe = E2EPipe(wl)
+    state = {}
 
-    def e2e_frame(i):
-        cam = [x.to("cuda", non_blocking=True) for x in wl.cam_host]
-        means = wl.means_host[i % N_TIMESTAMPS].to("cuda", non_blocking=True)
-        frame(i, means, cam)
-        outs_host[0].copy_(color, non_blocking=True)
-        outs_host[1].copy_(lang, non_blocking=True)
-        outs_host[2].copy_(depth, non_blocking=True)
+    def render(i, means, cam):
+        _, o = frame(i, means, cam)
+        state["o"] = o
+        return o["color"], o["lang"], o["depth"]
 
-    for i in range(max(1, warmup) * FRAMES_PER_STEP):
-        e2e_frame(i)
-    barrier(world)
-    t0 = time.perf_counter()
-    for k in range(steps):
-        for f in range(FRAMES_PER_STEP):
-            e2e_frame(k * FRAMES_PER_STEP + f)
-        torch.cuda.synchronize()
-    t1 = time.perf_counter()
-    barrier(world)
-    e2e_s = max_over_ranks(t1 - t0, world)
+    # remember each set's download event so that the set is not overwritten before it has reached the host
+    pipe.on_copied = lambda ev: state["o"].__setitem__("copied", ev)
+    e2e_s = pipe.run(steps, warmup, world, render)
     return dict(ms=ms, n_frames=n_frames, stage_ms=None, R=float(np.mean(Rs)), V=V, launches=0, e2e_s=e2e_s,
-                h2d=h2d * FRAMES_PER_STEP, d2h=d2h * FRAMES_PER_STEP)
+                h2d=pipe.h2d * FRAMES_PER_STEP, d2h=pipe.d2h * FRAMES_PER_STEP)
 
 
 TRAIN_VIEWS = 4  # BASELINE.json configs[2]: HyperNeRF-shaped training step, batch of 4 views
