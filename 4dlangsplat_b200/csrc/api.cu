@@ -14,7 +14,7 @@ static inline void rec(void** ev, int i, cudaStream_t st) {
 // preprocess_fwd.cu
 cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, float4* rec, uint32_t* tiles_touched,
                                   uint8_t* clamped, uint64_t* depth_keys, uint32_t* depth_vals, uint32_t* depth_hist,
-                                  cudaStream_t st);
+                                  uint32_t* tickets, cudaStream_t st);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 // binning.cu
 size_t scan_scratch_bytes(int P);
@@ -194,7 +194,7 @@ FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
   rc = sort_prepare(a->P, 0, 32, dscr, dscr_bytes, st);
   if (rc < 0) return rc;
   if (launch_preprocess_fwd(a, vp, (float4*)(g + L.rec), (uint32_t*)(g + L.tiles_touched), (uint8_t*)(g + L.clamped),
-                            dk_a, order, a->P > 0 ? sort_hist(dscr) : nullptr, st) != cudaSuccess)
+                            dk_a, order, a->P > 0 ? sort_hist(dscr) : nullptr, nr + 2, st) != cudaSuccess)
     return FDLS_ECUDA;
   rec(a->stage_events, 1, st);
   // (1) order the GAUSSIANS by depth bits (stable, P elements) ...

@@ -43,10 +43,13 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t& total,
   return r;
 }
 
+// Block sums; the LAST block to finish (ticket in num_rendered[2], zeroed by the preprocess kernel and reset here)
+// also scans them in place and publishes R and the overflow flag, which saves the one-block spine launch.
 __global__ void __launch_bounds__(SCAN_THREADS)
 scan_reduce_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __restrict__ order,
-                   uint32_t* __restrict__ block_sums) {
+                   uint32_t* __restrict__ block_sums, uint32_t* __restrict__ num_rendered, long long capacity) {
   __shared__ uint32_t s_warp[33];
+  __shared__ uint32_t s_last;
   const int base = blockIdx.x * SCAN_TILE;
   uint32_t s = 0;
 #pragma unroll
@@ -56,7 +59,29 @@ scan_reduce_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __res
   }
   uint32_t total;
   block_excl_scan<SCAN_THREADS>(s, total, s_warp);
-  if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+  if (threadIdx.x == 0) {
+    block_sums[blockIdx.x] = total;
+    __threadfence();
+    s_last = atomicAdd(&num_rendered[2], 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const int nblocks = gridDim.x;
+  uint32_t carry = 0;
+  for (int b0 = 0; b0 < nblocks; b0 += SCAN_THREADS) {
+    const int k = b0 + threadIdx.x;
+    const uint32_t v = k < nblocks ? __ldcg(&block_sums[k]) : 0;
+    uint32_t tot;
+    const uint32_t ex = block_excl_scan<SCAN_THREADS>(v, tot, s_warp);
+    if (k < nblocks) block_sums[k] = carry + ex;
+    carry += tot;
+  }
+  if (threadIdx.x == 0) {
+    num_rendered[0] = carry;
+    num_rendered[1] = ((long long)carry > capacity) ? 1u : 0u;
+    num_rendered[2] = 0;  // ready for the next use of this workspace
+  }
 }
 
 // one block: exclusive scan of the block sums in place; publishes R and the overflow flag
@@ -250,8 +275,12 @@ size_t scan_scratch_bytes(int P) { return align_up((size_t)(cdiv(P, SCAN_TILE) +
 cudaError_t launch_scan(int P, const uint32_t* tiles_touched, const uint32_t* order, uint32_t* offsets,
                         uint32_t* block_sums, uint32_t* num_rendered, long long capacity, cudaStream_t st) {
   const int nb = cdiv(P, SCAN_TILE);
-  if (P > 0) { scan_reduce_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, order, block_sums); count_launch(); }
-  scan_spine_kernel<<<1, 1024, 0, st>>>(nb, block_sums, num_rendered, capacity, nullptr); count_launch();
+  if (P > 0) {
+    scan_reduce_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, order, block_sums, num_rendered, capacity);
+    count_launch();
+  } else {
+    scan_spine_kernel<<<1, 1024, 0, st>>>(nb, block_sums, num_rendered, capacity, nullptr); count_launch();
+  }
   if (P > 0) { scan_apply_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, order, block_sums, offsets); count_launch(); }
   return cudaGetLastError();
 }

@@ -206,9 +206,18 @@ part_count_kernel(int P, int T, const uint32_t* __restrict__ num_rendered,
 // per tile: exclusive scan over the CTAs (table is [ctas][T], coalesced along t); tile_total[t] = column sum.
 // CTA = 32 tiles x 32 row groups: each thread sums its slice of rows, the 32 slice sums of a tile are scanned through
 // shared memory, then the slice is rewritten as running prefixes (second read served by L1/L2).
+__device__ __forceinline__ void tilescan_body(int T, const uint32_t* tile_total, uint32_t* __restrict__ tile_start,
+                                              uint2* __restrict__ ranges, uint32_t* __restrict__ num_rendered,
+                                              long long capacity);
+
+// The LAST block to finish (ticket in num_rendered[3], zeroed by the preprocess kernel and reset here) goes on to scan
+// the tile totals (tilescan_body), which saves the one-block launch that used to follow.
 __global__ void __launch_bounds__(1024)
-part_colscan_kernel(int T, int ctas, uint32_t* __restrict__ table, uint32_t* __restrict__ tile_total) {
+part_colscan_kernel(int T, int ctas, uint32_t* __restrict__ table, uint32_t* __restrict__ tile_total,
+                    uint32_t* __restrict__ tile_start, uint2* __restrict__ ranges,
+                    uint32_t* __restrict__ num_rendered, long long capacity) {
   __shared__ uint32_t s_sum[32][33];
+  __shared__ uint32_t s_last;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int t = blockIdx.x * 32 + tx;
   const int per = (ctas + 31) / 32;
@@ -228,6 +237,14 @@ part_colscan_kernel(int T, int ctas, uint32_t* __restrict__ table, uint32_t* __r
     }
     if (ty == 31) tile_total[t] = run;  // the last slice ends at the column total (empty slices pass `run` through)
   }
+  __threadfence();  // every writer publishes its tile totals before the block takes its ticket
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(&num_rendered[3], 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  tilescan_body(T, tile_total, tile_start, ranges, num_rendered, capacity);
+  if (threadIdx.x == 0) num_rendered[3] = 0;
 }
 
 __global__ void __launch_bounds__(PT_THREADS)
@@ -270,15 +287,15 @@ part_scatter_kernel(int P, int T, const uint32_t* __restrict__ num_rendered,
 }
 
 // tile_scan_kernel lives in binning_scan below: exclusive scan over tile totals -> tile_start, ranges, R
-__global__ void __launch_bounds__(1024)
-part_tilescan_kernel(int T, const uint32_t* __restrict__ tile_total, uint32_t* __restrict__ tile_start,
-                     uint2* __restrict__ ranges, uint32_t* __restrict__ num_rendered, long long capacity) {
+__device__ __forceinline__ void tilescan_body(int T, const uint32_t* tile_total, uint32_t* __restrict__ tile_start,
+                                              uint2* __restrict__ ranges, uint32_t* __restrict__ num_rendered,
+                                              long long capacity) {
   __shared__ uint32_t s_warp[33];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   uint32_t carry = 0;
   for (int base = 0; base < T; base += 1024) {
     const int t = base + threadIdx.x;
-    const uint32_t c = t < T ? tile_total[t] : 0;
+    const uint32_t c = t < T ? __ldcg(&tile_total[t]) : 0;
     uint32_t incl = c;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -317,6 +334,13 @@ part_tilescan_kernel(int T, const uint32_t* __restrict__ tile_total, uint32_t* _
   }
 }
 
+__global__ void __launch_bounds__(1024)
+part_tilescan_kernel(int T, const uint32_t* __restrict__ tile_total, uint32_t* __restrict__ tile_start,
+                     uint2* __restrict__ ranges, uint32_t* __restrict__ num_rendered, long long capacity) {
+  tilescan_body(T, tile_total, tile_start, ranges, num_rendered, capacity);
+}
+
+
 bool partition_supported(int gx, int gy) { return gx < 1024 && gy < 1024 && gx * gy <= PT_MAX_TILES; }
 int partition_ctas(long long capacity, int P, int T) { return pt_ctas(capacity < 1 ? 1 : capacity, P < 1 ? 1 : P, T); }
 size_t partition_table_bytes(long long capacity, int P, int T) {
@@ -343,9 +367,8 @@ cudaError_t launch_partition(int P, int gx, int gy, const uint32_t* order, const
   }
   part_count_kernel<<<ctas, PT_THREADS, sa, st>>>(P, T, num_rendered, depth_hist, order, offsets, radii, rec, gx, gy, table);
   count_launch();
-  part_colscan_kernel<<<cdiv(T, 32), 1024, 0, st>>>(T, ctas, table, tile_total);
-  count_launch();
-  part_tilescan_kernel<<<1, 1024, 0, st>>>(T, tile_total, tile_start, ranges, num_rendered, capacity);
+  part_colscan_kernel<<<cdiv(T, 32), 1024, 0, st>>>(T, ctas, table, tile_total, tile_start, ranges, num_rendered,
+                                                    capacity);
   count_launch();
   part_scatter_kernel<<<ctas, PT_THREADS, sb, st>>>(P, T, num_rendered, depth_hist, order, offsets, radii, rec, gx, gy, table,
                                                     tile_start, point_list, keys, capacity);

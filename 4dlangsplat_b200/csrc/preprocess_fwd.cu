@@ -91,8 +91,10 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
                       int* __restrict__ radii, float4* __restrict__ rec, uint32_t* __restrict__ tiles_touched,
                       uint8_t* __restrict__ clamped, uint64_t* __restrict__ depth_keys,
                       uint32_t* __restrict__ depth_vals, int prefiltered, uint32_t sh_magic,
-                      uint32_t* __restrict__ depth_hist) {
-  extern __shared__ float s_sh[];  // [256][3M+1] when SH are staged (sh_magic != 0), else empty
+                      uint32_t* __restrict__ depth_hist, uint32_t* __restrict__ tickets) {
+  extern __shared__ float s_sh[];
+  // num_rendered[2..3]: "last block done" tickets of the scan / partition kernels that follow on this stream
+  if (tickets != nullptr && blockIdx.x == 0 && threadIdx.x < 2) tickets[threadIdx.x] = 0;  // [256][3M+1] when SH are staged (sh_magic != 0), else empty
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   __shared__ uint32_t s_hist[4][256];  // digit histograms of the depth keys, for the depth sort that follows
   if (depth_hist != nullptr)
@@ -237,7 +239,7 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
 
 cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, float4* rec, uint32_t* tiles_touched,
                                   uint8_t* clamped, uint64_t* depth_keys, uint32_t* depth_vals, uint32_t* depth_hist,
-                                  cudaStream_t st) {
+                                  uint32_t* tickets, cudaStream_t st) {
   if (a->P == 0) return cudaSuccess;
   // SH staging needs 256*(3M+1) floats of shared memory; M <= 16 (degree 3) -> 50 KB
   const bool stage = a->shs != nullptr && a->colors_precomp == nullptr && a->M >= 1 && a->M <= 16;
@@ -252,7 +254,7 @@ cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, fl
   preprocess_fwd_kernel<<<cdiv(a->P, 256), 256, smem, st>>>(
       a->P, a->D, a->M, a->F, a->means3D, a->scales, a->rotations, a->opacities, a->shs, a->cov3D_precomp,
       a->colors_precomp, a->language_feature, vp, a->radii, rec, tiles_touched, clamped, depth_keys, depth_vals,
-      a->prefiltered, magic, depth_hist); count_launch();
+      a->prefiltered, magic, depth_hist, tickets); count_launch();
   return cudaGetLastError();
 }
 
