@@ -109,8 +109,7 @@ __device__ __forceinline__ void walk(unsigned long long ws, unsigned long long w
   if (ws >= we) return;
   for (int g0 = first_pos_above(offsets, V, ws, lane);; g0 += 32) {
     const int pos = g0 + lane;
-    uint32_t idx = 0, depth_bits = 0, j0 = 0, j1 = 0;
-    uint2 rmin = {0, 0}, rmax = {0, 0};
+    uint32_t idx = 0, depth_bits = 0, j0 = 0, j1 = 0, packed = 0, magic = 0;
     bool past = pos >= V;
     if (!past) {
       idx = order[pos];
@@ -120,8 +119,12 @@ __device__ __forceinline__ void walk(unsigned long long ws, unsigned long long w
       if (radius > 0) {
         const float4 r0 = rec[(size_t)idx * 4];
         if (SCATTER && keys != nullptr) depth_bits = __float_as_uint(rec[(size_t)idx * 4 + 1].z);
+        uint2 rmin, rmax;
         get_rect(r0.x, r0.y, radius, gx, gy, rmin, rmax);
-        count = (rmax.x - rmin.x) * (rmax.y - rmin.y);
+        const uint32_t w = rmax.x - rmin.x;
+        count = w * (rmax.y - rmin.y);
+        packed = rmin.x | (rmin.y << 10) | (w << 20);   // gx, gy < 1024 (partition_supported)
+        magic = w > 1 ? 0xffffffffu / w + 1u : 0u;      // floor(i / w) == umulhi(i, magic) while i * w < 2^32
       }
       const unsigned long long w0 = (unsigned long long)(incl - count) + (unsigned long long)PT_C * (uint32_t)pos + PT_C;
       past = w0 - PT_C >= we;
@@ -137,17 +140,18 @@ __device__ __forceinline__ void walk(unsigned long long ws, unsigned long long w
       todo &= todo - 1;
       const uint32_t b_j0 = __shfl_sync(0xffffffffu, j0, src);
       const uint32_t b_j1 = __shfl_sync(0xffffffffu, j1, src);
-      const uint32_t b_x0 = __shfl_sync(0xffffffffu, rmin.x, src);
-      const uint32_t b_y0 = __shfl_sync(0xffffffffu, rmin.y, src);
-      const uint32_t b_w = __shfl_sync(0xffffffffu, rmax.x - rmin.x, src);
+      const uint32_t b_pack = __shfl_sync(0xffffffffu, packed, src);
+      const uint32_t b_magic = __shfl_sync(0xffffffffu, magic, src);
       uint32_t b_depth = 0, b_idx = 0;
       if (SCATTER) {
-        b_depth = __shfl_sync(0xffffffffu, depth_bits, src);
+        if (keys != nullptr) b_depth = __shfl_sync(0xffffffffu, depth_bits, src);
         b_idx = __shfl_sync(0xffffffffu, idx, src);
       }
+      const uint32_t b_w = b_pack >> 20;
+      const uint32_t t0 = ((b_pack >> 10) & 1023u) * gx + (b_pack & 1023u);  // tile of the rect's first cell
       for (uint32_t i = b_j0 + lane; i < b_j1; i += 32) {
-        const uint32_t row = i / b_w;
-        const uint32_t t = (b_y0 + row) * gx + b_x0 + (i - row * b_w);
+        const uint32_t row = b_w > 1 ? __umulhi(i, b_magic) : i;
+        const uint32_t t = t0 + row * gx + (i - row * b_w);
         const uint32_t old = cnt_inc(wcnt, t);
         if (SCATTER) {
           const long long slot = (long long)blockbase[t] + old;
@@ -204,8 +208,8 @@ part_count_kernel(int P, int T, const uint32_t* __restrict__ num_rendered,
 }
 
 // per tile: exclusive scan over the CTAs (table is [ctas][T], coalesced along t); tile_total[t] = column sum.
-// CTA = 32 tiles x 32 row groups: each thread sums its slice of rows, the 32 slice sums of a tile are scanned through
-// shared memory, then the slice is rewritten as running prefixes (second read served by L1/L2).
+// Each thread sums its slice of rows, the slice sums of a tile are scanned through shared memory, then the slice is
+// rewritten as running prefixes (second read served by L1/L2).
 __device__ __forceinline__ void tilescan_body(int T, const uint32_t* tile_total, uint32_t* __restrict__ tile_start,
                                               uint2* __restrict__ ranges, uint32_t* __restrict__ num_rendered,
                                               long long capacity);
@@ -216,12 +220,13 @@ __global__ void __launch_bounds__(1024)
 part_colscan_kernel(int T, int ctas, uint32_t* __restrict__ table, uint32_t* __restrict__ tile_total,
                     uint32_t* __restrict__ tile_start, uint2* __restrict__ ranges,
                     uint32_t* __restrict__ num_rendered, long long capacity) {
-  __shared__ uint32_t s_sum[32][33];
+  // CTA = 8 tiles x 128 row groups (a warp reads 4 row groups x 32 bytes: whole sectors); T/8 CTAs fill the GPU
+  __shared__ uint32_t s_sum[128][9];
   __shared__ uint32_t s_last;
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int t = blockIdx.x * 32 + tx;
-  const int per = (ctas + 31) / 32;
-  const int r0 = ty * per, r1 = min(r0 + per, ctas);
+  const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;
+  const int t = blockIdx.x * 8 + tx;
+  const int per = (ctas + 127) / 128;
+  const int r0 = min(ty * per, ctas), r1 = min(r0 + per, ctas);
   uint32_t sum = 0;
   if (t < T)
     for (int r = r0; r < r1; ++r) sum += table[(size_t)r * T + t];
@@ -235,7 +240,7 @@ part_colscan_kernel(int T, int ctas, uint32_t* __restrict__ table, uint32_t* __r
       table[(size_t)r * T + t] = run;
       run += v;
     }
-    if (ty == 31) tile_total[t] = run;  // the last slice ends at the column total (empty slices pass `run` through)
+    if (ty == 127) tile_total[t] = run;  // the last slice ends at the column total (empty slices pass `run` through)
   }
   __threadfence();  // every writer publishes its tile totals before the block takes its ticket
   __syncthreads();
@@ -367,7 +372,7 @@ cudaError_t launch_partition(int P, int gx, int gy, const uint32_t* order, const
   }
   part_count_kernel<<<ctas, PT_THREADS, sa, st>>>(P, T, num_rendered, depth_hist, order, offsets, radii, rec, gx, gy, table);
   count_launch();
-  part_colscan_kernel<<<cdiv(T, 32), 1024, 0, st>>>(T, ctas, table, tile_total, tile_start, ranges, num_rendered,
+  part_colscan_kernel<<<cdiv(T, 8), 1024, 0, st>>>(T, ctas, table, tile_total, tile_start, ranges, num_rendered,
                                                     capacity);
   count_launch();
   part_scatter_kernel<<<ctas, PT_THREADS, sb, st>>>(P, T, num_rendered, depth_hist, order, offsets, radii, rec, gx, gy, table,
