@@ -189,22 +189,34 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ 
   st_relaxed(my_state, (tile == 0 ? FLAG_PREFIX : FLAG_AGG) | count);
   uint32_t excl = 0;
   if (tile > 0) {
+    // Look-back, 8 predecessors per step: the 8 loads are in flight together (one L2 round trip instead of eight),
+    // then consumed nearest-first; a not-yet-published entry ends the step and is polled again.
+    constexpr int LB = 8;
     long long t = (long long)tile - 1;
     uint32_t spins = 0;
-    while (true) {
-      const uint32_t v = ld_relaxed(tile_state + (size_t)t * RS_BINS + d);
-      const uint32_t f = v & FLAG_MASK;
-      if (f == 0) {
-        if (++spins > (1u << 24)) {  // never hang the GPU: report and bail out
-          atomicExch(error_flag, 1u);
+    bool done = false;
+    while (!done) {
+      uint32_t v[LB];
+#pragma unroll
+      for (int i = 0; i < LB; ++i) v[i] = (t - i >= 0) ? ld_relaxed(tile_state + (size_t)(t - i) * RS_BINS + d) : FLAG_PREFIX;
+#pragma unroll
+      for (int i = 0; i < LB; ++i) {
+        if (done) break;
+        const uint32_t f = v[i] & FLAG_MASK;
+        if (f == 0) {  // predecessor t-i has not published yet: resume from it
+          t -= i;
+          if (++spins > (1u << 22)) {  // never hang the GPU: report and bail out
+            atomicExch(error_flag, 1u);
+            done = true;
+          } else if (i == 0) {
+            __nanosleep(20);
+          }
           break;
         }
-        __nanosleep(20);
-        continue;
+        excl += v[i] & VAL_MASK;
+        if (f == FLAG_PREFIX) done = true;
+        if (i == LB - 1 && !done) t -= LB;
       }
-      excl += v & VAL_MASK;
-      if (f == FLAG_PREFIX) break;
-      --t;
     }
     st_relaxed(my_state, FLAG_PREFIX | ((excl + count) & VAL_MASK));
   }
