@@ -512,6 +512,22 @@ def cpu_baseline(wl, frames=1):
                       "rasterizer; the reference has no CPU rasterizer)" % (frames, wl.name)}
 
 
+def ncu_traffic(workload, stage):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's kernel, from the committed ncu --set full
+    capture of one frame (profiles/r01_ncu_full_cfg2_frame.json; cfg2 only), else None."""
+    kernels = {"render": "render_fwd_kernel", "preprocess": "preprocess_fwd_kernel", "duplicate": "part_scatter_kernel"}
+    try:
+        if workload != "cfg2" or stage not in kernels:
+            return None
+        rows = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_full_cfg2_frame.json")))
+        for r in rows:
+            if r["kernel"].startswith(kernels[stage]):
+                return int((r["rd"] + r["wr"]) * 1e6)
+    except Exception:
+        pass
+    return None
+
+
 def stage_bytes(P, V, R, HW, T, F):
     """Algorithmic bytes per launch sequence of each forward stage."""
     return {"preprocess": 48 * P + 232 * V, "scan": 8 * P, "duplicate": 20 * P + 12 * R, "sort": 24 * R,
@@ -624,11 +640,14 @@ def main():
         dom = max(st, key=st.get)
         ach = sb[dom] / (st[dom] * 1e-3) / 1e9
         line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": round(ach, 1), "peak": pk["hbm_gbs"],
-                            "unit": "GB/s", "frac": round(ach / pk["hbm_gbs"], 4), "traffic": None,
+                            "unit": "GB/s", "frac": round(ach / pk["hbm_gbs"], 4), "traffic": ncu_traffic(a.workload, dom),
                             "peak_source": pk_kind + " (MEASURED_PEAKS.json hbm_gbs)" if pk_kind == "measured" else "fallback",
                             "algorithmic_bytes_per_launch": int(sb[dom]), "avg_launch_ms": round(st[dom], 4)}
         total_b = 48 * s.P + 232 * r["V"] + (80 + 4 * s.F) * r["R"] + (24 + 4 * s.F) * HW
         line["stages_ms"] = {k: round(v, 4) for k, v in st.items()}
+        line["stages_note"] = ("default (partition) binning: 'scan' = depth sort of the Gaussians + tile-count scan, "
+                               "'duplicate' = count / column scan / scatter of the stable partition by tile, "
+                               "'sort' and 'tile_ranges' are empty (they belong to binning_algo=1)")
         line["stages_gbs"] = {k: round(sb[k] / (st[k] * 1e-3) / 1e9, 1) if st[k] > 0 else None for k in names}
         line["whole_path"] = {"algorithmic_bytes_per_frame": int(total_b),
                               "achieved_gbs": round(total_b / (r["ms"] / r["n_frames"] * 1e-3) / 1e9, 1)}
