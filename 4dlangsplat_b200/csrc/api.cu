@@ -19,7 +19,8 @@ cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, 
 // binning.cu
 size_t scan_scratch_bytes(int P);
 cudaError_t launch_scan(int P, const uint32_t* tiles_touched, const uint32_t* order, uint32_t* offsets,
-                        uint32_t* block_sums, uint32_t* num_rendered, long long capacity, cudaStream_t st);
+                        uint32_t* block_sums, uint32_t* num_rendered, long long capacity, uint32_t* host_mirror,
+                        cudaStream_t st);
 cudaError_t launch_duplicate(int P, const float4* rec, const uint32_t* order, const uint32_t* offsets, const int* radii,
                              uint64_t* keys, uint32_t* vals, int gx, int gy, long long capacity, uint32_t* global_hist,
                              int passes, cudaStream_t st);
@@ -203,12 +204,9 @@ FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
   if (sel != 0) return FDLS_ECUDA;  // 4 passes: result is back in the `a` buffers by construction
   // (2) ... and scan the tile counts in that order, so instances are emitted depth-sorted
   if (launch_scan(a->P, (uint32_t*)(g + L.tiles_touched), order, (uint32_t*)(g + L.point_offsets),
-                  (uint32_t*)(g + L.scan_scratch), nr, a->capacity, st) != cudaSuccess)
+                  (uint32_t*)(g + L.scan_scratch), nr, a->capacity, a->num_rendered_host, st) != cudaSuccess)
     return FDLS_ECUDA;
   rec(a->stage_events, 2, st);
-  if (a->num_rendered_host &&
-      cudaMemcpyAsync(a->num_rendered_host, nr, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st) != cudaSuccess)
-    return FDLS_ECUDA;
   return FDLS_OK;
 }
 

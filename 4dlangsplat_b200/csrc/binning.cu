@@ -47,7 +47,8 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t& total,
 // also scans them in place and publishes R and the overflow flag, which saves the one-block spine launch.
 __global__ void __launch_bounds__(SCAN_THREADS)
 scan_reduce_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __restrict__ order,
-                   uint32_t* __restrict__ block_sums, uint32_t* __restrict__ num_rendered, long long capacity) {
+                   uint32_t* __restrict__ block_sums, uint32_t* __restrict__ num_rendered, long long capacity,
+                   uint32_t* host_mirror) {
   __shared__ uint32_t s_warp[33];
   __shared__ uint32_t s_last;
   const int base = blockIdx.x * SCAN_TILE;
@@ -81,13 +82,19 @@ scan_reduce_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __res
     num_rendered[0] = carry;
     num_rendered[1] = ((long long)carry > capacity) ? 1u : 0u;
     num_rendered[2] = 0;  // ready for the next use of this workspace
+    if (host_mirror != nullptr) {  // pinned, device-mapped host memory: no copy-engine hop between the kernels
+      volatile uint32_t* h = host_mirror;
+      h[0] = carry;
+      h[1] = ((long long)carry > capacity) ? 1u : 0u;
+      __threadfence_system();
+    }
   }
 }
 
 // one block: exclusive scan of the block sums in place; publishes R and the overflow flag
 __global__ void __launch_bounds__(1024)
 scan_spine_kernel(int nblocks, uint32_t* __restrict__ block_sums, uint32_t* __restrict__ num_rendered,
-                  long long capacity, uint32_t* __restrict__ host_mirror) {
+                  long long capacity, uint32_t* host_mirror) {
   __shared__ uint32_t s_warp[33];
   uint32_t carry = 0;
   for (int base = 0; base < nblocks; base += 1024) {
@@ -101,6 +108,12 @@ scan_spine_kernel(int nblocks, uint32_t* __restrict__ block_sums, uint32_t* __re
   if (threadIdx.x == 0) {
     num_rendered[0] = carry;
     num_rendered[1] = ((long long)carry > capacity) ? 1u : 0u;
+    if (host_mirror != nullptr) {
+      volatile uint32_t* h = host_mirror;
+      h[0] = carry;
+      h[1] = ((long long)carry > capacity) ? 1u : 0u;
+      __threadfence_system();
+    }
   }
 }
 
@@ -273,13 +286,15 @@ tile_ranges_kernel(const uint32_t* __restrict__ num_rendered, long long capacity
 size_t scan_scratch_bytes(int P) { return align_up((size_t)(cdiv(P, SCAN_TILE) + 1) * sizeof(uint32_t)); }
 
 cudaError_t launch_scan(int P, const uint32_t* tiles_touched, const uint32_t* order, uint32_t* offsets,
-                        uint32_t* block_sums, uint32_t* num_rendered, long long capacity, cudaStream_t st) {
+                        uint32_t* block_sums, uint32_t* num_rendered, long long capacity, uint32_t* host_mirror,
+                        cudaStream_t st) {
   const int nb = cdiv(P, SCAN_TILE);
   if (P > 0) {
-    scan_reduce_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, order, block_sums, num_rendered, capacity);
+    scan_reduce_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, order, block_sums, num_rendered, capacity,
+                                                    host_mirror);
     count_launch();
   } else {
-    scan_spine_kernel<<<1, 1024, 0, st>>>(nb, block_sums, num_rendered, capacity, nullptr); count_launch();
+    scan_spine_kernel<<<1, 1024, 0, st>>>(nb, block_sums, num_rendered, capacity, host_mirror); count_launch();
   }
   if (P > 0) { scan_apply_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, order, block_sums, offsets); count_launch(); }
   return cudaGetLastError();

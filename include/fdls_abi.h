@@ -109,7 +109,8 @@ typedef struct FdlsFwdArgs {
   void* img_ws;     size_t img_bytes;
   void* binning_ws; size_t binning_bytes;
   int64_t capacity; /* instances the binning workspace was sized for */
-  /* optional pinned-host uint32[2]: asynchronously receives {R, overflow}; valid after the stream reaches that point */
+  /* optional pinned, DEVICE-ACCESSIBLE host uint32[2] (cudaHostAlloc / torch pin_memory under UVA): the scan kernel
+   * stores {R, overflow} into it directly; valid once the stream has passed fdls_preprocess's work */
   uint32_t* num_rendered_host;
   /* host-known instance count for grid sizing in fdls_bin_and_render; <0 = unknown, size grids by capacity.
    * <0 also states that `capacity` is the one fdls_preprocess ran with (its clipped tile ranges are reused);
