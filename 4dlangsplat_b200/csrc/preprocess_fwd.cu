@@ -115,6 +115,22 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
       const int n_fl = min(32, P - g0) * 3 * M;
       const float* src = shs + (size_t)g0 * 3 * M;
       float* dst = s_sh + warp * 32 * sh_stride;
+      if (n_fl == 1536) {  // full warp, M = 16 (degree 3): all twelve 16-byte loads in flight before the first store
+        const float4* src4 = reinterpret_cast<const float4*>(src);
+        float4 q[12];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) q[i] = src4[lane + 32 * i];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) {
+          const float v[4] = {q[i].x, q[i].y, q[i].z, q[i].w};
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint32_t e = 4 * (lane + 32 * i) + k;
+            const uint32_t g = __umulhi(e, sh_magic);  // e / 48
+            dst[g * sh_stride + (e - g * 48)] = v[k];
+          }
+        }
+      } else
       for (int e0 = 4 * lane; e0 < n_fl; e0 += 128) {
         float v[4];
         if (e0 + 3 < n_fl) {
