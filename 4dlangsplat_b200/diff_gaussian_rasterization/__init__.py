@@ -65,6 +65,10 @@ class _RasterizeGaussians(torch.autograd.Function):
                                "\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
+        # an output the loss never touches arrives as None instead of a zeros tensor (the depth image in every stage of
+        # train.py): the backward then skips that output's gradient terms instead of multiplying by zeros
+        ctx.set_materialize_grads(False)
+        ctx.out_shapes = (color.shape, language_feature.shape)
         ctx.save_for_backward(colors_precomp, language_feature_precomp, means3D, scales, rotations, cov3Ds_precomp,
                               radii, sh, geomBuffer, binningBuffer, imgBuffer)
         ctx.mark_non_differentiable(radii)
@@ -75,6 +79,14 @@ class _RasterizeGaussians(torch.autograd.Function):
         rs = ctx.raster_settings
         (colors_precomp, language_feature_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
          binningBuffer, imgBuffer) = ctx.saved_tensors
+        if grad_out_color is None and grad_out_language_feature is None and grad_depth is None:
+            return (None,) * 10
+        if grad_out_color is None:
+            grad_out_color = torch.zeros(ctx.out_shapes[0], device=means3D.device)
+        if grad_out_language_feature is None:
+            grad_out_language_feature = torch.zeros(ctx.out_shapes[1], device=means3D.device)
+        if grad_depth is None:
+            grad_depth = torch.Tensor([])  # NULL on the native side: "treated as zeros" (include/fdls_abi.h)
         native_args = (rs.bg, means3D, radii, colors_precomp, language_feature_precomp, scales, rotations,
                        rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
                        grad_out_color, grad_out_language_feature, grad_depth, sh, rs.sh_degree, rs.campos, geomBuffer,

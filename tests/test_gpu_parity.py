@@ -348,3 +348,35 @@ def test_full_size_backward(synth, name):
                      ("opacity", g.opacity, gr.opacity), ("means3D", g.means3D, gr.means3D), ("sh", g.sh, gr.sh),
                      ("scales", g.scales, gr.scales), ("rots", g.rots, gr.rots)):
         _assert_grad(a, b, "dL_d" + nm)
+
+
+def test_autograd_function_matches_native_backward(synth, fdls):
+    """The public autograd path (GaussianRasterizer -> loss.backward()) with an unused depth output -- its gradient
+    arrives as None and the depth terms are skipped -- equals the native backward fed explicit zero depth gradients."""
+    s = synth.scene("small")
+    dgr = fdls.diff_gaussian_rasterization
+    dcol, dlang, ddepth = synth.upstream_grads(s)
+    o = helpers.run_forward(s)
+    g = helpers.run_backward(s, o, dcol, dlang, ddepth)
+    t = lambda a, rg=False: torch.tensor(a, device="cuda", requires_grad=rg)
+    rs = dgr.GaussianRasterizationSettings(s.H, s.W, s.tanfovx, s.tanfovy, t(s.bg), 1.0, t(s.viewmatrix), t(s.projmatrix),
+                                           s.sh_degree, t(s.campos), False, False, True)
+    means3D, shs, lang = t(s.means3D, True), t(s.shs, True), t(s.language_feature, True)
+    opac, scales, rots = t(s.opacities, True), t(s.scales, True), t(s.rotations, True)
+    means2D = torch.zeros_like(means3D, requires_grad=True)
+    color, feat, radii, depth = dgr.GaussianRasterizer(rs)(means3D, means2D, opac, shs=shs, language_feature_precomp=lang,
+                                                             scales=scales, rotations=rots)
+    ((color * t(dcol)).sum() + (feat * t(dlang)).sum()).backward()
+    for nm, a, b in (("means3D", means3D.grad, g.means3D), ("means2D", means2D.grad, g.means2D), ("sh", shs.grad, g.sh),
+                     ("lang", lang.grad, g.lang), ("opacity", opac.grad, g.opacity), ("scales", scales.grad, g.scales),
+                     ("rots", rots.grad, g.rots)):
+        _assert_grad(a, b, "autograd dL_d" + nm)
+    # only the feature image used (fine-lang stage): colour gradient arrives as None
+    for x in (means3D, means2D, shs, lang, opac, scales, rots):
+        x.grad = None
+    color, feat, radii, depth = dgr.GaussianRasterizer(rs)(means3D, means2D, opac, shs=shs, language_feature_precomp=lang,
+                                                             scales=scales, rotations=rots)
+    (feat * t(dlang)).sum().backward()
+    g2 = helpers.run_backward(s, o, np.zeros_like(dcol), dlang, ddepth)
+    _assert_grad(lang.grad, g2.lang, "feature-only dL_dlang")
+    _assert_grad(opac.grad, g2.opacity, "feature-only dL_dopacity")
