@@ -164,9 +164,11 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
 def rasterize_gaussians_backward(background, means3D, radii, colors, language_feature, scales, rotations,
                                  scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
                                  dL_dout_color, dL_dout_language_feature, dL_dout_depth, sh, degree, campos, geomBuffer,
-                                 R, binningBuffer, imageBuffer, debug, include_feature):
+                                 R, binningBuffer, imageBuffer, debug, include_feature, want=None):
     """RasterizeGaussiansBackwardCUDA (rasterize_points.cu:131-235).  Returns (dL_dmeans2D, dL_dcolors,
-    dL_dlanguage_feature, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)."""
+    dL_dlanguage_feature, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations).
+    `want` (an addition; None = all, like the reference): 9 booleans in that order -- gradients not wanted are neither
+    allocated nor written (the C ABI takes a null pointer for them) and come back as None."""
     lib = _lib.load()
     means3D = _prep(means3D, "means3D")
     dev = means3D.device
@@ -186,15 +188,17 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, language_fe
     M = sh.size(1) if (sh is not None and sh.numel() > 0) else 0
     f32 = dict(dtype=torch.float32, device=dev)
     # every element of these is written by the backward kernels (zeros for culled Gaussians): no zero-fill pass
-    g_means3D = torch.empty((P, 3), **f32)
-    g_means2D = torch.empty((P, 3), **f32)
-    g_colors = torch.empty((P, 3), **f32)
-    g_lang = torch.empty((P, F), **f32) if include_feature else torch.zeros((1,), **f32)
-    g_opacity = torch.empty((P, 1), **f32)
-    g_cov3D = torch.empty((P, 6), **f32)
-    g_sh = torch.empty((P, M, 3), **f32) if M > 0 else torch.zeros((P, 0, 3), **f32)
-    g_scales = torch.empty((P, 3), **f32)
-    g_rot = torch.empty((P, 4), **f32)
+    w = (True,) * 9 if want is None else tuple(bool(x) for x in want)
+    E = lambda shape: torch.empty(shape, **f32)
+    g_means2D = E((P, 3)) if w[0] else None
+    g_colors = E((P, 3)) if w[1] else None
+    g_lang = (E((P, F)) if include_feature else torch.zeros((1,), **f32)) if w[2] else None
+    g_opacity = E((P, 1)) if w[3] else None
+    g_means3D = E((P, 3)) if w[4] else None
+    g_cov3D = E((P, 6)) if w[5] else None
+    g_sh = (E((P, M, 3)) if M > 0 else torch.zeros((P, 0, 3), **f32)) if w[6] else None
+    g_scales = E((P, 3)) if w[7] else None
+    g_rot = E((P, 4)) if w[8] else None
     if P == 0:
         return g_means2D, g_colors, g_lang, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rot
     gb = lib.fdls_grad_workspace_bytes(P)
@@ -211,11 +215,12 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, language_fe
     a.dL_dout_language = _ptr(dL_dout_language_feature) if include_feature else None
     a.dL_dout_depth = _ptr(dL_dout_depth)
     a.grad_ws, a.grad_bytes = grad_ws.data_ptr(), gb
-    a.dL_dmeans3D, a.dL_dmeans2D, a.dL_dcolors = g_means3D.data_ptr(), g_means2D.data_ptr(), g_colors.data_ptr()
-    a.dL_dsh = g_sh.data_ptr() if M > 0 else None
-    a.dL_dlanguage = g_lang.data_ptr() if include_feature else None
-    a.dL_dopacity, a.dL_dcov3D = g_opacity.data_ptr(), g_cov3D.data_ptr()
-    a.dL_dscales, a.dL_drotations = g_scales.data_ptr(), g_rot.data_ptr()
+    dp = lambda t: None if t is None else t.data_ptr()
+    a.dL_dmeans3D, a.dL_dmeans2D, a.dL_dcolors = dp(g_means3D), dp(g_means2D), dp(g_colors)
+    a.dL_dsh = dp(g_sh) if M > 0 else None
+    a.dL_dlanguage = dp(g_lang) if include_feature else None
+    a.dL_dopacity, a.dL_dcov3D = dp(g_opacity), dp(g_cov3D)
+    a.dL_dscales, a.dL_drotations = dp(g_scales), dp(g_rot)
     a.dL_dconic, a.dL_ddepths = None, None
     if profile["bwd"] is not None:
         a.stage_events = profile["bwd"]

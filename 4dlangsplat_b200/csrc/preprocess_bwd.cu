@@ -79,6 +79,8 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
   if (o.depths) o.depths[idx] = g[G_DEPTH];
   if (o.conic) reinterpret_cast<float4*>(o.conic)[idx] = make_float4(g[G_CA], g[G_CB], 0.f, g[G_CC]);
 
+  // nothing but pass-through gradients wanted (e.g. the fine-lang stage trains the language features only)
+  if (!o.means3D && !o.cov3D && !o.sh && !o.scales && !o.rots) return;
   float dL_dcov[6] = {0, 0, 0, 0, 0, 0};
   float3 dL_dmeans = {0, 0, 0};
   float dsc[3] = {0, 0, 0};

@@ -91,9 +91,14 @@ class _RasterizeGaussians(torch.autograd.Function):
                        rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
                        grad_out_color, grad_out_language_feature, grad_depth, sh, rs.sh_degree, rs.campos, geomBuffer,
                        ctx.num_rendered, binningBuffer, imgBuffer, rs.debug, rs.include_feature)
+        # inputs that do not require grad get None and their kernels' outputs are skipped (the fine-lang stage freezes
+        # everything but the language features, scene/gaussian_model.py:258-270); forward's input order is
+        # (means3D, means2D, sh, colors, lang, opacities, scales, rotations, cov3D, settings)
+        n = ctx.needs_input_grad
+        want = (n[1], n[3], n[4], n[5], n[0], n[8], n[2], n[6], n[7])
         (grad_means2D, grad_colors_precomp, grad_language_feature_precomp, grad_opacities, grad_means3D,
          grad_cov3Ds_precomp, grad_sh, grad_scales, grad_rotations) = _guarded(
-             _C.rasterize_gaussians_backward, native_args, rs.debug, "snapshot_bw.dump",
+             lambda *args: _C.rasterize_gaussians_backward(*args, want=want), native_args, rs.debug, "snapshot_bw.dump",
              "\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
         # input order of forward(); the settings get no gradient (ref :152-163)
         return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_language_feature_precomp,

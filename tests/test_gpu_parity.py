@@ -380,3 +380,10 @@ def test_autograd_function_matches_native_backward(synth, fdls):
     g2 = helpers.run_backward(s, o, np.zeros_like(dcol), dlang, ddepth)
     _assert_grad(lang.grad, g2.lang, "feature-only dL_dlang")
     _assert_grad(opac.grad, g2.opacity, "feature-only dL_dopacity")
+    # frozen inputs (fine-lang stage): only the language features require grad -> nothing else is computed or returned
+    lang2 = t(s.language_feature, True)
+    color, feat, radii, depth = dgr.GaussianRasterizer(rs)(t(s.means3D), None, t(s.opacities), shs=t(s.shs),
+                                                             language_feature_precomp=lang2, scales=t(s.scales),
+                                                             rotations=t(s.rotations))
+    (feat * t(dlang)).sum().backward()
+    _assert_grad(lang2.grad, g2.lang, "frozen-inputs dL_dlang")
