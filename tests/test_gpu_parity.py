@@ -387,3 +387,30 @@ def test_autograd_function_matches_native_backward(synth, fdls):
                                                              rotations=t(s.rotations))
     (feat * t(dlang)).sum().backward()
     _assert_grad(lang2.grad, g2.lang, "frozen-inputs dL_dlang")
+
+
+@pytest.mark.parametrize("F", [3, 6])
+def test_against_committed_golden_vectors(synth, F):
+    """The product path against tests/golden/ref_tiny_f{F}.npz (outputs of the reference CUDA build, committed): the
+    same bars as above, without needing oracle/_ref at run time."""
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_tiny_f%d.npz" % F)
+    gold = np.load(path)
+    s = synth.scene("tiny", F=F, bg=(1.0, 1.0, 1.0) if F == 3 else (0.0, 0.0, 0.0))
+    o = helpers.run_forward(s)
+    T = lambda a: torch.as_tensor(np.ascontiguousarray(a)).cuda()
+    assert o.R == int(gold["R"])
+    _assert_same(o.radii, T(gold["radii"]), "radii")
+    _assert_same(o.keys, T(gold["keys"].astype(np.int64)), "sorted keys")
+    _assert_same(o.point_list, T(gold["point_list"].astype(np.int32)), "sorted values")
+    _assert_same(o.ranges, T(gold["ranges"].astype(np.int32)), "tile ranges")
+    _assert_same(o.n_contrib, T(gold["n_contrib"].astype(np.int32)), "n_contrib")
+    _assert_same(o.final_T, T(gold["final_T"]), "final_T")
+    _assert_close(o.color, T(gold["color"]), IMG_RTOL, "color")
+    _assert_close(o.lang, T(gold["lang"]), IMG_RTOL, "language feature")
+    _assert_close(o.depth, T(gold["depth"]), IMG_RTOL, "depth")
+    dcol, dlang, ddepth = synth.upstream_grads(s, depth=True)
+    g = helpers.run_backward(s, o, dcol, dlang, ddepth)
+    for nm, a in (("means2D", g.means2D), ("colors", g.colors), ("lang", g.lang), ("opacity", g.opacity),
+                  ("means3D", g.means3D), ("cov3D", g.cov3D), ("sh", g.sh), ("scales", g.scales), ("rots", g.rots)):
+        _assert_grad(a, T(gold["g_" + nm]), "dL_d" + nm)
