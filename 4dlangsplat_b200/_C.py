@@ -69,8 +69,10 @@ def _round_capacity(n):
     return (n + g - 1) & ~(g - 1)
 
 
-def _stream():
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+def _stream(device=None):
+    """Raw cudaStream_t of torch's current stream (the fast private getter; torch.cuda.current_stream() costs ~14 us)."""
+    idx = device.index if (device is not None and device.index is not None) else torch.cuda.current_device()
+    return C.c_void_p(torch._C._cuda_getCurrentRawStream(idx))
 
 
 def rasterize_gaussians(background, means3D, colors, language_feature, opacity, scales, rotations, scale_modifier,
@@ -124,7 +126,7 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
     a.emit_keys = int(bool(emit_keys or debug))
     if profile["fwd"] is not None:
         a.stage_events = profile["fwd"]
-    stream = _stream()
+    stream = _stream(dev)
 
     def run_stage2(capacity, hint):
         bs = _sizes(P, W, H, capacity)[2] if capacity > 0 else 0
@@ -224,7 +226,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, language_fe
     a.dL_dconic, a.dL_ddepths = None, None
     if profile["bwd"] is not None:
         a.stage_events = profile["bwd"]
-    _lib.check(lib.fdls_backward(C.byref(a), _stream()), "fdls_backward")
+    _lib.check(lib.fdls_backward(C.byref(a), _stream(dev)), "fdls_backward")
     if debug:
         torch.cuda.current_stream().synchronize()
     return g_means2D, g_colors, g_lang, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rot

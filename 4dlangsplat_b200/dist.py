@@ -54,18 +54,17 @@ class GradBucket:
                 v.copy_(p.grad)
 
     def unpack(self):
+        """Point every .grad at its slice of the reduced bucket (no copy back; the slices stay valid until the next
+        pack(), i.e. until the next iteration's gradients exist)."""
         for p, v in zip(self.params, self.views):
-            if p.grad is None:
-                p.grad = v.clone()
-            else:
-                p.grad.copy_(v)
+            p.grad = v
 
     def all_reduce(self):
         """Sum the bucket over ranks (no-op for a single process).  Returns the bytes each rank contributed."""
-        self.pack()
         if world()[1] > 1:
+            self.pack()
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
-        self.unpack()
+            self.unpack()
         return self.flat.numel() * 4
 
 
