@@ -16,5 +16,6 @@ from . import _lib  # noqa: F401  (ctypes view of include/fdls_abi.h)
 _C = _il.import_module(__name__ + "._C")
 diff_gaussian_rasterization = _il.import_module(__name__ + ".diff_gaussian_rasterization")
 simple_knn = _il.import_module(__name__ + ".simple_knn")
+hexplane = _il.import_module(__name__ + ".hexplane")
 
-__all__ = ["_lib", "_C", "diff_gaussian_rasterization", "simple_knn"]
+__all__ = ["_lib", "_C", "diff_gaussian_rasterization", "simple_knn", "hexplane"]

@@ -70,6 +70,23 @@ class FdlsBwdArgs(C.Structure):
 
 
 # every symbol include/fdls_abi.h declares: name -> (restype, argtypes)
+FDLS_HEX_MAX_LEVELS = 4
+FDLS_HEX_PLANES = 6
+
+
+class FdlsHexArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("C", C.c_int32), ("L", C.c_int32),
+        ("reso", (C.c_int32 * 4) * FDLS_HEX_MAX_LEVELS),
+        ("pts", _f32p), ("time", _f32p), ("aabb", _f32p),
+        ("planes", (C.c_void_p * FDLS_HEX_PLANES) * FDLS_HEX_MAX_LEVELS),
+        ("out", _f32p),
+        ("dL_dout", _f32p),
+        ("dL_dplanes", (C.c_void_p * FDLS_HEX_PLANES) * FDLS_HEX_MAX_LEVELS),
+        ("dL_dpts", _f32p), ("dL_dtime", _f32p),
+    ]
+
+
 SYMBOLS = {
     "fdls_abi_version": (C.c_int, []),
     "fdls_kernel_launches": (C.c_uint64, []),
@@ -87,6 +104,10 @@ SYMBOLS = {
     "fdls_sort_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "fdls_sort_pairs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int,
                                   C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "fdls_hexplane_forward": (C.c_int, [C.POINTER(FdlsHexArgs), C.c_void_p]),
+    "fdls_hexplane_backward": (C.c_int, [C.POINTER(FdlsHexArgs), C.c_void_p]),
+    "fdls_hexplane_pack": (C.c_int, [C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fdls_hexplane_unpack_grad": (C.c_int, [C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
 _lib = None

@@ -56,6 +56,9 @@ cudaError_t launch_preprocess_bwd(const FdlsBwdArgs* a, const ViewParams& vp, co
 // knn.cu
 size_t knn_workspace_bytes(int N);
 int knn_dist2(int N, const float* xyz, float* out, void* ws, size_t ws_bytes, cudaStream_t st);
+int hexplane_forward(const FdlsHexArgs* a, cudaStream_t st);
+int hexplane_backward(const FdlsHexArgs* a, cudaStream_t st);
+int hexplane_transpose(bool pack, int C, int64_t HW, const float* in, float* out, cudaStream_t st);
 
 // rasterizer_impl.cu:35-50
 static uint32_t higher_msb(uint32_t n) {
@@ -351,6 +354,19 @@ FDLS_API int fdls_sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_
   if (n_max < 0 || (n_max > 0 && (!keys_a || !keys_b || !vals_a || !vals_b || !scratch))) return FDLS_EINVAL;
   return sort_pairs(keys_a, keys_b, vals_a, vals_b, n_max, n_dev, begin_bit, end_bit, scratch, scratch_bytes,
                     (cudaStream_t)stream);
+}
+
+FDLS_API int fdls_hexplane_forward(const FdlsHexArgs* a, void* stream) {
+  return hexplane_forward(a, (cudaStream_t)stream);
+}
+FDLS_API int fdls_hexplane_backward(const FdlsHexArgs* a, void* stream) {
+  return hexplane_backward(a, (cudaStream_t)stream);
+}
+FDLS_API int fdls_hexplane_pack(int32_t C, int64_t HW, const float* chw, float* hwc, void* stream) {
+  return hexplane_transpose(true, C, HW, chw, hwc, (cudaStream_t)stream);
+}
+FDLS_API int fdls_hexplane_unpack_grad(int32_t C, int64_t HW, const float* hwc, float* chw, void* stream) {
+  return hexplane_transpose(false, C, HW, hwc, chw, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -1,0 +1,292 @@
+// hexplane.cu -- the HexPlane feature field (first step), forward and backward as one kernel each.
+// Replaces HexPlaneField.get_density / interpolate_ms_features / grid_sample_wrapper (scene/hexplane.py:22-47,65-106,
+// 145-165): per level, product over the six coordinate planes of a bilinear, border-padded, align_corners=True
+// grid sample; levels concatenated.  The bilinear arithmetic follows torch's grid_sampler_2d (unnormalise, clip,
+// nw/ne/sw/se weights, accumulation order) so the forward agrees with the reference to the last bit or two.
+//
+// Work split: C/4 consecutive lanes per point, each lane owns one float4 of channels.  Planes are read from
+// channel-last (H,W,C) copies, so a corner is one 16-byte load per lane and 4*C contiguous bytes per point; the
+// plane set (~30 MB at the HyperNeRF configuration) lives in the 126 MB L2, the only HBM streams are the points in
+// and the features out (12 + 4 + 4*L*C bytes per point).
+#include "common.cuh"
+#include "../../include/fdls_abi.h"
+
+namespace fdls {
+
+constexpr int HX_THREADS = 256;
+// itertools.combinations(range(4), 2): xy, xz, xt, yz, yt, zt (hexplane.py:76-78); first index -> width, second -> height
+__host__ __device__ constexpr int hx_a0(int ci) { return ci < 3 ? 0 : (ci < 5 ? 1 : 2); }
+__host__ __device__ constexpr int hx_a1(int ci) { return ci < 3 ? ci + 1 : (ci < 5 ? ci - 1 : 3); }
+
+struct HxAxis {
+  float ix;    // unnormalised, border-clipped coordinate
+  float mult;  // d ix / d coord: (size-1)/2, or 0 where the clip is active
+  int i0;      // floor(ix)
+};
+
+// grid_sampler_unnormalize(align_corners=true) + clip_coordinates(_set_grad) of torch's GridSampler
+__device__ __forceinline__ HxAxis hx_axis(float coord, int size) {
+  HxAxis r;
+  r.ix = ((coord + 1.f) / 2) * (size - 1);
+  r.mult = (size - 1) / 2.f;
+  if (r.ix <= 0.f) {
+    r.ix = 0.f;
+    r.mult = 0.f;
+  } else {
+    const float mx = (float)(size - 1);
+    if (r.ix >= mx) {
+      r.ix = mx;
+      r.mult = 0.f;
+    }
+  }
+  r.i0 = (int)floorf(r.ix);
+  return r;
+}
+
+__device__ __forceinline__ float4 hx_ld(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float4 hx_mul(float4 a, float4 b) { return make_float4(a.x * b.x, a.y * b.y, a.z * b.z, a.w * b.w); }
+__device__ __forceinline__ void hx_fma(float4& acc, float4 v, float w) {
+  acc.x += v.x * w;
+  acc.y += v.y * w;
+  acc.z += v.z * w;
+  acc.w += v.w * w;
+}
+
+struct HxCorner {
+  float nw, ne, sw, se;  // weights
+  bool x1, y1;           // east column / south row inside the plane
+  int64_t o00;           // element offset of the nw corner (channel 0)
+  int64_t dx, dy;        // element strides to east / south
+};
+
+__device__ __forceinline__ HxCorner hx_corner(const HxAxis& u, const HxAxis& v, int Wd, int Hd, int C) {
+  HxCorner c;
+  const float x0 = (float)u.i0, y0 = (float)v.i0, x1 = x0 + 1.f, y1 = y0 + 1.f;
+  c.nw = (x1 - u.ix) * (y1 - v.ix);
+  c.ne = (u.ix - x0) * (y1 - v.ix);
+  c.sw = (x1 - u.ix) * (v.ix - y0);
+  c.se = (u.ix - x0) * (v.ix - y0);
+  c.x1 = u.i0 + 1 < Wd;
+  c.y1 = v.i0 + 1 < Hd;
+  c.o00 = ((int64_t)v.i0 * Wd + u.i0) * C;
+  c.dx = C;
+  c.dy = (int64_t)Wd * C;
+  return c;
+}
+
+__device__ __forceinline__ float4 hx_bilinear(const float* plane, const HxCorner& c) {
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float* b = plane + c.o00;
+  hx_fma(acc, hx_ld(b), c.nw);
+  if (c.x1) hx_fma(acc, hx_ld(b + c.dx), c.ne);
+  if (c.y1) hx_fma(acc, hx_ld(b + c.dy), c.sw);
+  if (c.x1 && c.y1) hx_fma(acc, hx_ld(b + c.dy + c.dx), c.se);
+  return acc;
+}
+
+// normalize_aabb (hexplane.py:20-21) as the three separate roundings torch performs (no FMA contraction)
+__device__ __forceinline__ void hx_coords(const FdlsHexArgs& a, int p, float (&c)[4], float (&scale)[3]) {
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const float lo = __ldg(a.aabb + k), hi = __ldg(a.aabb + 3 + k);
+    scale[k] = 2.0f / __fsub_rn(hi, lo);
+    c[k] = __fsub_rn(__fmul_rn(__fsub_rn(__ldg(a.pts + 3 * (size_t)p + k), lo), scale[k]), 1.0f);
+  }
+  c[3] = __ldg(a.time + p);
+}
+
+template <int G>
+__global__ void __launch_bounds__(HX_THREADS) hex_fwd_kernel(const __grid_constant__ FdlsHexArgs a) {
+  const int64_t t = (int64_t)blockIdx.x * HX_THREADS + threadIdx.x;
+  const int p = (int)(t / G), g = (int)(t % G);
+  if (p >= a.P) return;
+  const int C = 4 * G;
+  float c[4], scale[3];
+  hx_coords(a, p, c, scale);
+  for (int l = 0; l < a.L; ++l) {
+    HxAxis ax[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) ax[k] = hx_axis(c[k], a.reso[l][k]);
+    float4 f = make_float4(1.f, 1.f, 1.f, 1.f);
+#pragma unroll
+    for (int ci = 0; ci < 6; ++ci) {
+      const int a0 = hx_a0(ci), a1 = hx_a1(ci);
+      const HxCorner cr = hx_corner(ax[a0], ax[a1], a.reso[l][a0], a.reso[l][a1], C);
+      f = hx_mul(f, hx_bilinear(a.planes[l][ci] + 4 * g, cr));
+    }
+    *reinterpret_cast<float4*>(a.out + ((size_t)p * a.L + l) * C + 4 * g) = f;
+  }
+}
+
+__device__ __forceinline__ float hx_dot(float4 a, float4 b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
+__device__ __forceinline__ float4 hx_scale(float4 a, float s) { return make_float4(a.x * s, a.y * s, a.z * s, a.w * s); }
+
+template <int G>
+__global__ void __launch_bounds__(HX_THREADS) hex_bwd_kernel(const __grid_constant__ FdlsHexArgs a) {
+  const int64_t t = (int64_t)blockIdx.x * HX_THREADS + threadIdx.x;
+  const bool valid = t / G < a.P;
+  const int p = valid ? (int)(t / G) : a.P - 1, g = (int)(t % G);
+  const int C = 4 * G;
+  float c[4], scale[3];
+  hx_coords(a, p, c, scale);
+  float dcoord[4] = {0.f, 0.f, 0.f, 0.f};
+  const bool want_coord = a.dL_dpts != nullptr || a.dL_dtime != nullptr;
+  for (int l = 0; l < a.L; ++l) {
+    HxAxis ax[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) ax[k] = hx_axis(c[k], a.reso[l][k]);
+    // pass 1: the six interpolated vectors and their running products  pre[i] = f0 * ... * f(i-1)
+    float4 f[6], pre[6];
+    float4 run = make_float4(1.f, 1.f, 1.f, 1.f);
+#pragma unroll
+    for (int ci = 0; ci < 6; ++ci) {
+      const int a0 = hx_a0(ci), a1 = hx_a1(ci);
+      const HxCorner cr = hx_corner(ax[a0], ax[a1], a.reso[l][a0], a.reso[l][a1], C);
+      f[ci] = hx_bilinear(a.planes[l][ci] + 4 * g, cr);
+      pre[ci] = run;
+      run = hx_mul(run, f[ci]);
+    }
+    // pass 2, last plane first (the order autograd unwinds the chained product): d f_i = carry * pre_i
+    float4 carry = valid ? *reinterpret_cast<const float4*>(a.dL_dout + ((size_t)p * a.L + l) * C + 4 * g)
+                         : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int ci = 5; ci >= 0; --ci) {
+      const int a0 = hx_a0(ci), a1 = hx_a1(ci);
+      const float4 gf = hx_mul(carry, pre[ci]);
+      carry = hx_mul(carry, f[ci]);
+      const HxCorner cr = hx_corner(ax[a0], ax[a1], a.reso[l][a0], a.reso[l][a1], C);
+      float* gp = a.dL_dplanes[l][ci];
+      if (gp != nullptr && valid) {
+        float4* b = reinterpret_cast<float4*>(gp + cr.o00 + 4 * g);
+        atomicAdd(b, hx_scale(gf, cr.nw));
+        if (cr.x1) atomicAdd(b + cr.dx / 4, hx_scale(gf, cr.ne));
+        if (cr.y1) atomicAdd(b + cr.dy / 4, hx_scale(gf, cr.sw));
+        if (cr.x1 && cr.y1) atomicAdd(b + (cr.dy + cr.dx) / 4, hx_scale(gf, cr.se));
+      }
+      if (want_coord) {
+        const float* b = a.planes[l][ci] + cr.o00 + 4 * g;
+        const HxAxis &u = ax[a0], &v = ax[a1];
+        const float x0 = (float)u.i0, y0 = (float)v.i0, x1 = x0 + 1.f, y1 = y0 + 1.f;
+        float gix = 0.f, giy = 0.f;
+        {
+          const float d = hx_dot(hx_ld(b), gf);
+          gix -= d * (y1 - v.ix);
+          giy -= d * (x1 - u.ix);
+        }
+        if (cr.x1) {
+          const float d = hx_dot(hx_ld(b + cr.dx), gf);
+          gix += d * (y1 - v.ix);
+          giy -= d * (u.ix - x0);
+        }
+        if (cr.y1) {
+          const float d = hx_dot(hx_ld(b + cr.dy), gf);
+          gix -= d * (v.ix - y0);
+          giy += d * (x1 - u.ix);
+        }
+        if (cr.x1 && cr.y1) {
+          const float d = hx_dot(hx_ld(b + cr.dy + cr.dx), gf);
+          gix += d * (v.ix - y0);
+          giy += d * (u.ix - x0);
+        }
+        dcoord[a0] += u.mult * gix;
+        dcoord[a1] += v.mult * giy;
+      }
+    }
+  }
+  if (want_coord) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+#pragma unroll
+      for (int o = G / 2; o > 0; o >>= 1) dcoord[k] += __shfl_xor_sync(0xffffffffu, dcoord[k], o);
+    }
+    if (valid && g == 0) {
+      if (a.dL_dpts != nullptr) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) a.dL_dpts[3 * (size_t)p + k] = dcoord[k] * scale[k];
+      }
+      if (a.dL_dtime != nullptr) a.dL_dtime[p] = dcoord[3];
+    }
+  }
+}
+
+// (rows = C) x (cols = HW) row-major  <->  HW x C row-major; 256 columns per block through a padded shared tile.
+template <bool PACK>
+__global__ void __launch_bounds__(HX_THREADS) hex_transpose_kernel(int C, int64_t HW, const float* __restrict__ in,
+                                                                    float* __restrict__ out) {
+  extern __shared__ float s_t[];  // [256][C+1]
+  const int64_t hw0 = (int64_t)blockIdx.x * HX_THREADS;
+  const int n = (int)min((int64_t)HX_THREADS, HW - hw0);
+  const int tid = threadIdx.x;
+  if (PACK) {
+    if (tid < n)
+      for (int ch = 0; ch < C; ++ch) s_t[tid * (C + 1) + ch] = in[(size_t)ch * HW + hw0 + tid];
+    __syncthreads();
+    for (int i = tid; i < n * C; i += HX_THREADS) out[(size_t)hw0 * C + i] = s_t[(i / C) * (C + 1) + (i % C)];
+  } else {
+    for (int i = tid; i < n * C; i += HX_THREADS) s_t[(i / C) * (C + 1) + (i % C)] = in[(size_t)hw0 * C + i];
+    __syncthreads();
+    if (tid < n)
+      for (int ch = 0; ch < C; ++ch) out[(size_t)ch * HW + hw0 + tid] = s_t[tid * (C + 1) + ch];
+  }
+}
+
+static int hx_check(const FdlsHexArgs* a, bool bwd) {
+  if (!a || a->P < 0 || a->L < 1 || a->L > FDLS_HEX_MAX_LEVELS) return FDLS_EINVAL;
+  if (a->C != 4 && a->C != 8 && a->C != 16 && a->C != 32) return FDLS_EUNSUPPORTED;
+  if (a->P == 0) return FDLS_OK;
+  if (!a->pts || !a->time || !a->aabb) return FDLS_EINVAL;
+  if (!bwd && !a->out) return FDLS_EINVAL;
+  if (bwd && !a->dL_dout) return FDLS_EINVAL;
+  for (int l = 0; l < a->L; ++l) {
+    for (int k = 0; k < 4; ++k)
+      if (a->reso[l][k] < 1) return FDLS_EINVAL;
+    for (int ci = 0; ci < FDLS_HEX_PLANES; ++ci)
+      if (!a->planes[l][ci]) return FDLS_EINVAL;
+  }
+  return FDLS_OK;
+}
+
+template <bool BWD>
+static int hx_launch(const FdlsHexArgs* a, cudaStream_t st) {
+  const int G = a->C / 4;
+  const int blocks = cdiv((int64_t)a->P * G, HX_THREADS);
+  count_launch();
+#define HX_CASE(N)                                                \
+  case N:                                                         \
+    if (BWD)                                                      \
+      hex_bwd_kernel<N><<<blocks, HX_THREADS, 0, st>>>(*a);       \
+    else                                                          \
+      hex_fwd_kernel<N><<<blocks, HX_THREADS, 0, st>>>(*a);       \
+    break;
+  switch (G) { HX_CASE(1) HX_CASE(2) HX_CASE(4) HX_CASE(8) }
+#undef HX_CASE
+  return cudaGetLastError() == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
+}
+
+int hexplane_forward(const FdlsHexArgs* a, cudaStream_t st) {
+  const int rc = hx_check(a, false);
+  if (rc != FDLS_OK || a->P == 0) return rc;
+  return hx_launch<false>(a, st);
+}
+
+int hexplane_backward(const FdlsHexArgs* a, cudaStream_t st) {
+  const int rc = hx_check(a, true);
+  if (rc != FDLS_OK || a->P == 0) return rc;
+  return hx_launch<true>(a, st);
+}
+
+int hexplane_transpose(bool pack, int C, int64_t HW, const float* in, float* out, cudaStream_t st) {
+  if (C < 1 || C > 64 || HW < 0) return FDLS_EINVAL;
+  if (HW == 0) return FDLS_OK;
+  if (!in || !out) return FDLS_EINVAL;
+  const int blocks = cdiv(HW, HX_THREADS);
+  const size_t smem = (size_t)HX_THREADS * (C + 1) * sizeof(float);
+  count_launch();
+  if (pack)
+    hex_transpose_kernel<true><<<blocks, HX_THREADS, smem, st>>>(C, HW, in, out);
+  else
+    hex_transpose_kernel<false><<<blocks, HX_THREADS, smem, st>>>(C, HW, in, out);
+  return cudaGetLastError() == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
+}
+
+}  // namespace fdls

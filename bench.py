@@ -585,6 +585,125 @@ def main_train(a, rank, world, local, warmup):
         dist.destroy_process_group()
 
 
+def main_hexplane(a, rank, world, local, warmup):
+    """SURVEY 8f N1 (first step): the HexPlane feature field in front of the rasterizer, HyperNeRF configuration
+    (arguments/hypernerf/default.py:1-15: 16 channels, [64,64,64,150], multires [1,2,4]) over cfg2's 300k Gaussians.
+    One frame = features of every Gaussian at one timestamp; one step = the 100-timestamp sweep.  `--impl reference`
+    runs the reference's own op sequence (scene/hexplane.py:65-106: 18 F.grid_sample + 18 products + cat) with stock
+    torch on the same GPU.  Extra keys time forward+backward (all planes + points trainable)."""
+    import itertools
+    import torch.nn.functional as F
+    fd = importlib.import_module("4dlangsplat_b200")
+    dev = torch.device("cuda", local)
+    P, Cc, reso, multires = 300_000, 16, [64, 64, 64, 150], [1, 2, 4]
+    torch.manual_seed(7)
+    cfg = dict(grid_dimensions=2, input_coordinate_dim=4, output_coordinate_dim=Cc, resolution=reso)
+    field = fd.hexplane.HexPlaneField(1.6, cfg, multires).to(dev)
+    with torch.no_grad():
+        for lv in field.grids:
+            for p in lv:
+                p.add_(0.3 * torch.randn_like(p))
+    gen = torch.Generator(device="cpu").manual_seed(11)
+    pts_h = (torch.rand(P, 3, generator=gen) * 3.0 - 1.5).pin_memory()
+    pts = pts_h.to(dev)
+    mine = [t for t in range(N_TIMESTAMPS) if t % world == rank]
+    times_h = [torch.full((P, 1), 2.0 * t / (N_TIMESTAMPS - 1) - 1.0).pin_memory() for t in mine]
+    times = [t.to(dev) for t in times_h]
+    combs = list(itertools.combinations(range(4), 2))
+
+    def ref_forward(p3, tm):
+        q = torch.cat([(p3 - field.aabb[0]) * (2.0 / (field.aabb[1] - field.aabb[0])) - 1.0, tm], dim=-1)
+        feats = []
+        for level in field.grids:
+            space = 1.0
+            for ci, comb in enumerate(combs):
+                o = F.grid_sample(level[ci], q[..., list(comb)].view(1, 1, -1, 2), align_corners=True, mode="bilinear",
+                                  padding_mode="border")
+                space = space * o.view(level[ci].shape[1], -1).t()
+            feats.append(space)
+        return torch.cat(feats, dim=-1)
+
+    fwd = (lambda p3, tm: field(p3, tm)) if a.impl == "ours" else ref_forward
+    lib = fd._lib.load()
+
+    def sweep(train):
+        for tm in times:
+            if train:
+                p3 = pts.detach().requires_grad_(True)
+                fwd(p3, tm).backward(g_out)
+                for q in field.parameters():
+                    q.grad = None
+            else:
+                with torch.no_grad():
+                    fwd(pts, tm)
+
+    g_out = torch.randn(P, field.feat_dim, device=dev)
+    res = {}
+    for train in (False, True):
+        for _ in range(warmup):
+            sweep(train)
+        barrier(world)
+        l0 = lib.fdls_kernel_launches()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler = ClockSampler(local)
+        sampler.start()
+        e0.record()
+        for _ in range(a.steps):
+            sweep(train)
+        e1.record()
+        barrier(world)
+        res[train] = (max_over_ranks(e0.elapsed_time(e1), world), lib.fdls_kernel_launches() - l0, sampler.result())
+    # end to end: points + time column uploaded from pinned memory every frame, a 4-byte checksum read back
+    up = torch.empty(P, 4, device=dev)
+    chk = torch.zeros(1, dtype=torch.float32).pin_memory()
+    barrier(world)
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        for th in times_h:
+            up[:, :3].copy_(pts_h, non_blocking=True)
+            up[:, 3:].copy_(th, non_blocking=True)
+            with torch.no_grad():
+                chk.copy_(fwd(up[:, :3], up[:, 3:]).sum().reshape(1), non_blocking=True)
+        torch.cuda.synchronize()
+    barrier(world)
+    e2e_s = max_over_ranks(time.perf_counter() - t0, world)
+    n_frames = len(times) * a.steps
+    total = sum_over_ranks(n_frames, world)
+    ms, launches, clocks = res[False]
+    pk, pk_kind = peaks()
+    bytes_frame = P * (12 + 4 + 4 * field.feat_dim)
+    per_launch_ms = ms / n_frames
+    line = {"metric": "hexplane_frames_per_s", "value": round(total / (ms * 1e-3), 2), "unit": "frames/s",
+            "n_gpus": world, "steps": a.steps, "warmup": warmup, "ms_per_step": round(ms / a.steps, 4),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "hexplane: %d points x %d timestamps per step, %d channels, resolution %s, multires %s "
+                                   "(HyperNeRF configuration), forward" % (P, N_TIMESTAMPS, Cc, reso, multires),
+                       "l2": "outputs (58 MB per frame) stream through HBM; the 30 MB plane set is L2-resident by design",
+                       "sharding": "timestamps round-robin over ranks, no collective"},
+            "clocks": clocks,
+            "e2e": {"value": round(total / e2e_s, 2), "unit": "frames/s", "h2d_bytes_per_step": 16 * P * len(times),
+                    "d2h_bytes_per_step": 4 * len(times)},
+            "gpu_launches": int(launches),
+            "train": {"metric": "hexplane_fwd_bwd_frames_per_s", "value": round(total / (res[True][0] * 1e-3), 2),
+                      "gpu_launches": int(res[True][1])}}
+    if a.impl == "ours":
+        ach = bytes_frame / (per_launch_ms * 1e-3) / 1e9
+        line["roofline"] = {"bound": "hbm", "kernel": "hex_fwd_kernel", "achieved": round(ach, 1),
+                            "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": round(ach / pk["hbm_gbs"], 4), "traffic": None,
+                            "peak_source": pk_kind, "algorithmic_bytes_per_launch": bytes_frame,
+                            "avg_launch_ms": round(per_launch_ms, 4)}
+    else:
+        line["impl"] = "reference"
+        line["cpu_baseline"] = {"value": line["value"], "unit": "frames/s", "cores": 1, "kind": "port",
+                                "sample": "the reference's op sequence (18 grid_sample + 18 products + cat per frame) "
+                                          "on stock torch CUDA kernels, same GPU, same %d frames" % n_frames}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -593,7 +712,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--mode", default="render", choices=["render", "train"],
+    ap.add_argument("--mode", default="render", choices=["render", "train", "hexplane"],
                     help="render: forward sweep (headline, cfg2); train: fwd+bwd over a batch of 4 views (cfg3)")
     a = ap.parse_args()
     if not torch.cuda.is_available():
@@ -605,6 +724,8 @@ def main():
         os.environ["WORLD_SIZE"], os.environ["LOCAL_RANK"] = "1", "0"
     rank, world, local = dist_setup(a.gpus)
     warmup = max(3, a.warmup)
+    if a.mode == "hexplane":
+        return main_hexplane(a, rank, world, local, warmup)
     if a.mode == "train" or a.workload in ("cfg3",):
         return main_train(a, rank, world, local, warmup)
     wl = Workload(a.workload, rank, world)

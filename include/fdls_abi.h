@@ -206,6 +206,41 @@ int fdls_sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32
                     const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes,
                     void* stream);
 
+/* ---- SURVEY 8f N1, first step: the HexPlane feature field that feeds the deformation network ----------------------
+ * Replaces HexPlaneField.forward / get_density (scene/hexplane.py:145-170): normalize_aabb (:20-21), then per
+ * resolution level the PRODUCT over the six coordinate planes (xy, xz, xt, yz, yt, zt; itertools.combinations order,
+ * :76-78) of a bilinear F.grid_sample(align_corners=True, padding_mode='border') (:22-47), levels concatenated
+ * (:80-106).  The reference issues 6*L grid_sample launches + 6*L products + a cat and as many backward nodes; here
+ * one kernel per direction.
+ *
+ * Plane storage: the reference parameter is (1, C, H, W) with W = reso[first coord], H = reso[second coord]
+ * (init_grid_param, :60-62).  The kernels read CHANNEL-LAST copies (H, W, C): a bilinear corner is then one 4*C-byte
+ * vector instead of C scattered words.  fdls_hexplane_pack converts parameter -> channel-last (once per parameter
+ * update); fdls_hexplane_unpack_grad converts the channel-last gradient back into the parameter's layout. */
+#define FDLS_HEX_MAX_LEVELS 4
+#define FDLS_HEX_PLANES 6
+typedef struct FdlsHexArgs {
+  int32_t P;      /* points */
+  int32_t C;      /* channels per plane (output_coordinate_dim): 4, 8, 16 or 32 */
+  int32_t L;      /* resolution levels (len(multires)), <= FDLS_HEX_MAX_LEVELS */
+  int32_t reso[FDLS_HEX_MAX_LEVELS][4]; /* per level: grid resolution along x, y, z, t */
+  const float* pts;   /* (P,3) world positions */
+  const float* time;  /* (P,1) time coordinate, used as given (already in [-1,1] grid units, hexplane.py:150-151) */
+  const float* aabb;  /* (2,3) device: aabb[0], aabb[1] of normalize_aabb */
+  const float* planes[FDLS_HEX_MAX_LEVELS][FDLS_HEX_PLANES]; /* channel-last (H,W,C) copies */
+  float* out;         /* forward: (P, L*C) features */
+  /* backward only (all optional = may be null): */
+  const float* dL_dout;  /* (P, L*C) */
+  float* dL_dplanes[FDLS_HEX_MAX_LEVELS][FDLS_HEX_PLANES]; /* channel-last, ACCUMULATED into (caller zero-fills) */
+  float* dL_dpts;        /* (P,3) written */
+  float* dL_dtime;       /* (P,1) written */
+} FdlsHexArgs;
+int fdls_hexplane_forward(const FdlsHexArgs* a, void* stream);
+int fdls_hexplane_backward(const FdlsHexArgs* a, void* stream);
+/* (C,H,W) -> (H,W,C) and back; plain tiled transposes of a C x (H*W) matrix. */
+int fdls_hexplane_pack(int32_t C, int64_t HW, const float* chw, float* hwc, void* stream);
+int fdls_hexplane_unpack_grad(int32_t C, int64_t HW, const float* hwc, float* chw, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -28,7 +28,8 @@ def test_struct_layouts_match_header(fdls):
     """Field names and order of the ctypes structs follow the header text."""
     hdr = open(os.path.join(ROOT, "include", "fdls_abi.h")).read()
     for cname, cls in (("FdlsFwdArgs", fdls._lib.FdlsFwdArgs), ("FdlsBwdArgs", fdls._lib.FdlsBwdArgs),
-                       ("FdlsLayout", fdls._lib.FdlsLayout), ("FdlsWorkspaceSizes", fdls._lib.FdlsWorkspaceSizes)):
+                       ("FdlsLayout", fdls._lib.FdlsLayout), ("FdlsWorkspaceSizes", fdls._lib.FdlsWorkspaceSizes),
+                       ("FdlsHexArgs", fdls._lib.FdlsHexArgs)):
         body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (cname, cname), hdr, re.S).group(1)
         body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
         names = []
@@ -37,7 +38,7 @@ def test_struct_layouts_match_header(fdls):
             if not stmt:
                 continue
             decl = re.sub(r"^(const\s+)?[A-Za-z_0-9]+\s*\**", "", stmt, count=1)
-            names += [n.strip().lstrip("*").strip() for n in decl.split(",")]
+            names += [re.sub(r"\[.*", "", n.strip().lstrip("*").strip()) for n in decl.split(",")]
         assert names == [f[0] for f in cls._fields_], cname
 
 
@@ -63,6 +64,13 @@ def test_null_and_bad_arguments_are_rejected_without_touching_the_gpu(fdls):
     assert lib.fdls_backward(C.byref(b), None) == -1
     assert lib.fdls_sort_pairs(None, None, None, None, 10, None, 0, 32, None, 0, None) == -1
     assert lib.fdls_knn_dist2(5, None, None, None, 0, None) == -1
+    h = fdls._lib.FdlsHexArgs()
+    assert lib.fdls_hexplane_forward(C.byref(h), None) == -1  # L = 0
+    h.L, h.C, h.P = 2, 12, 0
+    assert lib.fdls_hexplane_forward(C.byref(h), None) == -4  # C not in {4, 8, 16, 32}
+    h.C, h.P = 16, 5
+    assert lib.fdls_hexplane_backward(C.byref(h), None) == -1  # null pointers
+    assert lib.fdls_hexplane_pack(16, 10, None, None, None) == -1
 
 
 def test_python_surface_matches_reference(fdls):
