@@ -56,9 +56,13 @@ struct HxCorner {
   float nw, ne, sw, se;  // weights
   bool x1, y1;           // east column / south row inside the plane
   int64_t o00;           // element offset of the nw corner (channel 0)
-  int64_t dx, dy;        // element strides to east / south
+  int64_t dx, dy;        // element strides to east / south; 0 where that neighbour is outside the plane
 };
 
+// torch skips a corner that lies outside the plane.  With border clipping that only happens for the east column when
+// ix == W-1 exactly (and the south row when iy == H-1), where that corner's weight is exactly 0: reading the clamped
+// (= same) texel and adding value*0 gives the same sum for finite planes, and keeps the four loads unconditional so
+// all 24 of a level are in flight together.
 __device__ __forceinline__ HxCorner hx_corner(const HxAxis& u, const HxAxis& v, int Wd, int Hd, int C) {
   HxCorner c;
   const float x0 = (float)u.i0, y0 = (float)v.i0, x1 = x0 + 1.f, y1 = y0 + 1.f;
@@ -69,18 +73,19 @@ __device__ __forceinline__ HxCorner hx_corner(const HxAxis& u, const HxAxis& v, 
   c.x1 = u.i0 + 1 < Wd;
   c.y1 = v.i0 + 1 < Hd;
   c.o00 = ((int64_t)v.i0 * Wd + u.i0) * C;
-  c.dx = C;
-  c.dy = (int64_t)Wd * C;
+  c.dx = c.x1 ? C : 0;
+  c.dy = c.y1 ? (int64_t)Wd * C : 0;
   return c;
 }
 
 __device__ __forceinline__ float4 hx_bilinear(const float* plane, const HxCorner& c) {
-  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   const float* b = plane + c.o00;
-  hx_fma(acc, hx_ld(b), c.nw);
-  if (c.x1) hx_fma(acc, hx_ld(b + c.dx), c.ne);
-  if (c.y1) hx_fma(acc, hx_ld(b + c.dy), c.sw);
-  if (c.x1 && c.y1) hx_fma(acc, hx_ld(b + c.dy + c.dx), c.se);
+  const float4 vnw = hx_ld(b), vne = hx_ld(b + c.dx), vsw = hx_ld(b + c.dy), vse = hx_ld(b + c.dy + c.dx);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  hx_fma(acc, vnw, c.nw);
+  hx_fma(acc, vne, c.ne);
+  hx_fma(acc, vsw, c.sw);
+  hx_fma(acc, vse, c.se);
   return acc;
 }
 
@@ -161,32 +166,28 @@ __global__ void __launch_bounds__(HX_THREADS) hex_bwd_kernel(const __grid_consta
         atomicAdd(b, hx_scale(gf, cr.nw));
         if (cr.x1) atomicAdd(b + cr.dx / 4, hx_scale(gf, cr.ne));
         if (cr.y1) atomicAdd(b + cr.dy / 4, hx_scale(gf, cr.sw));
-        if (cr.x1 && cr.y1) atomicAdd(b + (cr.dy + cr.dx) / 4, hx_scale(gf, cr.se));
+        if (cr.x1 && cr.y1) atomicAdd(b + (cr.dy + cr.dx) / 4, hx_scale(gf, cr.se));  // dx, dy != 0 here
       }
       if (want_coord) {
         const float* b = a.planes[l][ci] + cr.o00 + 4 * g;
         const HxAxis &u = ax[a0], &v = ax[a1];
         const float x0 = (float)u.i0, y0 = (float)v.i0, x1 = x0 + 1.f, y1 = y0 + 1.f;
         float gix = 0.f, giy = 0.f;
-        {
-          const float d = hx_dot(hx_ld(b), gf);
-          gix -= d * (y1 - v.ix);
-          giy -= d * (x1 - u.ix);
-        }
+        const float dnw = hx_dot(hx_ld(b), gf), dne = hx_dot(hx_ld(b + cr.dx), gf);
+        const float dsw = hx_dot(hx_ld(b + cr.dy), gf), dse = hx_dot(hx_ld(b + cr.dy + cr.dx), gf);
+        gix -= dnw * (y1 - v.ix);
+        giy -= dnw * (x1 - u.ix);
         if (cr.x1) {
-          const float d = hx_dot(hx_ld(b + cr.dx), gf);
-          gix += d * (y1 - v.ix);
-          giy -= d * (u.ix - x0);
+          gix += dne * (y1 - v.ix);
+          giy -= dne * (u.ix - x0);
         }
         if (cr.y1) {
-          const float d = hx_dot(hx_ld(b + cr.dy), gf);
-          gix -= d * (v.ix - y0);
-          giy += d * (x1 - u.ix);
+          gix -= dsw * (v.ix - y0);
+          giy += dsw * (x1 - u.ix);
         }
         if (cr.x1 && cr.y1) {
-          const float d = hx_dot(hx_ld(b + cr.dy + cr.dx), gf);
-          gix += d * (v.ix - y0);
-          giy += d * (u.ix - x0);
+          gix += dse * (v.ix - y0);
+          giy += dse * (u.ix - x0);
         }
         dcoord[a0] += u.mult * gix;
         dcoord[a1] += v.mult * giy;

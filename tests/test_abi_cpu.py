@@ -108,3 +108,23 @@ def test_argument_validation_messages(fdls):
     with pytest.raises(RuntimeError, match="CUDA tensor"):
         r(m, m, torch.zeros(4, 1), colors_precomp=m, scales=m, rotations=torch.zeros(4, 4),
           language_feature_precomp=torch.zeros(4, 3))
+
+
+def test_hexplane_surface_matches_reference(fdls):
+    """Constructor, attributes and parameter shapes of scene/hexplane.py:109-143 (CPU: construction only)."""
+    import hexplane_b200 as top
+    cfg = dict(grid_dimensions=2, input_coordinate_dim=4, output_coordinate_dim=16, resolution=[64, 64, 64, 150])
+    f = top.HexPlaneField(1.6, cfg, [1, 2, 4])
+    assert top.HexPlaneField is fdls.hexplane.HexPlaneField
+    assert f.feat_dim == 48 and f.concat_features and len(f.grids) == 3 and all(len(lv) == 6 for lv in f.grids)
+    # xy, xz, xt, yz, yt, zt; (1, C, reso[second], reso[first]); only the spatial axes scale with the level
+    assert [tuple(p.shape) for p in f.grids[1]] == [(1, 16, 128, 128), (1, 16, 128, 128), (1, 16, 150, 128),
+                                                    (1, 16, 128, 128), (1, 16, 150, 128), (1, 16, 150, 128)]
+    assert all(bool((f.grids[0][ci] == 1).all()) for ci in (2, 4, 5))  # time planes start at exactly 1
+    assert all(0.1 <= float(f.grids[0][ci].detach().min()) and float(f.grids[0][ci].detach().max()) <= 0.5 for ci in (0, 1, 3))
+    assert sorted(f.state_dict()) == sorted(["aabb"] + ["grids.%d.%d" % (l, c) for l in range(3) for c in range(6)])
+    assert not f.aabb.requires_grad and f.aabb.tolist() == [[1.6000000238418579] * 3, [-1.6000000238418579] * 3]
+    f.set_aabb([1.0, 2.0, 3.0], [-1.0, -2.0, -3.0])
+    assert [t.tolist() for t in f.get_aabb] == [[1.0, 2.0, 3.0], [-1.0, -2.0, -3.0]]
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        f(torch.zeros(4, 3), torch.zeros(4, 1))
