@@ -108,6 +108,10 @@ SYMBOLS = {
     "fdls_hexplane_backward": (C.c_int, [C.POINTER(FdlsHexArgs), C.c_void_p]),
     "fdls_hexplane_pack": (C.c_int, [C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fdls_hexplane_unpack_grad": (C.c_int, [C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fdls_hexplane_pack_batch": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_void_p),
+                                           C.POINTER(C.c_void_p), C.c_void_p]),
+    "fdls_hexplane_unpack_grad_batch": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_void_p),
+                                                  C.POINTER(C.c_void_p), C.c_void_p]),
 }
 
 _lib = None

@@ -58,7 +58,8 @@ size_t knn_workspace_bytes(int N);
 int knn_dist2(int N, const float* xyz, float* out, void* ws, size_t ws_bytes, cudaStream_t st);
 int hexplane_forward(const FdlsHexArgs* a, cudaStream_t st);
 int hexplane_backward(const FdlsHexArgs* a, cudaStream_t st);
-int hexplane_transpose(bool pack, int C, int64_t HW, const float* in, float* out, cudaStream_t st);
+int hexplane_transpose(bool pack, int n, int C, const int64_t* HW, const float* const* in, float* const* out,
+                       cudaStream_t st);
 
 // rasterizer_impl.cu:35-50
 static uint32_t higher_msb(uint32_t n) {
@@ -363,10 +364,18 @@ FDLS_API int fdls_hexplane_backward(const FdlsHexArgs* a, void* stream) {
   return hexplane_backward(a, (cudaStream_t)stream);
 }
 FDLS_API int fdls_hexplane_pack(int32_t C, int64_t HW, const float* chw, float* hwc, void* stream) {
-  return hexplane_transpose(true, C, HW, chw, hwc, (cudaStream_t)stream);
+  return hexplane_transpose(true, 1, C, &HW, &chw, &hwc, (cudaStream_t)stream);
 }
 FDLS_API int fdls_hexplane_unpack_grad(int32_t C, int64_t HW, const float* hwc, float* chw, void* stream) {
-  return hexplane_transpose(false, C, HW, hwc, chw, (cudaStream_t)stream);
+  return hexplane_transpose(false, 1, C, &HW, &hwc, &chw, (cudaStream_t)stream);
+}
+FDLS_API int fdls_hexplane_pack_batch(int32_t n, int32_t C, const int64_t* HW, const float* const* chw,
+                                      float* const* hwc, void* stream) {
+  return hexplane_transpose(true, n, C, HW, chw, hwc, (cudaStream_t)stream);
+}
+FDLS_API int fdls_hexplane_unpack_grad_batch(int32_t n, int32_t C, const int64_t* HW, const float* const* hwc,
+                                             float* const* chw, void* stream) {
+  return hexplane_transpose(false, n, C, HW, hwc, chw, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -140,25 +140,25 @@ __global__ void __launch_bounds__(HX_THREADS) hex_bwd_kernel(const __grid_consta
     HxAxis ax[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) ax[k] = hx_axis(c[k], a.reso[l][k]);
-    // pass 1: the six interpolated vectors and their running products  pre[i] = f0 * ... * f(i-1)
-    float4 f[6], pre[6];
-    float4 run = make_float4(1.f, 1.f, 1.f, 1.f);
+    // pass 1: the six interpolated vectors
+    float4 f[6];
 #pragma unroll
     for (int ci = 0; ci < 6; ++ci) {
       const int a0 = hx_a0(ci), a1 = hx_a1(ci);
       const HxCorner cr = hx_corner(ax[a0], ax[a1], a.reso[l][a0], a.reso[l][a1], C);
       f[ci] = hx_bilinear(a.planes[l][ci] + 4 * g, cr);
-      pre[ci] = run;
-      run = hx_mul(run, f[ci]);
     }
-    // pass 2, last plane first (the order autograd unwinds the chained product): d f_i = carry * pre_i
-    float4 carry = valid ? *reinterpret_cast<const float4*>(a.dL_dout + ((size_t)p * a.L + l) * C + 4 * g)
-                         : make_float4(0.f, 0.f, 0.f, 0.f);
+    // pass 2: d f_i = dL_dout * prod_{j != i} f_j (recomputed per plane: 4 multiplies are cheaper than holding the
+    // prefix products in registers), then the plane atomics and the coordinate gradients
+    const float4 go = valid ? *reinterpret_cast<const float4*>(a.dL_dout + ((size_t)p * a.L + l) * C + 4 * g)
+                            : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int ci = 5; ci >= 0; --ci) {
       const int a0 = hx_a0(ci), a1 = hx_a1(ci);
-      const float4 gf = hx_mul(carry, pre[ci]);
-      carry = hx_mul(carry, f[ci]);
+      float4 gf = go;
+#pragma unroll
+      for (int cj = 5; cj >= 0; --cj)
+        if (cj != ci) gf = hx_mul(gf, f[cj]);
       const HxCorner cr = hx_corner(ax[a0], ax[a1], a.reso[l][a0], a.reso[l][a1], C);
       float* gp = a.dL_dplanes[l][ci];
       if (gp != nullptr && valid) {
@@ -210,12 +210,27 @@ __global__ void __launch_bounds__(HX_THREADS) hex_bwd_kernel(const __grid_consta
   }
 }
 
-// (rows = C) x (cols = HW) row-major  <->  HW x C row-major; 256 columns per block through a padded shared tile.
+// (rows = C) x (cols = HW) row-major  <->  HW x C row-major for up to 24 planes in ONE launch (a level set has 18;
+// one 5 us launch per plane would cost more than the backward's atomics).  256 columns per block through a padded
+// shared tile; blk0[] is the running block count, so a block finds its plane with a short scan.
+struct HxBatch {
+  int n, C;
+  int64_t hw[FDLS_HEX_MAX_LEVELS * FDLS_HEX_PLANES];
+  const float* in[FDLS_HEX_MAX_LEVELS * FDLS_HEX_PLANES];
+  float* out[FDLS_HEX_MAX_LEVELS * FDLS_HEX_PLANES];
+  int blk0[FDLS_HEX_MAX_LEVELS * FDLS_HEX_PLANES + 1];
+};
+
 template <bool PACK>
-__global__ void __launch_bounds__(HX_THREADS) hex_transpose_kernel(int C, int64_t HW, const float* __restrict__ in,
-                                                                    float* __restrict__ out) {
+__global__ void __launch_bounds__(HX_THREADS) hex_transpose_kernel(const __grid_constant__ HxBatch b) {
   extern __shared__ float s_t[];  // [256][C+1]
-  const int64_t hw0 = (int64_t)blockIdx.x * HX_THREADS;
+  int k = 0;
+  while (k + 1 < b.n && (int)blockIdx.x >= b.blk0[k + 1]) ++k;
+  const int C = b.C;
+  const int64_t HW = b.hw[k];
+  const float* __restrict__ in = b.in[k];
+  float* __restrict__ out = b.out[k];
+  const int64_t hw0 = (int64_t)(blockIdx.x - b.blk0[k]) * HX_THREADS;
   const int n = (int)min((int64_t)HX_THREADS, HW - hw0);
   const int tid = threadIdx.x;
   if (PACK) {
@@ -276,17 +291,31 @@ int hexplane_backward(const FdlsHexArgs* a, cudaStream_t st) {
   return hx_launch<true>(a, st);
 }
 
-int hexplane_transpose(bool pack, int C, int64_t HW, const float* in, float* out, cudaStream_t st) {
-  if (C < 1 || C > 64 || HW < 0) return FDLS_EINVAL;
-  if (HW == 0) return FDLS_OK;
-  if (!in || !out) return FDLS_EINVAL;
-  const int blocks = cdiv(HW, HX_THREADS);
+int hexplane_transpose(bool pack, int n, int C, const int64_t* HW, const float* const* in, float* const* out,
+                       cudaStream_t st) {
+  if (C < 1 || C > 64 || n < 0 || n > FDLS_HEX_MAX_LEVELS * FDLS_HEX_PLANES) return FDLS_EINVAL;
+  if (n > 0 && (!HW || !in || !out)) return FDLS_EINVAL;
+  HxBatch b;
+  b.n = 0;
+  b.C = C;
+  b.blk0[0] = 0;
+  for (int i = 0; i < n; ++i) {
+    if (HW[i] < 0) return FDLS_EINVAL;
+    if (HW[i] == 0) continue;
+    if (!in[i] || !out[i]) return FDLS_EINVAL;
+    b.hw[b.n] = HW[i];
+    b.in[b.n] = in[i];
+    b.out[b.n] = out[i];
+    b.blk0[b.n + 1] = b.blk0[b.n] + cdiv(HW[i], HX_THREADS);
+    ++b.n;
+  }
+  if (b.n == 0) return FDLS_OK;
   const size_t smem = (size_t)HX_THREADS * (C + 1) * sizeof(float);
   count_launch();
   if (pack)
-    hex_transpose_kernel<true><<<blocks, HX_THREADS, smem, st>>>(C, HW, in, out);
+    hex_transpose_kernel<true><<<b.blk0[b.n], HX_THREADS, smem, st>>>(b);
   else
-    hex_transpose_kernel<false><<<blocks, HX_THREADS, smem, st>>>(C, HW, in, out);
+    hex_transpose_kernel<false><<<b.blk0[b.n], HX_THREADS, smem, st>>>(b);
   return cudaGetLastError() == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
 }
 

@@ -52,24 +52,42 @@ def init_grid_param(grid_nd: int, in_dim: int, out_dim: int, reso: Sequence[int]
     return grid_coefs
 
 
-def _pack(plane):
-    """Channel-last (H, W, C) copy of a (1, C, H, W) plane, cached per parameter version."""
-    if not plane.is_cuda:
-        raise RuntimeError("HexPlane planes must be CUDA tensors (this build has no CPU path)")
-    src = plane.detach()
-    if src.dtype is not torch.float32 or not src.is_contiguous():
-        src = src.float().contiguous()
-    key = (src.data_ptr(), tuple(src.shape))
-    hit = _packed.get(key)
-    if hit is not None and hit[2]() is not plane:  # the address was recycled by another tensor
-        hit = None
-    if hit is not None and hit[0] == plane._version:
-        return hit[1]
-    _, Cc, H, W = src.shape
-    out = hit[1] if hit is not None else torch.empty(H, W, Cc, dtype=torch.float32, device=src.device)
-    _lib.check(_lib.load().fdls_hexplane_pack(Cc, H * W, src.data_ptr(), out.data_ptr(), _stream(src.device)),
-               "fdls_hexplane_pack")
-    _packed[key] = (plane._version, out, weakref.ref(plane))
+def _transpose_batch(fn_name, Cc, hw, src, dst, device):
+    n = len(hw)
+    if n == 0:
+        return
+    HW = (C.c_int64 * n)(*hw)
+    a = (C.c_void_p * n)(*[t.data_ptr() for t in src])
+    b = (C.c_void_p * n)(*[t.data_ptr() for t in dst])
+    _lib.check(getattr(_lib.load(), fn_name)(n, Cc, HW, a, b, _stream(device)), fn_name)
+
+
+def _pack_all(planes):
+    """Channel-last (H, W, C) copies of (1, C, H, W) planes, cached per parameter version; every stale plane is
+    converted in ONE launch (fdls_hexplane_pack_batch)."""
+    out, stale = [], []
+    for plane in planes:
+        if not plane.is_cuda:
+            raise RuntimeError("HexPlane planes must be CUDA tensors (this build has no CPU path)")
+        src = plane.detach()
+        if src.dtype is not torch.float32 or not src.is_contiguous():
+            src = src.float().contiguous()
+        key = (src.data_ptr(), tuple(src.shape))
+        hit = _packed.get(key)
+        if hit is not None and hit[2]() is not plane:  # the address was recycled by another tensor
+            hit = None
+        if hit is not None and hit[0] == plane._version:
+            out.append(hit[1])
+            continue
+        _, Cc, H, W = src.shape
+        cl = hit[1] if hit is not None else torch.empty(H, W, Cc, dtype=torch.float32, device=src.device)
+        _packed[key] = (plane._version, cl, weakref.ref(plane))
+        stale.append((src, cl))
+        out.append(cl)
+    if stale:
+        Cc = stale[0][0].shape[1]
+        _transpose_batch("fdls_hexplane_pack_batch", Cc, [s.shape[2] * s.shape[3] for s, _ in stale],
+                         [s for s, _ in stale], [c for _, c in stale], stale[0][0].device)
     return out
 
 
@@ -92,7 +110,9 @@ class _HexPlaneFeatures(torch.autograd.Function):
         # plane ci of a level is (1, C, reso[a1], reso[a0]) for (a0, a1) in xy, xz, xt, yz, yt, zt
         reso = [(planes[l * 6 + 0].shape[3], planes[l * 6 + 0].shape[2], planes[l * 6 + 1].shape[2],
                  planes[l * 6 + 2].shape[2]) for l in range(L)]
-        packed = [_pack(p) for p in planes]
+        if any(p.shape[1] != Cc for p in planes):
+            raise NotImplementedError("all planes must have the same channel count")
+        packed = _pack_all(planes)
         out = torch.empty(pts.shape[0], L * Cc, dtype=torch.float32, device=pts.device)
         a = _args(pts, time, aabb, packed, L, Cc, reso)
         a.out = out.data_ptr()
@@ -126,16 +146,11 @@ class _HexPlaneFeatures(torch.autograd.Function):
                 a.dL_dplanes[i // 6][i % 6] = g_cl[i].data_ptr()
         st = _stream(pts.device)
         _lib.check(_lib.load().fdls_hexplane_backward(C.byref(a), st), "fdls_hexplane_backward")
-        g_planes = []
-        for i in range(len(packed)):
-            if g_cl[i] is None:
-                g_planes.append(None)
-                continue
-            _, c, H, W = shapes[i]
-            g = torch.empty(shapes[i], dtype=torch.float32, device=pts.device)
-            _lib.check(_lib.load().fdls_hexplane_unpack_grad(c, H * W, g_cl[i].data_ptr(), g.data_ptr(), st),
-                       "fdls_hexplane_unpack_grad")
-            g_planes.append(g)
+        g_planes = [None] * len(packed)
+        for i in want:
+            g_planes[i] = torch.empty(shapes[i], dtype=torch.float32, device=pts.device)
+        _transpose_batch("fdls_hexplane_unpack_grad_batch", Cc, [shapes[i][2] * shapes[i][3] for i in want],
+                         [g_cl[i] for i in want], [g_planes[i] for i in want], pts.device)
         return (g_pts, g_time, None, None, *g_planes)
 
 

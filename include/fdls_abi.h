@@ -240,6 +240,12 @@ int fdls_hexplane_backward(const FdlsHexArgs* a, void* stream);
 /* (C,H,W) -> (H,W,C) and back; plain tiled transposes of a C x (H*W) matrix. */
 int fdls_hexplane_pack(int32_t C, int64_t HW, const float* chw, float* hwc, void* stream);
 int fdls_hexplane_unpack_grad(int32_t C, int64_t HW, const float* hwc, float* chw, void* stream);
+/* The same for n <= FDLS_HEX_MAX_LEVELS*FDLS_HEX_PLANES planes of C channels in ONE launch; HW, the source and the
+ * destination pointers are HOST arrays of n entries (entries with HW == 0 are skipped). */
+int fdls_hexplane_pack_batch(int32_t n, int32_t C, const int64_t* HW, const float* const* chw, float* const* hwc,
+                             void* stream);
+int fdls_hexplane_unpack_grad_batch(int32_t n, int32_t C, const int64_t* HW, const float* const* hwc,
+                                    float* const* chw, void* stream);
 
 #ifdef __cplusplus
 }

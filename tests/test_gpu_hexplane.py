@@ -149,3 +149,16 @@ def test_pack_unpack_round_trip(fdls):
         _lib.check(lib.fdls_hexplane_unpack_grad(C_, H * W, cl.data_ptr(), back.data_ptr(), st), "unpack")
         assert torch.equal(cl, x[0].permute(1, 2, 0).contiguous())
         assert torch.equal(back, x)
+    # batched form: three planes of different sizes (one empty) in one launch
+    import ctypes as C
+    xs = [torch.randn(1, 16, h, w, device=dev) for h, w in ((150, 64), (3, 0), (257, 300))]
+    cls = [torch.empty(x.shape[2], x.shape[3], 16, device=dev) for x in xs]
+    HW = (C.c_int64 * 3)(*[x.shape[2] * x.shape[3] for x in xs])
+    src = (C.c_void_p * 3)(*[x.data_ptr() for x in xs])
+    dst = (C.c_void_p * 3)(*[c.data_ptr() for c in cls])
+    _lib.check(lib.fdls_hexplane_pack_batch(3, 16, HW, src, dst, fdls._C._stream(dev)), "pack_batch")
+    backs = [torch.empty_like(x) for x in xs]
+    bk = (C.c_void_p * 3)(*[b.data_ptr() for b in backs])
+    _lib.check(lib.fdls_hexplane_unpack_grad_batch(3, 16, HW, dst, bk, fdls._C._stream(dev)), "unpack_batch")
+    for x, c, b in zip(xs, cls, backs):
+        assert torch.equal(c, x[0].permute(1, 2, 0).contiguous()) and torch.equal(b, x)
