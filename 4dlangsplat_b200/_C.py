@@ -30,9 +30,20 @@ def _dev_state(device):
     key = device.index if device.index is not None else torch.cuda.current_device()
     st = _state.get(key)
     if st is None:
-        st = {"pinned": torch.zeros(2, dtype=torch.int32).pin_memory(), "last_R": None, "grad_ws": None}
+        st = {"last_R": None, "streams": {}}
         _state[key] = st
     return st
+
+
+def _stream_state(st, stream):
+    """Per (device, stream): the pinned {R, overflow} pair the scan kernel stores into, and the event the host waits
+    on.  Frames issued on different streams (a render sweep alternating two streams overlaps one frame's
+    latency-bound preprocess/sort/scan with the previous frame's compositor) must not share them."""
+    ss = st["streams"].get(stream.value)
+    if ss is None:
+        ss = {"pinned": torch.zeros(2, dtype=torch.int32).pin_memory(), "event": torch.cuda.Event()}
+        st["streams"][stream.value] = ss
+    return ss
 
 
 def _ptr(t):
@@ -120,13 +131,14 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
     a.out_color, a.out_depth, a.radii = out_color.data_ptr(), out_depth.data_ptr(), radii.data_ptr()
     a.out_language = out_lang.data_ptr() if include_feature else None
     a.geom_ws, a.geom_bytes, a.img_ws, a.img_bytes = geom.data_ptr(), geom_bytes, img.data_ptr(), img_bytes
-    a.num_rendered_host = st["pinned"].data_ptr()
+    stream = _stream(dev)
+    ss = _stream_state(st, stream)
+    a.num_rendered_host = ss["pinned"].data_ptr()
     a.num_rendered_hint = -1
     a.binning_algo = 1 if os.environ.get("FDLS_BINNING", "partition") == "onesweep" else 0
     a.emit_keys = int(bool(emit_keys or debug))
     if profile["fwd"] is not None:
         a.stage_events = profile["fwd"]
-    stream = _stream(dev)
 
     def run_stage2(capacity, hint):
         bs = _sizes(P, W, H, capacity)[2] if capacity > 0 else 0
@@ -142,19 +154,17 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
         capacity = _round_capacity(st["last_R"] * 1.25 + 4096)
         a.capacity = capacity
         _lib.check(lib.fdls_preprocess(C.byref(a), stream), "fdls_preprocess")
-        ev = st.get("event")
-        if ev is None:
-            ev = st["event"] = torch.cuda.Event()
+        ev = ss["event"]
         ev.record()
         binning = run_stage2(capacity, -1)
         ev.synchronize()
-        R = int(st["pinned"][0])
+        R = int(ss["pinned"][0])
         if R > capacity:
             binning = run_stage2(R, R)
     else:
         _lib.check(lib.fdls_preprocess(C.byref(a), stream), "fdls_preprocess")
         torch.cuda.current_stream().synchronize()
-        R = int(st["pinned"][0])
+        R = int(ss["pinned"][0])
         binning = run_stage2(R, R)
     st["last_R"] = R
     st["last_capacity"] = int(a.capacity)  # read by the tests to decode the binning workspace

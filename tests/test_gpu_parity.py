@@ -414,3 +414,38 @@ def test_against_committed_golden_vectors(synth, F):
     for nm, a in (("means2D", g.means2D), ("colors", g.colors), ("lang", g.lang), ("opacity", g.opacity),
                   ("means3D", g.means3D), ("cov3D", g.cov3D), ("sh", g.sh), ("scales", g.scales), ("rots", g.rots)):
         _assert_grad(a, T(gold["g_" + nm]), "dL_d" + nm)
+
+
+def test_two_stream_sweep_is_bit_identical_to_one_stream(synth, fdls):
+    """A render sweep alternating two CUDA streams (4dlangsplat_b200/sweep.py) must give, frame by frame, exactly the
+    images, radii and instance counts of the same sweep on one stream: the binding's per-(device, stream) state
+    (pinned R pair, event, speculative capacity) must not leak between frames in flight.  Frames differ in size
+    (different point sets) so that the speculative capacity both over- and under-shoots."""
+    dev = torch.device("cuda:0")
+    dgr = fdls.diff_gaussian_rasterization
+    scenes = [synth.scene("small", seed=s_) for s_ in (1, 2)] + [synth.scene("tiny", seed=3)]
+    t = lambda a: torch.tensor(a, device=dev)
+    packs = []
+    for s in scenes:
+        rs = dgr.GaussianRasterizationSettings(s.H, s.W, s.tanfovx, s.tanfovy, t(s.bg), 1.0, t(s.viewmatrix),
+                                               t(s.projmatrix), 3, t(s.campos), False, False, True)
+        packs.append((dgr.GaussianRasterizer(rs), dict(means3D=t(s.means3D), means2D=None, opacities=t(s.opacities),
+                                                       shs=t(s.shs), language_feature_precomp=t(s.language_feature),
+                                                       scales=t(s.scales), rotations=t(s.rotations))))
+    order = [0, 2, 1, 1, 2, 0, 0, 1, 2, 2, 0, 1] * 3
+
+    def sweep(n_streams):
+        ring = fdls.sweep.StreamRing(n_streams)
+        outs = []
+        with torch.no_grad(), ring:
+            for i, k in enumerate(order):
+                with ring.stream(i):
+                    r, kw = packs[k]
+                    outs.append(r(**kw))
+        torch.cuda.synchronize()
+        return outs
+
+    one, two, three = sweep(1), sweep(2), sweep(3)
+    for a, b, c in zip(one, two, three):
+        for x, y, z in zip(a, b, c):
+            assert torch.equal(x, y) and torch.equal(x, z)
