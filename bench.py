@@ -174,33 +174,51 @@ class E2EPipe:
         self.d2h = sum(x.numel() * 4 for x in self.outs_host)
         self.next = None
         self.on_copied = None
+        # the camera (view 16 + proj 16 + campos 3 + bg 3 floats) travels as ONE pinned block per frame
+        self.cam_block = torch.cat([x.reshape(-1) for x in wl.cam_host]).pin_memory()
+        self.cam_shapes = [tuple(x.shape) for x in wl.cam_host]
+        self.events = [torch.cuda.Event() for _ in range(48)]
+        self.n_ev = 0
+        self.alive = []  # device tensors of the frames in flight (instead of record_stream: cheaper on the host)
+
+    def event(self):
+        self.n_ev += 1
+        return self.events[self.n_ev % len(self.events)]
 
     def upload(self, i):
         with torch.cuda.stream(self.up):
-            cam = [x.to("cuda", non_blocking=True) for x in self.wl.cam_host]
+            blk = self.cam_block.to("cuda", non_blocking=True)
             means = self.wl.means_host[i % N_TIMESTAMPS].to("cuda", non_blocking=True)
-            ev = torch.cuda.Event()
+            ev = self.event()
             ev.record(self.up)
-        return cam, means, ev
+        cam, o = [], 0
+        for shp in self.cam_shapes:
+            n = int(np.prod(shp))
+            cam.append(blk[o:o + n].view(shp))
+            o += n
+        return cam, means, ev, blk
 
     def frame(self, i, render):
         """render(i, means, cam) -> (color, lang, depth) enqueued on the current stream."""
         main = torch.cuda.current_stream()
-        cam, means, ev = self.next if self.next is not None else self.upload(i)
+        cam, means, ev, blk = self.next if self.next is not None else self.upload(i)
         self.next = self.upload(i + 1)
         main.wait_event(ev)
         outs = render(i, means, cam)
-        for t in cam + [means]:
-            t.record_stream(main)
-        done = torch.cuda.Event()
+        done = self.event()
         done.record(main)
         self.down.wait_event(done)
         with torch.cuda.stream(self.down):
             for h, o in zip(self.outs_host, outs):
                 h.copy_(o, non_blocking=True)
-                o.record_stream(self.down)
-            copied = torch.cuda.Event()
+            copied = self.event()
             copied.record(self.down)
+        # keep this frame's device tensors referenced until 8 more frames have been issued: the host never runs more
+        # than a few frames ahead of the device (every forward waits for its own preprocess), so their memory cannot
+        # be handed to a younger frame while a copy or a kernel still reads it
+        self.alive.append((blk, means, outs))
+        if len(self.alive) > 8:
+            self.alive.pop(0)
         if self.on_copied is not None:
             self.on_copied(copied)
         return copied
@@ -219,9 +237,12 @@ class E2EPipe:
         torch.cuda.synchronize()
         barrier(world)
         t0 = time.perf_counter()
+        self.host_s = 0.0  # time the host spent issuing work (if ~ the whole step, the arm is host-bound)
         for k in range(steps):
+            th = time.perf_counter()
             for f in range(FRAMES_PER_STEP):
                 one(k * FRAMES_PER_STEP + f)
+            self.host_s += time.perf_counter() - th
             torch.cuda.synchronize()  # the step's images are on the host
         t1 = time.perf_counter()
         barrier(world)
@@ -301,6 +322,7 @@ def run_ours(wl, steps, warmup, world):
         return color, lang, depth
 
     e2e_s = pipe.run(steps, warmup, world, render, compute_streams=streams)
+    sys.stderr.write('e2e: host issue time %.1f us/frame of %.1f us/frame\n' % (1e6 * pipe.host_s / n_frames, 1e6 * e2e_s / n_frames))
     h2d, d2h = pipe.h2d, pipe.d2h  # per frame
     return dict(ms=ms, n_frames=n_frames, stage_ms=stage_ms, stage_iso=stage_iso, R=float(np.mean(Rs)), V=V,
                 launches=int(launches), e2e_s=e2e_s, h2d=h2d * FRAMES_PER_STEP, d2h=d2h * FRAMES_PER_STEP)
