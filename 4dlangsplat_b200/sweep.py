@@ -11,6 +11,11 @@ this is safe from one host thread.  On cfg2 two streams give 3382 frames/s again
             with ring.stream(i):
                 outs.append(rasterizer(...))
     # leaving the block makes the caller's stream wait for every frame
+
+Forward sweeps only.  Tried for the training step too (the views of a batch on alternating streams, autograd replaying
+each view's backward on its forward's stream): 147 iters/s against 276 on one stream at cfg3 -- the cross-stream
+synchronisation autograd inserts around the shared leaves' gradient accumulation costs far more than the overlap
+gains -- so dist.sharded_step stays on one stream.
 """
 import torch
 

@@ -4,6 +4,8 @@ for sm_100a (oracle/_ref/libref_f{3,6}.so) on identical synthetic inputs.
 Bars (BASELINE.json north_star): sort keys/values, tile ranges, per-pixel contributor counts bit-exact; forward
 images within 1e-5 relative; gradients within 1e-4 relative (atomic-order nondeterminism on both sides).
 """
+import importlib
+
 import numpy as np
 import pytest
 import torch
@@ -449,3 +451,4 @@ def test_two_stream_sweep_is_bit_identical_to_one_stream(synth, fdls):
     for a, b, c in zip(one, two, three):
         for x, y, z in zip(a, b, c):
             assert torch.equal(x, y) and torch.equal(x, z)
+
