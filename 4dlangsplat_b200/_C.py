@@ -22,6 +22,11 @@ from . import _lib
 _state = {}  # per-device: pinned R buffer, last R
 # bench.py hooks: ctypes arrays of cudaEvent_t handles (FDLS_FWD_EVENTS / FDLS_BWD_EVENTS entries) or None
 profile = {"fwd": None, "bwd": None}
+# While a pipelined sweep is active (sweep.render_sweep) this is a list: a no-grad forward then appends its
+# "wait for R, re-run stage 2 on overflow" closure here instead of waiting, and returns a LIST whose [0] (num_rendered)
+# is -1 until the closure has run.  The sweep runs the closure before it hands the frame's outputs to the caller.
+_deferred = None
+
 # parity tests set this: the partition binning then also writes the reference-format sorted keys (not needed to render)
 emit_keys = False
 
@@ -150,27 +155,46 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
 
     speculative = os.environ.get("FDLS_SPECULATIVE", "1") != "0" and st["last_R"] is not None and not debug
     a.capacity = 0
+    result = [None, out_color, out_lang, out_depth, radii, geom, None, img]
     if speculative:
         capacity = _round_capacity(st["last_R"] * 1.25 + 4096)
         a.capacity = capacity
         _lib.check(lib.fdls_preprocess(C.byref(a), stream), "fdls_preprocess")
         ev = ss["event"]
         ev.record()
-        binning = run_stage2(capacity, -1)
-        ev.synchronize()
-        R = int(ss["pinned"][0])
-        if R > capacity:
-            binning = run_stage2(R, R)
+        result[6] = run_stage2(capacity, -1)
+        defer = _deferred is not None and not torch.is_grad_enabled()
+        tstream = torch.cuda.current_stream(dev) if defer else None
+
+        def finish():
+            ev.synchronize()
+            R = int(ss["pinned"][0])
+            if R > capacity:  # the guess was too small: bin and composite again into the same outputs
+                if tstream is not None:
+                    with torch.cuda.stream(tstream):
+                        result[6] = run_stage2(R, R)
+                else:
+                    result[6] = run_stage2(R, R)
+            result[0] = R
+            st["last_R"] = R
+            st["last_capacity"] = int(a.capacity)  # read by the tests to decode the binning workspace
+
+        if defer:  # a pipelined sweep (sweep.render_sweep) checks R later, before it hands the images out
+            _deferred.append(finish)
+            result[0] = -1
+            return result
+        finish()
     else:
         _lib.check(lib.fdls_preprocess(C.byref(a), stream), "fdls_preprocess")
         torch.cuda.current_stream().synchronize()
         R = int(ss["pinned"][0])
-        binning = run_stage2(R, R)
-    st["last_R"] = R
-    st["last_capacity"] = int(a.capacity)  # read by the tests to decode the binning workspace
+        result[6] = run_stage2(R, R)
+        result[0] = R
+        st["last_R"] = R
+        st["last_capacity"] = int(a.capacity)
     if debug:  # CHECK_CUDA semantics (auxiliary.h:166-173): surface asynchronous errors here
         torch.cuda.current_stream().synchronize()
-    return R, out_color, out_lang, out_depth, radii, geom, binning, img
+    return tuple(result)
 
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, language_feature, scales, rotations,

@@ -447,8 +447,30 @@ def test_two_stream_sweep_is_bit_identical_to_one_stream(synth, fdls):
         torch.cuda.synchronize()
         return outs
 
+    def pipelined(n_streams):
+        fns = [(lambda k=k: packs[k][0](**packs[k][1])) for k in order]
+        outs = list(fdls.sweep.render_sweep(fns, n_streams))
+        torch.cuda.synchronize()
+        return outs
+
     one, two, three = sweep(1), sweep(2), sweep(3)
     for a, b, c in zip(one, two, three):
         for x, y, z in zip(a, b, c):
             assert torch.equal(x, y) and torch.equal(x, z)
+    # the pipelined sweep (instance-count check deferred; the small frames after big ones over-provision, the big
+    # ones after small ones overflow and are re-run when they are handed out)
+    for n in (1, 2, 3, 4):
+        for a, b in zip(one, pipelined(n)):
+            for x, y in zip(a, b):
+                assert torch.equal(x, y)
+    # and the binding reports the true instance count once a deferred frame has been finished
+    E = torch.Tensor([])
+    s0 = scenes[0]
+    args = (t(s0.bg), t(s0.means3D), E, t(s0.language_feature), t(s0.opacities), t(s0.scales), t(s0.rotations), 1.0, E,
+            t(s0.viewmatrix), t(s0.projmatrix), s0.tanfovx, s0.tanfovy, s0.H, s0.W, t(s0.shs), 3, t(s0.campos), False,
+            False, True)
+    with torch.no_grad():
+        R_direct = fdls._C.rasterize_gaussians(*args)[0]
+    outs = list(fdls.sweep.render_sweep([lambda: fdls._C.rasterize_gaussians(*args)] * 5, 3))
+    assert all(o[0] == R_direct for o in outs)
 
