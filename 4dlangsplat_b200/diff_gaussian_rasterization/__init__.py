@@ -107,6 +107,16 @@ class _RasterizeGaussians(torch.autograd.Function):
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, language_feature_precomp, opacities, scales, rotations,
                         cov3Ds_precomp, raster_settings):
+    if not torch.is_grad_enabled():
+        # inference (render.py runs under torch.no_grad()): same native call, none of the autograd.Function bookkeeping
+        rs = raster_settings
+        native_args = (rs.bg, means3D, colors_precomp, language_feature_precomp, opacities, scales, rotations,
+                       rs.scale_modifier, cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
+                       rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug,
+                       rs.include_feature)
+        out = _guarded(_C.rasterize_gaussians, native_args, rs.debug, "snapshot_fw.dump",
+                       "\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
+        return out[1], out[2], out[4], out[3]
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, language_feature_precomp, opacities,
                                      scales, rotations, cov3Ds_precomp, raster_settings)
 
@@ -114,7 +124,10 @@ def rasterize_gaussians(means3D, means2D, sh, colors_precomp, language_feature_p
 def _or_empty(t):
     # the reference stands in a CPU torch.Tensor([]) for every absent optional (ref :208-221); the native side
     # recognises it by data_ptr()==nullptr
-    return torch.Tensor([]) if t is None else t
+    return _EMPTY if t is None else t
+
+
+_EMPTY = torch.Tensor([])  # never written to: one shared placeholder instead of a new tensor per absent argument
 
 
 class GaussianRasterizer(nn.Module):
