@@ -463,6 +463,12 @@ def test_two_stream_sweep_is_bit_identical_to_one_stream(synth, fdls):
         for a, b in zip(one, pipelined(n)):
             for x, y in zip(a, b):
                 assert torch.equal(x, y)
+    # the no-grad fast path of the public API returns what the autograd.Function path returns
+    r0, kw0 = packs[0]
+    with torch.enable_grad():
+        with_grad = r0(**dict(kw0, means3D=kw0["means3D"].clone().requires_grad_(True)))
+    for x, y in zip(one[order.index(0)], with_grad):
+        assert torch.equal(x, y.detach())
     # and the binding reports the true instance count once a deferred frame has been finished
     E = torch.Tensor([])
     s0 = scenes[0]
