@@ -44,7 +44,7 @@ class StreamRing:
         return False
 
 
-def render_sweep(render_fns, n_streams=3):
+def render_sweep(render_fns, n_streams=3, sync_to_caller=True):
     """Pipelined no-grad sweep: `render_fns` is an iterable of zero-argument callables, each rendering one frame through
     GaussianRasterizer / _C.rasterize_gaussians; yields their results in order.
 
@@ -52,8 +52,9 @@ def render_sweep(render_fns, n_streams=3):
     next one: the binding's "wait for R, re-run binning + compositing if the speculative capacity was too small" step
     is collected and run only when the frame is about to be handed out -- at the latest just before frame
     i + n_streams reuses its stream -- so up to n_streams frames are in flight and every result the caller sees has
-    been verified.  The caller's stream waits for all frames when the generator is exhausted; a result taken earlier
-    must be consumed on (or synchronised with) the stream it was issued on (`ring.streams[i % n]`).
+    been verified.  With sync_to_caller (default) the caller's stream is ordered after each frame before the frame is
+    yielded, so results can be used on the caller's stream like the results of a plain call; without it a result must
+    be consumed on the stream it was issued on (`i mod n_streams`) until the generator is exhausted.
     """
     from collections import deque
 
@@ -61,10 +62,27 @@ def render_sweep(render_fns, n_streams=3):
     ring = StreamRing(n_streams)
     pending = deque()
 
+    def tensors(x):
+        if isinstance(x, torch.Tensor):
+            yield x
+        elif isinstance(x, dict):
+            for v in x.values():
+                yield from tensors(v)
+        elif isinstance(x, (list, tuple)):
+            for v in x:
+                yield from tensors(v)
+
     def finish(item):
-        out, closures = item
+        out, closures, stream = item
         for f in closures:
             f()
+        if sync_to_caller and stream is not ring.main:
+            # the caller consumes the result on ITS stream: order that stream after the frame, and tell the caching
+            # allocator that the frame's tensors are in use there too
+            ring.main.wait_stream(stream)
+            for t in tensors(out):
+                if t.is_cuda:
+                    t.record_stream(ring.main)
         return out
 
     with torch.no_grad(), ring:
@@ -77,6 +95,6 @@ def render_sweep(render_fns, n_streams=3):
                     out = fn()
                 finally:
                     _C._deferred = None
-            pending.append((out, closures))
+            pending.append((out, closures, ring.streams[i % len(ring)]))
         while pending:
             yield finish(pending.popleft())
