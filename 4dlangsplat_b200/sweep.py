@@ -22,16 +22,19 @@ import torch
 
 
 class StreamRing:
-    def __init__(self, n_streams=2, device=None):
+    def __init__(self, n_streams=2, device=None, include_main=True):
         self.main = torch.cuda.current_stream(device)
-        self.streams = [self.main] + [torch.cuda.Stream(device) for _ in range(max(1, int(n_streams)) - 1)]
+        n = max(1, int(n_streams))
+        self.streams = ([self.main] if include_main else []) + [
+            torch.cuda.Stream(device) for _ in range(n - 1 if include_main else n)]
 
     def __len__(self):
         return len(self.streams)
 
     def __enter__(self):
-        for s in self.streams[1:]:
-            s.wait_stream(self.main)  # inputs produced on the caller's stream are visible to every frame
+        for s in self.streams:
+            if s is not self.main:
+                s.wait_stream(self.main)  # inputs produced on the caller's stream are visible to every frame
         return self
 
     def stream(self, i):
@@ -39,8 +42,9 @@ class StreamRing:
         return torch.cuda.stream(self.streams[i % len(self.streams)])
 
     def __exit__(self, *exc):
-        for s in self.streams[1:]:
-            self.main.wait_stream(s)
+        for s in self.streams:
+            if s is not self.main:
+                self.main.wait_stream(s)
         return False
 
 
@@ -59,36 +63,27 @@ def render_sweep(render_fns, n_streams=3, sync_to_caller=True):
     from collections import deque
 
     from . import _C
-    ring = StreamRing(n_streams)
+    # with sync_to_caller the frames run on n side streams and the caller's stream only carries the caller's own work
+    ring = StreamRing(n_streams, include_main=not sync_to_caller)
     pending = deque()
-
-    def tensors(x):
-        if isinstance(x, torch.Tensor):
-            yield x
-        elif isinstance(x, dict):
-            for v in x.values():
-                yield from tensors(v)
-        elif isinstance(x, (list, tuple)):
-            for v in x:
-                yield from tensors(v)
 
     def finish(item):
         out, closures, stream = item
         for f in closures:
             f()
-        if sync_to_caller and stream is not ring.main:
-            # the caller consumes the result on ITS stream: order that stream after the frame, and tell the caching
-            # allocator that the frame's tensors are in use there too
-            ring.main.wait_stream(stream)
-            for t in tensors(out):
-                if t.is_cuda:
-                    t.record_stream(ring.main)
+        if sync_to_caller:
+            ring.main.wait_stream(stream)  # the caller consumes the result on ITS stream: order it after the frame
         return out
 
     with torch.no_grad(), ring:
         for i, fn in enumerate(render_fns):
             if len(pending) == len(ring):
                 yield finish(pending.popleft())
+            if sync_to_caller:
+                # whatever the caller enqueued on its stream for the frame that last used this stream is done before
+                # the stream's memory can be handed to this frame (no record_stream: that would park the big
+                # workspaces in the allocator until the caller's stream catches up, and force fresh cudaMallocs)
+                ring.streams[i % len(ring)].wait_stream(ring.main)
             with ring.stream(i):
                 _C._deferred = closures = []
                 try:
