@@ -27,6 +27,11 @@ profile = {"fwd": None, "bwd": None}
 # is -1 until the closure has run.  The sweep runs the closure before it hands the frame's outputs to the caller.
 _deferred = None
 
+# Optional high-priority torch stream for stage 1 (preprocess, depth sort, scan) of the next forward; set per frame by
+# sweep.render_sweep.  The block scheduler then places the small, latency-bound stage-1 grids of a younger frame ahead
+# of the still-pending compositor CTAs of an older one.  Stage 2 stays on the current stream, ordered behind stage 1.
+_front = None
+
 # parity tests set this: the partition binning then also writes the reference-format sorted keys (not needed to render)
 emit_keys = False
 
@@ -159,9 +164,16 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
     if speculative:
         capacity = _round_capacity(st["last_R"] * 1.25 + 4096)
         a.capacity = capacity
-        _lib.check(lib.fdls_preprocess(C.byref(a), stream), "fdls_preprocess")
         ev = ss["event"]
-        ev.record()
+        if _front is not None:
+            cur = torch.cuda.current_stream(dev)
+            _front.wait_stream(cur)  # inputs and recycled workspaces are ordered on the current stream
+            _lib.check(lib.fdls_preprocess(C.byref(a), C.c_void_p(_front.cuda_stream)), "fdls_preprocess")
+            ev.record(_front)
+            cur.wait_event(ev)
+        else:
+            _lib.check(lib.fdls_preprocess(C.byref(a), stream), "fdls_preprocess")
+            ev.record()
         result[6] = run_stage2(capacity, -1)
         defer = _deferred is not None and not torch.is_grad_enabled()
         tstream = torch.cuda.current_stream(dev) if defer else None

@@ -29,7 +29,7 @@ import torch  # noqa: E402
 
 FRAMES_PER_STEP = int(os.environ.get('FDLS_BENCH_FRAMES_PER_STEP', '100'))  # one step = the config's 100-timestamp sweep
 N_TIMESTAMPS = 100
-N_STREAMS = max(1, int(os.environ.get('FDLS_BENCH_STREAMS', '3')))  # streams the device-resident sweep alternates over
+N_STREAMS = max(1, int(os.environ.get('FDLS_BENCH_STREAMS', '4')))  # streams the device-resident sweep alternates over
 N_PARAM_SETS = 3  # static per-Gaussian parameters are cycled over 3 copies (3 x 71 MB > 126 MB L2)
 
 
@@ -318,7 +318,7 @@ def run_ours(wl, steps, warmup, world):
     def sweep(n, pool=None, keep=None):
         out = None
         fns = ((lambda i=i: frame(i, pool.arrays[i] if pool is not None else None)) for i in range(n))
-        for out in fsweep.render_sweep(fns, N_STREAMS):  # each result arrives with its instance count verified
+        for out in fsweep.render_sweep(fns, N_STREAMS, front_priority=os.environ.get('FDLS_FRONT', '0') == '1'):
             if keep is not None:
                 keep.append(out[0])
         return out
