@@ -447,9 +447,9 @@ def test_two_stream_sweep_is_bit_identical_to_one_stream(synth, fdls):
         torch.cuda.synchronize()
         return outs
 
-    def pipelined(n_streams):
+    def pipelined(n_streams, **kw):
         fns = [(lambda k=k: packs[k][0](**packs[k][1])) for k in order]
-        outs = list(fdls.sweep.render_sweep(fns, n_streams))
+        outs = list(fdls.sweep.render_sweep(fns, n_streams, **kw))
         torch.cuda.synchronize()
         return outs
 
@@ -459,8 +459,8 @@ def test_two_stream_sweep_is_bit_identical_to_one_stream(synth, fdls):
             assert torch.equal(x, y) and torch.equal(x, z)
     # the pipelined sweep (instance-count check deferred; the small frames after big ones over-provision, the big
     # ones after small ones overflow and are re-run when they are handed out)
-    for n in (1, 2, 3, 4):
-        for a, b in zip(one, pipelined(n)):
+    for n, kw in ((1, {}), (2, {}), (3, {}), (4, {}), (3, dict(front_priority=True)), (2, dict(sync_to_caller=False))):
+        for a, b in zip(one, pipelined(n, **kw)):
             for x, y in zip(a, b):
                 assert torch.equal(x, y)
     # the no-grad fast path of the public API returns what the autograd.Function path returns
