@@ -76,6 +76,11 @@ __device__ __forceinline__ uint32_t cnt_get(const uint32_t* w, uint32_t t) {
 // inner iteration ~ one full 32-lane iteration).  Spans are equal in COST: W_incl(p) = offsets[p] + PT_C * (p + 1)
 // over the V visible Gaussians, which come first in depth order (culled ones carry the key 0xffffffff).
 constexpr uint32_t PT_C = 32;
+#ifndef PT_GL_
+#define PT_GL_ 8
+#endif
+constexpr int PT_GL = PT_GL_;                 // lanes per Gaussian in the counting walks
+constexpr uint32_t PT_SMALL = 8u * PT_GL;    // more tiles than this: the Gaussian takes the whole warp
 __device__ __forceinline__ unsigned long long w_incl(const uint32_t* __restrict__ offsets, int p) {
   return (unsigned long long)offsets[p] + (unsigned long long)PT_C * (uint32_t)(p + 1);
 }
@@ -139,14 +144,14 @@ __device__ __forceinline__ void walk(unsigned long long ws, unsigned long long w
       // Counting needs no order (the counters are shared-memory atomics): Gaussians with few tiles -- the bulk: ten
       // tiles on average -- go FOUR at a time, eight lanes each, instead of one at a time with two thirds of the warp
       // idle; only the big ones keep the whole warp.
-      const uint32_t big = __ballot_sync(0xffffffffu, j1 - j0 > 64u);
+      const uint32_t big = __ballot_sync(0xffffffffu, j1 - j0 > PT_SMALL);
       uint32_t small = todo & ~big;
       todo = big;
-      const int grp = lane >> 3, sub = lane & 7;
+      const int grp = lane / PT_GL, sub = lane % PT_GL;
       while (small) {
         int src = -1;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < 32 / PT_GL; ++q) {
           const int b = __ffs(small) - 1;  // -1 once the set is exhausted
           if (q == grp) src = b;
           small &= small - 1;
@@ -159,7 +164,7 @@ __device__ __forceinline__ void walk(unsigned long long ws, unsigned long long w
         if (src < 0) b_j1 = b_j0;
         const uint32_t b_w = b_pack >> 20;
         const uint32_t t0 = ((b_pack >> 10) & 1023u) * gx + (b_pack & 1023u);
-        for (uint32_t i = b_j0 + sub; i < b_j1; i += 8) {
+        for (uint32_t i = b_j0 + sub; i < b_j1; i += PT_GL) {
           const uint32_t row = b_w > 1 ? __umulhi(i, b_magic) : i;
           cnt_inc(wcnt, t0 + row * gx + (i - row * b_w));
         }

@@ -21,12 +21,24 @@ gains -- so dist.sharded_step stays on one stream.
 import torch
 
 
+_side = {}  # (device index, priority) -> side streams created so far
+
+
+def _side_streams(device, n, priority=0):
+    """The same n side streams every time: the caching allocator keeps one pool per stream, so a sweep on fresh streams
+    would start with empty pools and cudaMalloc its workspaces inside the sweep (measured: 3600 -> 2200 frames/s)."""
+    idx = torch.cuda.current_device() if device is None else torch.device(device).index
+    have = _side.setdefault((idx, priority), [])
+    while len(have) < n:
+        have.append(torch.cuda.Stream(idx, priority=priority))
+    return have[:n]
+
+
 class StreamRing:
     def __init__(self, n_streams=2, device=None, include_main=True):
         self.main = torch.cuda.current_stream(device)
         n = max(1, int(n_streams))
-        self.streams = ([self.main] if include_main else []) + [
-            torch.cuda.Stream(device) for _ in range(n - 1 if include_main else n)]
+        self.streams = ([self.main] if include_main else []) + _side_streams(device, n - 1 if include_main else n)
 
     def __len__(self):
         return len(self.streams)
@@ -69,7 +81,7 @@ def render_sweep(render_fns, n_streams=3, sync_to_caller=True, front_priority=Fa
     # with sync_to_caller the frames run on n side streams and the caller's stream only carries the caller's own work
     ring = StreamRing(n_streams, include_main=not sync_to_caller)
     pending = deque()
-    front = [torch.cuda.Stream(priority=-1) for _ in range(len(ring))] if front_priority else None
+    front = _side_streams(None, len(ring), priority=-1) if front_priority else None
 
     def finish(item):
         out, closures, stream = item
