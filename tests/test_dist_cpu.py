@@ -51,8 +51,12 @@ def _worker(rank, world_size, port, n_views, out):
     dist.destroy_process_group()
 
 
-def test_sharded_step_matches_single_process_gradient():
-    n_views, world_size = 5, 2  # ragged: rank 0 gets 3 views, rank 1 gets 2
+import pytest
+
+
+@pytest.mark.parametrize("n_views", [5, 1])  # 5: ragged (3 + 2 views); 1: rank 1 has NO view (more GPUs than views)
+def test_sharded_step_matches_single_process_gradient(n_views):
+    world_size = 2
     ctx = mp.get_context("spawn")
     out = ctx.SimpleQueue()
     port = _free_port()
