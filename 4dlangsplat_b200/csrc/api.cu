@@ -302,6 +302,8 @@ FDLS_API int fdls_backward(const FdlsBwdArgs* a, void* stream) {
   if (a->F < 0 || a->F > FDLS_MAX_LANG_CHANNELS) return FDLS_EUNSUPPORTED;
   if (a->P == 0) return FDLS_OK;
   if (!a->geom_ws || !a->img_ws || !a->grad_ws || !a->dL_dout_color || !a->radii || !a->means3D) return FDLS_EINVAL;
+  if (!a->viewmatrix || !a->projmatrix || !a->background) return FDLS_EINVAL;
+  if (a->shs && !a->campos) return FDLS_EINVAL;  // like the reference, campos is only read by the SH colour path
   if (a->include_feature && (a->F < 1 || !a->dL_dout_language)) return FDLS_EINVAL;
   if (a->grad_bytes < fdls_grad_workspace_bytes(a->P)) return FDLS_EWORKSPACE;
   cudaStream_t st = (cudaStream_t)stream;

@@ -394,18 +394,10 @@ cudaError_t launch_partition(int P, int gx, int gy, const uint32_t* order, const
                              uint2* ranges, uint32_t* num_rendered, uint32_t* point_list, uint64_t* keys,
                              const uint32_t* depth_hist, long long capacity, cudaStream_t st) {
   const int T = gx * gy, ctas = partition_ctas(capacity, P, T);
-  static size_t attr_a = 0, attr_b = 0;
+  static SmemOptIn optin_a, optin_b;  // per device (common.cuh)
   const size_t sa = pt_smem_bytes(T, false), sb = pt_smem_bytes(T, true);
-  if (sa > attr_a) {
-    cudaError_t e = cudaFuncSetAttribute(part_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa);
-    if (e != cudaSuccess) return e;
-    attr_a = sa;
-  }
-  if (sb > attr_b) {
-    cudaError_t e = cudaFuncSetAttribute(part_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb);
-    if (e != cudaSuccess) return e;
-    attr_b = sb;
-  }
+  if (cudaError_t e = optin_a.ensure(part_count_kernel, sa)) return e;
+  if (cudaError_t e = optin_b.ensure(part_scatter_kernel, sb)) return e;
   part_count_kernel<<<ctas, PT_THREADS, sa, st>>>(P, T, num_rendered, depth_hist, order, offsets, radii, rec, gx, gy, table);
   count_launch();
   part_colscan_kernel<<<cdiv(T, 8), 1024, 0, st>>>(T, ctas, table, tile_total, tile_start, ranges, num_rendered,

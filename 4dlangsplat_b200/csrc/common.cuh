@@ -6,7 +6,9 @@
 // The file is compiled WITHOUT --use_fast_math and with the default -fmad=true, like the reference
 // (setup.py:33 passes no math flags).
 #pragma once
+#include <atomic>
 #include <cstdint>
+#include <mutex>
 #include <cuda_runtime.h>
 #include "../../include/fdls_abi.h"
 
@@ -144,6 +146,33 @@ __device__ __forceinline__ float2 strip_summary(float gx_, float gy_, float A, f
 }
 
 void count_launch(int n = 1);  // api.cu: feeds fdls_kernel_launches()
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute of a kernel.  One of these per kernel
+// remembers the size opted in on each device, so a process that drives several GPUs (one host thread per GPU, or
+// one thread switching devices) opts in on every one of them.  Thread-safe: lock-free fast path, mutex on the
+// (first-launch) slow path so that two racing threads cannot leave a smaller size behind than the one recorded.
+struct SmemOptIn {
+  static constexpr int MAX_DEV = 64;
+  std::atomic<size_t> bytes[MAX_DEV];
+  std::mutex mu;
+  SmemOptIn() {
+    for (auto& b : bytes) b.store(0, std::memory_order_relaxed);
+  }
+  template <class K>
+  cudaError_t ensure(K* kernel, size_t want) {
+    if (want <= 48 * 1024) return cudaSuccess;  // within the default limit on every device
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    const bool tracked = dev >= 0 && dev < MAX_DEV;
+    if (tracked && bytes[dev].load(std::memory_order_acquire) >= want) return cudaSuccess;
+    std::lock_guard<std::mutex> lock(mu);
+    if (tracked && bytes[dev].load(std::memory_order_relaxed) >= want) return cudaSuccess;
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want);
+    if (e == cudaSuccess && tracked) bytes[dev].store(want, std::memory_order_release);
+    return e;
+  }
+};
 
 static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }

@@ -43,7 +43,7 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   if (threadIdx.x < 16) s_view[threadIdx.x] = vp.view[threadIdx.x];
   else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = vp.proj[threadIdx.x - 16];
-  else if (threadIdx.x < 35) s_cam[threadIdx.x - 32] = vp.campos[threadIdx.x - 32];
+  else if (threadIdx.x < 35) s_cam[threadIdx.x - 32] = vp.campos != nullptr ? vp.campos[threadIdx.x - 32] : 0.f;
   __syncthreads();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P) return;

@@ -101,7 +101,7 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
     for (int i = threadIdx.x; i < 1024; i += 256) (&s_hist[0][0])[i] = 0;
   if (threadIdx.x < 16) s_view[threadIdx.x] = vp.view[threadIdx.x];
   else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = vp.proj[threadIdx.x - 16];
-  else if (threadIdx.x < 35) s_cam[threadIdx.x - 32] = vp.campos[threadIdx.x - 32];
+  else if (threadIdx.x < 35) s_cam[threadIdx.x - 32] = vp.campos != nullptr ? vp.campos[threadIdx.x - 32] : 0.f;  // only SH needs it
   __syncthreads();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int sh_stride = 3 * M + 1;
@@ -261,12 +261,8 @@ cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, fl
   const bool stage = a->shs != nullptr && a->colors_precomp == nullptr && a->M >= 1 && a->M <= 16;
   const size_t smem = stage ? (size_t)256 * (3 * a->M + 1) * sizeof(float) : 0;
   const uint32_t magic = stage ? (uint32_t)(0xffffffffu / (uint32_t)(3 * a->M) + 1u) : 0u;
-  static size_t attr = 0;
-  if (smem > attr) {
-    cudaError_t e = cudaFuncSetAttribute(preprocess_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    attr = smem;
-  }
+  static SmemOptIn optin;  // per device (common.cuh)
+  if (cudaError_t e = optin.ensure(preprocess_fwd_kernel, smem)) return e;
   preprocess_fwd_kernel<<<cdiv(a->P, 256), 256, smem, st>>>(
       a->P, a->D, a->M, a->F, a->means3D, a->scales, a->rotations, a->opacities, a->shs, a->cov3D_precomp,
       a->colors_precomp, a->language_feature, vp, a->radii, rec, tiles_touched, clamped, depth_keys, depth_vals,

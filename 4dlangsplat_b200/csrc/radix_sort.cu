@@ -205,11 +205,16 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ 
         const uint32_t f = v[i] & FLAG_MASK;
         if (f == 0) {  // predecessor t-i has not published yet: resume from it
           t -= i;
-          if (++spins > (1u << 22)) {  // never hang the GPU: report and bail out
+          // Forward progress: tiles are handed out by ticket, so every predecessor belongs to a CTA that is already
+          // running and never waits on a later tile -- it will publish.  The poll limit (>= 2^26 x 100 ns = 6.7 s of
+          // waiting on ONE entry) only exists so that a corrupted scratch cannot hang the GPU; reaching it is never
+          // silent: the flag is set and the kernel traps, so the stream's next CUDA call reports a launch failure
+          // instead of handing out a mis-sorted frame.
+          if (++spins > (1u << 26)) {
             atomicExch(error_flag, 1u);
-            done = true;
+            __trap();
           } else if (i == 0) {
-            __nanosleep(20);
+            __nanosleep(spins < 64 ? 20 : 100);
           }
           break;
         }
@@ -316,13 +321,8 @@ template <int IPT>
 static int rs_launch_passes(uint64_t* kin, uint64_t* kout, uint32_t* vin, uint32_t* vout, long long n_max,
                             const uint32_t* n_dev, int begin_bit, int end_bit, int passes, RsScratch& sc,
                             cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(rs_onesweep_kernel<IPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)sizeof(RsSmem<IPT>)) != cudaSuccess)
-      return FDLS_ECUDA;
-    attr_set = true;
-  }
+  static SmemOptIn optin;  // per device (common.cuh); one per IPT instantiation
+  if (optin.ensure(rs_onesweep_kernel<IPT>, sizeof(RsSmem<IPT>)) != cudaSuccess) return FDLS_ECUDA;
   const int tiles = cdiv(n_max, RS_THREADS * IPT);
   for (int p = 0; p < passes; ++p) {
     const int shift = begin_bit + p * 8;

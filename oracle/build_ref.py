@@ -22,25 +22,28 @@ def lib_path(F):
     return os.path.join(OUT, "libref_f%d.so" % F)
 
 
-def build(force=False, widths=(3, 6)):
+def build(force=False, widths=(3, 6, 1, 2, 4, 5)):
     """Returns the list of built library paths ([] when the reference tree is not present)."""
     if not os.path.isdir(REF):
         return [lib_path(F) for F in widths if os.path.exists(lib_path(F))]
     os.makedirs(OUT, exist_ok=True)
     srcs = [os.path.join(REF, "cuda_rasterizer", n) for n in ("forward.cu", "backward.cu", "rasterizer_impl.cu")]
     shim = os.path.join(HERE, "ref_shim.cu")
-    built = []
+    built, procs = [], []
     for F in widths:
         out = lib_path(F)
         newest = max(os.path.getmtime(s) for s in srcs + [shim, os.path.abspath(__file__)])
         if force or not os.path.exists(out) or os.path.getmtime(out) < newest:
             cmd = ["nvcc", "-std=c++17", "-O3", "-shared", "-Xcompiler", "-fPIC", "-lineinfo",
-                   "-gencode", "arch=compute_100a,code=sm_100a", "-include", "cstdint",
+                   "-gencode", "arch=compute_100a,code=sm_100a", "-include", "cstdint", "-diag-suppress", "177",
                    "-DNUM_CHANNELS_language_feature=%d" % F,
                    "-I", os.path.join(REF, "third_party", "glm"), "-I", os.path.join(REF, "cuda_rasterizer"),
                    "-o", out, shim] + srcs
-            subprocess.check_call(cmd)
+            procs.append((cmd, subprocess.Popen(cmd)))  # the widths build side by side
         built.append(out)
+    for cmd, p in procs:
+        if p.wait() != 0:
+            raise subprocess.CalledProcessError(p.returncode, cmd)
     return built
 
 
