@@ -35,6 +35,18 @@ _front = None
 # parity tests set this: the partition binning then also writes the reference-format sorted keys (not needed to render)
 emit_keys = False
 
+# Gradient sinks (dist.GradBucket.register): leaf tensor's data_ptr() -> _Sink.  When an input of the rasterizer is a registered
+# leaf, the backward kernels ADD its gradient straight into the sink's tensor (a slice of the rank's all-reduce bucket)
+# and autograd receives None for it: no per-view gradient tensors, no autograd accumulation pass, no pack copy.
+grad_sinks = {}
+
+
+class _Sink:
+    __slots__ = ("view", "owner")
+
+    def __init__(self, view, owner):
+        self.view, self.owner = view, owner  # owner.fresh: nothing has been written to the bucket this iteration
+
 
 def _dev_state(device):
     key = device.index if device.index is not None else torch.cuda.current_device()
@@ -173,7 +185,7 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
             cur.wait_event(ev)
         else:
             _lib.check(lib.fdls_preprocess(C.byref(a), stream), "fdls_preprocess")
-            ev.record()
+            ev.record(torch.cuda.current_stream(dev))
         result[6] = run_stage2(capacity, -1)
         defer = _deferred is not None and not torch.is_grad_enabled()
         tstream = torch.cuda.current_stream(dev) if defer else None
@@ -198,25 +210,28 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
         finish()
     else:
         _lib.check(lib.fdls_preprocess(C.byref(a), stream), "fdls_preprocess")
-        torch.cuda.current_stream().synchronize()
+        torch.cuda.current_stream(dev).synchronize()
         R = int(ss["pinned"][0])
         result[6] = run_stage2(R, R)
         result[0] = R
         st["last_R"] = R
         st["last_capacity"] = int(a.capacity)
     if debug:  # CHECK_CUDA semantics (auxiliary.h:166-173): surface asynchronous errors here
-        torch.cuda.current_stream().synchronize()
+        torch.cuda.current_stream(dev).synchronize()
     return tuple(result)
 
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, language_feature, scales, rotations,
                                  scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
                                  dL_dout_color, dL_dout_language_feature, dL_dout_depth, sh, degree, campos, geomBuffer,
-                                 R, binningBuffer, imageBuffer, debug, include_feature, want=None):
+                                 R, binningBuffer, imageBuffer, debug, include_feature, want=None, out=None,
+                                 accumulate=False):
     """RasterizeGaussiansBackwardCUDA (rasterize_points.cu:131-235).  Returns (dL_dmeans2D, dL_dcolors,
     dL_dlanguage_feature, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations).
     `want` (an addition; None = all, like the reference): 9 booleans in that order -- gradients not wanted are neither
-    allocated nor written (the C ABI takes a null pointer for them) and come back as None."""
+    allocated nor written (the C ABI takes a null pointer for them) and come back as None.
+    `out` (an addition): 9 optional tensors in that order to write into instead of allocating; with `accumulate` the
+    kernels add to every output (caller-provided ones must hold the running sum, fresh ones are zero-filled here)."""
     lib = _lib.load()
     means3D = _prep(means3D, "means3D")
     dev = means3D.device
@@ -237,16 +252,18 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, language_fe
     f32 = dict(dtype=torch.float32, device=dev)
     # every element of these is written by the backward kernels (zeros for culled Gaussians): no zero-fill pass
     w = (True,) * 9 if want is None else tuple(bool(x) for x in want)
-    E = lambda shape: torch.empty(shape, **f32)
-    g_means2D = E((P, 3)) if w[0] else None
-    g_colors = E((P, 3)) if w[1] else None
-    g_lang = (E((P, F)) if include_feature else torch.zeros((1,), **f32)) if w[2] else None
-    g_opacity = E((P, 1)) if w[3] else None
-    g_means3D = E((P, 3)) if w[4] else None
-    g_cov3D = E((P, 6)) if w[5] else None
-    g_sh = (E((P, M, 3)) if M > 0 else torch.zeros((P, 0, 3), **f32)) if w[6] else None
-    g_scales = E((P, 3)) if w[7] else None
-    g_rot = E((P, 4)) if w[8] else None
+    o = (None,) * 9 if out is None else out
+    mk = torch.zeros if accumulate else torch.empty
+    E = lambda i, shape: o[i] if o[i] is not None else mk(shape, **f32)
+    g_means2D = E(0, (P, 3)) if w[0] else None
+    g_colors = E(1, (P, 3)) if w[1] else None
+    g_lang = (E(2, (P, F)) if include_feature else torch.zeros((1,), **f32)) if w[2] else None
+    g_opacity = E(3, (P, 1)) if w[3] else None
+    g_means3D = E(4, (P, 3)) if w[4] else None
+    g_cov3D = E(5, (P, 6)) if w[5] else None
+    g_sh = (E(6, (P, M, 3)) if M > 0 else torch.zeros((P, 0, 3), **f32)) if w[6] else None
+    g_scales = E(7, (P, 3)) if w[7] else None
+    g_rot = E(8, (P, 4)) if w[8] else None
     if P == 0:
         return g_means2D, g_colors, g_lang, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rot
     gb = lib.fdls_grad_workspace_bytes(P)
@@ -270,11 +287,13 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, language_fe
     a.dL_dopacity, a.dL_dcov3D = dp(g_opacity), dp(g_cov3D)
     a.dL_dscales, a.dL_drotations = dp(g_scales), dp(g_rot)
     a.dL_dconic, a.dL_ddepths = None, None
+    a.bwd_algo = 1 if os.environ.get("FDLS_RENDER_BWD", "mma") == "shfl" else 0
+    a.accumulate = int(bool(accumulate))
     if profile["bwd"] is not None:
         a.stage_events = profile["bwd"]
     _lib.check(lib.fdls_backward(C.byref(a), _stream(dev)), "fdls_backward")
     if debug:
-        torch.cuda.current_stream().synchronize()
+        torch.cuda.current_stream(dev).synchronize()
     return g_means2D, g_colors, g_lang, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rot
 
 
@@ -286,7 +305,8 @@ def mark_visible(means3D, viewmatrix, projmatrix):
     present = torch.zeros((P,), dtype=torch.bool, device=means3D.device)
     if P:
         _lib.check(lib.fdls_mark_visible(P, means3D.data_ptr(), _prep(viewmatrix, "viewmatrix").data_ptr(),
-                                         _prep(projmatrix, "projmatrix").data_ptr(), present.data_ptr(), _stream()),
+                                         _prep(projmatrix, "projmatrix").data_ptr(), present.data_ptr(),
+                                         _stream(means3D.device)),
                    "fdls_mark_visible")
     return present
 
@@ -300,5 +320,6 @@ def dist_cuda2(points):
     if N:
         wb = lib.fdls_knn_workspace_bytes(N)
         ws = torch.empty(wb, dtype=torch.uint8, device=points.device)
-        _lib.check(lib.fdls_knn_dist2(N, points.data_ptr(), out.data_ptr(), ws.data_ptr(), wb, _stream()), "fdls_knn_dist2")
+        _lib.check(lib.fdls_knn_dist2(N, points.data_ptr(), out.data_ptr(), ws.data_ptr(), wb, _stream(points.device)),
+                   "fdls_knn_dist2")
     return out

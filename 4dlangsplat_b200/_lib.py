@@ -66,6 +66,8 @@ class FdlsBwdArgs(C.Structure):
         ("dL_dlanguage", _f32p), ("dL_dopacity", _f32p), ("dL_dscales", _f32p), ("dL_drotations", _f32p),
         ("dL_dcov3D", _f32p), ("dL_dconic", _f32p), ("dL_ddepths", _f32p),
         ("stage_events", C.POINTER(C.c_void_p)),
+        ("bwd_algo", C.c_int32),
+        ("accumulate", C.c_int32),
     ]
 
 

@@ -51,6 +51,10 @@ cudaError_t launch_render_bwd(int F, const uint2* ranges, const uint32_t* point_
                               int gx, int gy, const float* bg, const float* final_T, const uint32_t* n_contrib,
                               const uint32_t* tile_max, const float* dpix, const float* dpix_F, const float* dpix_D,
                               float* grad_rec, cudaStream_t st);
+cudaError_t launch_render_bwd_shfl(int F, const uint2* ranges, const uint32_t* point_list, const float4* rec, int W,
+                                   int H, int gx, int gy, const float* bg, const float* final_T,
+                                   const uint32_t* n_contrib, const uint32_t* tile_max, const float* dpix,
+                                   const float* dpix_F, const float* dpix_D, float* grad_rec, cudaStream_t st);
 cudaError_t launch_preprocess_bwd(const FdlsBwdArgs* a, const ViewParams& vp, const uint8_t* clamped,
                                   const float4* grad_rec, cudaStream_t st);
 // knn.cu
@@ -321,7 +325,8 @@ FDLS_API int fdls_backward(const FdlsBwdArgs* a, void* stream) {
   rec(a->stage_events, 1, st);
   if (a->num_rendered > 0 && b) {
     const int F = a->include_feature ? a->F : 0;
-    if (launch_render_bwd(F, (const uint2*)(im + L.ranges), (const uint32_t*)(b + L.vals), (const float4*)(g + L.rec),
+    auto* launch = a->bwd_algo == 1 ? launch_render_bwd_shfl : launch_render_bwd;
+    if (launch(F, (const uint2*)(im + L.ranges), (const uint32_t*)(b + L.vals), (const float4*)(g + L.rec),
                           a->W, a->H, gx, gy, a->background, (const float*)(im + L.final_T),
                           (const uint32_t*)(im + L.n_contrib), (const uint32_t*)(im + L.tile_max_contrib),
                           a->dL_dout_color, a->dL_dout_language, a->dL_dout_depth, (float*)a->grad_ws,

@@ -19,8 +19,17 @@ constexpr int TILE_PIX = TILE * TILE;
 constexpr int REC_FLOATS = 16;  // per-Gaussian render record (64 B): see FdlsLayout::rec
 // record slots
 enum { R_X = 0, R_Y = 1, R_CA = 2, R_CB = 3, R_CC = 4, R_OP = 5, R_DEPTH = 6, R_RGB = 7, R_LANG = 10 };
-// per-Gaussian screen-space gradient record (64 B), accumulated by render_bwd, consumed by preprocess_bwd
-enum { G_MX = 0, G_MY = 1, G_CA = 2, G_CB = 3, G_CC = 4, G_OP = 5, G_DEPTH = 6, G_RGB = 7, G_LANG = 10 };
+// per-Gaussian screen-space gradient record (64 B), accumulated by render_bwd, consumed by preprocess_bwd.
+// Slot order follows what the lanes of a quad hold after render_bwd's tensor-core reduction (render_bwd.cu): the first
+// 32-byte sector is the "channel" block (sum of weight x dL_dpixel per colour / depth / language channel), the second
+// the geometry block + the two language channels that do not fit the first.
+enum { G_RGB = 0, G_DEPTH = 3, G_LANG = 4, G_MX = 8, G_MY = 9, G_CA = 10, G_CB = 11, G_CC = 12, G_OP = 13, G_LANG_HI = 14 };
+__host__ __device__ constexpr int g_lang_slot(int k) { return k < 4 ? G_LANG + k : G_LANG_HI + (k - 4); }
+__host__ __device__ constexpr uint32_t g_used_slots(int F, bool depth) {
+  uint32_t m = 0x7u | (0x3fu << G_MX) | (depth ? 1u << G_DEPTH : 0u);
+  for (int k = 0; k < F; ++k) m |= 1u << g_lang_slot(k);
+  return m;
+}
 
 struct V3 {
   float x, y, z;
@@ -143,6 +152,44 @@ __device__ __forceinline__ float2 strip_summary(float gx_, float gy_, float A, f
     }
   }  // otherwise (degenerate / NaN conic): keep every strip
   return make_float2(thr, __uint_as_float(bits));
+}
+
+// Exact per-block visibility of one Gaussian for a tile cut into eight 8x4-pixel blocks (render_bwd.cu: warp w owns
+// block bx = w & 1, by = w >> 1): bit w set iff the block's rectangle of pixel centres can contain a point with
+// power >= thr, i.e. iff the minimum of the quadratic form q(d) = A dx^2 + 2 B dx dy + C dy^2 (power = -q/2) over the
+// rectangle is <= -2 thr.  q is convex with its minimum at the Gaussian's centre, so over a rectangle that does not
+// contain the centre the minimum lies on an edge facing it: on the near vertical edge at dy = clamp(-B dx / C) and on
+// the near horizontal edge at dx = clamp(-B dy / A).  (The bounding box of the level set, used by strip_summary, keeps
+// ~40 % more (warp, Gaussian) pairs for rotated, elongated Gaussians.)  Same slack terms as strip_summary; only ever
+// used to SKIP work the exact reference tests would discard.
+__device__ __forceinline__ uint32_t block_summary(float gx_, float gy_, float A, float B, float Cc, float op, float tile_x0,
+                                                  float tile_y0) {
+  const float thr = -__logf(255.0f * op) - 0.01f;
+  if (thr >= 0.0f) return 0u;  // opacity below 1/255
+  const float det = A * Cc - B * B;
+  if (!(det > 0.0f && A > 0.0f && Cc > 0.0f)) return 0xffu;  // degenerate / NaN conic: keep every block
+  const float K = -2.0f * thr * 1.001f;
+  const float gxr = gx_ - tile_x0, gyr = gy_ - tile_y0;
+  const float nB_A = -B / A, nB_C = -B / Cc;
+  uint32_t bits = 0;
+#pragma unroll
+  for (int bx = 0; bx < 2; ++bx) {
+    const float a0 = gxr - (float)(8 * bx + 7) - 0.05f, a1 = gxr - (float)(8 * bx) + 0.05f;  // d = gauss - pixel
+    const float dxc = fminf(fmaxf(0.f, a0), a1);
+#pragma unroll
+    for (int by = 0; by < 4; ++by) {
+      const float b0 = gyr - (float)(4 * by + 3) - 0.05f, b1 = gyr - (float)(4 * by) + 0.05f;
+      const float dyc = fminf(fmaxf(0.f, b0), b1);
+      const float dy1 = fminf(fmaxf(nB_C * dxc, b0), b1);  // best point of the edge dx = dxc
+      const float q1 = A * dxc * dxc + 2.f * B * dxc * dy1 + Cc * dy1 * dy1;
+      const float dx2 = fminf(fmaxf(nB_A * dyc, a0), a1);  // best point of the edge dy = dyc
+      const float q2 = A * dx2 * dx2 + 2.f * B * dx2 * dyc + Cc * dyc * dyc;
+      // when the centre's column (row) range contains 0 the corresponding edge is the line through the centre and its
+      // candidate is still a point of the rectangle, so min(q1, q2) is attained inside the rectangle in every case
+      if (fminf(q1, q2) <= K) bits |= 1u << (2 * by + bx);
+    }
+  }
+  return bits;
 }
 
 void count_launch(int n = 1);  // api.cu: feeds fdls_kernel_launches()

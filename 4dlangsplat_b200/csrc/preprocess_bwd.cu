@@ -33,7 +33,22 @@ __device__ __forceinline__ void cov3d_build(float3 s, float mod, float4 q, float
   cov3D[5] = Sigma.m[2][2];
 }
 
-template <bool VEC_SH>
+// ACC: add to the outputs instead of overwriting them (FdlsBwdArgs.accumulate: a rank sums the gradients of its
+// views in place, e.g. directly in its slice of the all-reduce bucket; culled Gaussians then write nothing)
+template <bool ACC>
+__device__ __forceinline__ void put(float* p, float v) {
+  *p = ACC ? *p + v : v;
+}
+template <bool ACC>
+__device__ __forceinline__ void put4(float4* p, float4 v) {
+  if (ACC) {
+    const float4 o = *p;
+    v = make_float4(o.x + v.x, o.y + v.y, o.z + v.z, o.w + v.w);
+  }
+  *p = v;
+}
+
+template <bool VEC_SH, bool ACC>
 __global__ void __launch_bounds__(256)
 preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ means3D, const int* __restrict__ radii,
                       const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
@@ -48,6 +63,7 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P) return;
   const bool vis = radii[idx] > 0;
+  if (ACC && !vis) return;  // adds nothing
 
   float g[16];
   if (vis) {
@@ -61,23 +77,23 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
   }
   // pass-through gradients (zeros when culled)
   if (o.means2D) {
-    o.means2D[3 * idx] = g[G_MX];
-    o.means2D[3 * idx + 1] = g[G_MY];
-    o.means2D[3 * idx + 2] = 0.f;
+    put<ACC>(o.means2D + 3 * idx, g[G_MX]);
+    put<ACC>(o.means2D + 3 * idx + 1, g[G_MY]);
+    if (!ACC) o.means2D[3 * idx + 2] = 0.f;
   }
   if (o.colors) {
-    o.colors[3 * idx] = g[G_RGB];
-    o.colors[3 * idx + 1] = g[G_RGB + 1];
-    o.colors[3 * idx + 2] = g[G_RGB + 2];
+    put<ACC>(o.colors + 3 * idx, g[G_RGB]);
+    put<ACC>(o.colors + 3 * idx + 1, g[G_RGB + 1]);
+    put<ACC>(o.colors + 3 * idx + 2, g[G_RGB + 2]);
   }
   if (o.lang) {
 #pragma unroll
     for (int k = 0; k < FDLS_MAX_LANG_CHANNELS; ++k)
-      if (k < F) o.lang[(size_t)idx * F + k] = g[G_LANG + k];
+      if (k < F) put<ACC>(o.lang + (size_t)idx * F + k, g[g_lang_slot(k)]);
   }
-  if (o.opacity) o.opacity[idx] = g[G_OP];
-  if (o.depths) o.depths[idx] = g[G_DEPTH];
-  if (o.conic) reinterpret_cast<float4*>(o.conic)[idx] = make_float4(g[G_CA], g[G_CB], 0.f, g[G_CC]);
+  if (o.opacity) put<ACC>(o.opacity + idx, g[G_OP]);
+  if (o.depths) put<ACC>(o.depths + idx, g[G_DEPTH]);
+  if (o.conic) put4<ACC>(reinterpret_cast<float4*>(o.conic) + idx, make_float4(g[G_CA], g[G_CB], 0.f, g[G_CC]));
 
   // nothing but pass-through gradients wanted (e.g. the fine-lang stage trains the language features only)
   if (!o.means3D && !o.cov3D && !o.sh && !o.scales && !o.rots) return;
@@ -265,14 +281,14 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
           float4* p = reinterpret_cast<float4*>(sh_out);
           const float* f = reinterpret_cast<const float*>(dsh);
 #pragma unroll
-          for (int k = 0; k < 12; ++k) p[k] = make_float4(f[4 * k], f[4 * k + 1], f[4 * k + 2], f[4 * k + 3]);
+          for (int k = 0; k < 12; ++k) put4<ACC>(p + k, make_float4(f[4 * k], f[4 * k + 1], f[4 * k + 2], f[4 * k + 3]));
         } else {
 #pragma unroll
           for (int k = 0; k < 16; ++k)
             if (k < M) {
-              sh_out[3 * k] = dsh[k].x;
-              sh_out[3 * k + 1] = dsh[k].y;
-              sh_out[3 * k + 2] = dsh[k].z;
+              put<ACC>(sh_out + 3 * k, dsh[k].x);
+              put<ACC>(sh_out + 3 * k + 1, dsh[k].y);
+              put<ACC>(sh_out + 3 * k + 2, dsh[k].z);
             }
         }
       }
@@ -318,20 +334,20 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
     }
   }
   if (o.means3D) {
-    o.means3D[3 * idx] = dL_dmeans.x;
-    o.means3D[3 * idx + 1] = dL_dmeans.y;
-    o.means3D[3 * idx + 2] = dL_dmeans.z;
+    put<ACC>(o.means3D + 3 * idx, dL_dmeans.x);
+    put<ACC>(o.means3D + 3 * idx + 1, dL_dmeans.y);
+    put<ACC>(o.means3D + 3 * idx + 2, dL_dmeans.z);
   }
   if (o.cov3D) {
 #pragma unroll
-    for (int i = 0; i < 6; ++i) o.cov3D[6 * idx + i] = dL_dcov[i];
+    for (int i = 0; i < 6; ++i) put<ACC>(o.cov3D + 6 * idx + i, dL_dcov[i]);
   }
   if (o.scales) {
-    o.scales[3 * idx] = dsc[0];
-    o.scales[3 * idx + 1] = dsc[1];
-    o.scales[3 * idx + 2] = dsc[2];
+    put<ACC>(o.scales + 3 * idx, dsc[0]);
+    put<ACC>(o.scales + 3 * idx + 1, dsc[1]);
+    put<ACC>(o.scales + 3 * idx + 2, dsc[2]);
   }
-  if (o.rots) reinterpret_cast<float4*>(o.rots)[idx] = drot;
+  if (o.rots) put4<ACC>(reinterpret_cast<float4*>(o.rots) + idx, drot);
 }
 
 cudaError_t launch_preprocess_bwd(const FdlsBwdArgs* a, const ViewParams& vp, const uint8_t* clamped,
@@ -341,12 +357,15 @@ cudaError_t launch_preprocess_bwd(const FdlsBwdArgs* a, const ViewParams& vp, co
               a->dL_dscales, a->dL_drotations, a->dL_dcov3D, a->dL_dconic, a->dL_ddepths};
   const int grid = cdiv(a->P, 256);
   count_launch();
-  if (a->M == 16)
-    preprocess_bwd_kernel<true><<<grid, 256, 0, st>>>(a->P, a->D, a->M, a->F, a->means3D, a->radii, a->shs, clamped,
-                                                      a->scales, a->rotations, a->cov3D_precomp, vp, grad_rec, o);
-  else
-    preprocess_bwd_kernel<false><<<grid, 256, 0, st>>>(a->P, a->D, a->M, a->F, a->means3D, a->radii, a->shs, clamped,
-                                                       a->scales, a->rotations, a->cov3D_precomp, vp, grad_rec, o);
+#define PB_LAUNCH(VEC, ACCUM)                                                                                        \
+  preprocess_bwd_kernel<VEC, ACCUM><<<grid, 256, 0, st>>>(a->P, a->D, a->M, a->F, a->means3D, a->radii, a->shs, clamped, \
+                                                          a->scales, a->rotations, a->cov3D_precomp, vp, grad_rec, o)
+  if (a->M == 16) {
+    if (a->accumulate) PB_LAUNCH(true, true); else PB_LAUNCH(true, false);
+  } else {
+    if (a->accumulate) PB_LAUNCH(false, true); else PB_LAUNCH(false, false);
+  }
+#undef PB_LAUNCH
   return cudaGetLastError();
 }
 

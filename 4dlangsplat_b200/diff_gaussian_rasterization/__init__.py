@@ -71,6 +71,13 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.out_shapes = (color.shape, language_feature.shape)
         ctx.save_for_backward(colors_precomp, language_feature_precomp, means3D, scales, rotations, cov3Ds_precomp,
                               radii, sh, geomBuffer, binningBuffer, imgBuffer)
+        # leaves registered with a gradient bucket (dist.GradBucket.register): their gradients are accumulated in place
+        ctx.sinks = None
+        if _C.grad_sinks:
+            sk = tuple(_C.grad_sinks.get(t.data_ptr()) for t in (means2D, colors_precomp, language_feature_precomp, opacities,
+                                                           means3D, cov3Ds_precomp, sh, scales, rotations))
+            if any(x is not None for x in sk):
+                ctx.sinks = sk
         ctx.mark_non_differentiable(radii)
         return color, language_feature, radii, depth
 
@@ -96,10 +103,24 @@ class _RasterizeGaussians(torch.autograd.Function):
         # (means3D, means2D, sh, colors, lang, opacities, scales, rotations, cov3D, settings)
         n = ctx.needs_input_grad
         want = (n[1], n[3], n[4], n[5], n[0], n[8], n[2], n[6], n[7])
+        out, acc, owners = None, False, ()
+        if ctx.sinks is not None:
+            # (means2D, colors, lang, opacities, means3D, cov3D, sh, scales, rotations): the native return order
+            out = tuple(k.view if (k is not None and wnt) else None for k, wnt in zip(ctx.sinks, want))
+            owners = {id(k.owner): k.owner for k in ctx.sinks if k is not None}.values()
+            acc = not all(b.fresh for b in owners)  # the iteration's first view overwrites, later ones add
+            if acc:
+                for b in owners:
+                    b.zero_if_fresh()
+        grads = _guarded(
+            lambda *args: _C.rasterize_gaussians_backward(*args, want=want, out=out, accumulate=acc), native_args,
+            rs.debug, "snapshot_bw.dump", "\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
+        for b in owners:
+            b.fresh = False
+        if out is not None:  # gradients that went into a sink are not handed to autograd
+            grads = tuple(None if o is not None else g for g, o in zip(grads, out))
         (grad_means2D, grad_colors_precomp, grad_language_feature_precomp, grad_opacities, grad_means3D,
-         grad_cov3Ds_precomp, grad_sh, grad_scales, grad_rotations) = _guarded(
-             lambda *args: _C.rasterize_gaussians_backward(*args, want=want), native_args, rs.debug, "snapshot_bw.dump",
-             "\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
+         grad_cov3Ds_precomp, grad_sh, grad_scales, grad_rotations) = grads
         # input order of forward(); the settings get no gradient (ref :152-163)
         return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_language_feature_precomp,
                 grad_opacities, grad_scales, grad_rotations, grad_cov3Ds_precomp, None)

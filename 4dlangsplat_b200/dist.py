@@ -34,7 +34,13 @@ def loss_weight(n_local_views, n_views):
 
 class GradBucket:
     """Flat fp32 bucket over the gradients of a fixed list of leaf tensors: one all-reduce per iteration instead of
-    one per parameter group.  The bucket is allocated once (grow-only) and reused."""
+    one per parameter group.  The bucket is allocated once and reused.
+
+    register() (CUDA only) makes the bucket the SINK of the rasterizer's backward for these leaves: the backward
+    kernels of every view of this rank write / add their gradients straight into the bucket's slices
+    (FdlsBwdArgs.accumulate), so there is no per-view gradient tensor, no autograd accumulation pass and no pack()
+    copy before the collective -- the kernel's output buffer IS the collective's buffer.  Without register() (gloo
+    tests on CPU tensors, or leaves that reach the rasterizer through other autograd nodes) pack() copies .grad in."""
 
     def __init__(self, params):
         self.params = [p for p in params if p is not None]
@@ -45,37 +51,94 @@ class GradBucket:
         for p in self.params:
             self.views.append(self.flat[o:o + p.numel()].view_as(p))
             o += p.numel()
+        self.fresh = True       # nothing written this iteration (the first backward overwrites, later ones add)
+        self.registered = False
+        self.work = None
+        self.timing = None      # set to a list to collect (start, end) CUDA event pairs around the collective
 
+    # ---- sink mode -----------------------------------------------------------------------------------------------
+    def register(self):
+        from . import _C
+        for p, v in zip(self.params, self.views):
+            _C.grad_sinks[p.data_ptr()] = _C._Sink(v, self)
+        self.registered = True
+        return self
+
+    def unregister(self):
+        from . import _C
+        for p in self.params:
+            _C.grad_sinks.pop(p.data_ptr(), None)
+        self.registered = False
+
+    def begin(self):
+        """Start of an iteration: the bucket's content is stale."""
+        self.fresh = True
+        if self.registered:
+            for p in self.params:
+                p.grad = None
+
+    def zero_if_fresh(self):
+        if self.fresh:
+            self.flat.zero_()
+            self.fresh = False
+
+    # ---- copy mode -----------------------------------------------------------------------------------------------
     def pack(self):
         for p, v in zip(self.params, self.views):
             if p.grad is None:
                 v.zero_()
-            else:
+            elif p.grad.data_ptr() != v.data_ptr():
                 v.copy_(p.grad)
 
     def unpack(self):
         """Point every .grad at its slice of the reduced bucket (no copy back; the slices stay valid until the next
-        pack(), i.e. until the next iteration's gradients exist)."""
+        iteration's gradients are written)."""
         for p, v in zip(self.params, self.views):
             p.grad = v
 
-    def all_reduce(self):
-        """Sum the bucket over ranks (no-op for a single process).  Returns the bytes each rank contributed."""
-        if world()[1] > 1:
+    def all_reduce(self, async_op=False):
+        """Sum the bucket over ranks.  Returns the bytes each rank contributed.  With async_op the collective is only
+        enqueued (NCCL runs it on its own stream, ordered after the current stream's work); wait() orders the current
+        stream after it -- whatever the caller enqueues in between overlaps the transfer."""
+        if self.registered:
+            self.zero_if_fresh()  # a rank without a view this iteration contributes zeros
+        else:
             self.pack()
-            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
+        if world()[1] > 1:
+            if self.timing is not None and self.flat.is_cuda:
+                e0 = torch.cuda.Event(enable_timing=True)
+                e0.record()
+                self.timing.append([e0, None])
+            self.work = dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, async_op=True)
+            if not async_op:
+                self.wait()
+        else:
             self.unpack()
         return self.flat.numel() * 4
+
+    def wait(self):
+        if self.work is not None:
+            self.work.wait()
+            self.work = None
+            if self.timing is not None and self.timing and self.timing[-1][1] is None:
+                e1 = torch.cuda.Event(enable_timing=True)
+                e1.record()
+                self.timing[-1][1] = e1
+        self.unpack()
+
+    def allreduce_ms(self):
+        """Mean time the compute stream was held by the collective (CUDA events; call after a synchronize)."""
+        t = [a.elapsed_time(b) for a, b in (self.timing or []) if b is not None]
+        return sum(t) / len(t) if t else 0.0
 
 
 def all_reduce_densification_stats(radii, visibility):
     """The reference keeps max radii and the union of visibility filters over the views of a batch
-    (train.py:270-271,390-391): MAX-reduce both over ranks."""
+    (train.py:270-271,390-391): MAX-reduce both over ranks -- as ONE int32 buffer, one collective."""
     if world()[1] > 1:
-        dist.all_reduce(radii, op=dist.ReduceOp.MAX)
-        vis = visibility.to(torch.int32)
-        dist.all_reduce(vis, op=dist.ReduceOp.MAX)
-        visibility = vis.bool()
+        both = torch.stack([radii.to(torch.int32), visibility.to(torch.int32)])
+        dist.all_reduce(both, op=dist.ReduceOp.MAX)
+        radii, visibility = both[0].to(radii.dtype), both[1].bool()
     return radii, visibility
 
 
@@ -88,6 +151,7 @@ def sharded_step(render_view, loss_of_view, n_views, bucket):
     the per-view means, so each rank back-propagates sum_v loss_v / n_views and the all-reduce restores the batch
     gradient.  Returns (local loss contribution, bytes all-reduced)."""
     mine = shard_views(n_views)
+    bucket.begin()
     total = None
     for v in mine:
         l = loss_of_view(v, render_view(v)) / float(n_views)

@@ -348,6 +348,20 @@ def run_ours(wl, steps, warmup, world):
         torch.cuda.synchronize()
         stage_iso = pool1.stage_ms(FRAMES_PER_STEP)
 
+    # ---- what an unchanged caller (render.py's loop: one frame at a time on the current stream, the host waiting for
+    # each frame's instance count) gets: a separate timed region of up to 3 steps, reported as value_one_stream
+    one_steps = max(1, min(3, steps))
+    for i in range(FRAMES_PER_STEP):
+        frame(i)
+    barrier(world)
+    o0, o1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    o0.record()
+    for i in range(one_steps * FRAMES_PER_STEP):
+        frame(i)
+    o1.record()
+    barrier(world)
+    one_ms = max_over_ranks(o0.elapsed_time(o1), world)
+
     # ---- end-to-end arm through the public API with host buffers
     pipe = E2EPipe(wl)
 
@@ -373,7 +387,8 @@ def run_ours(wl, steps, warmup, world):
     sys.stderr.write('e2e: host issue time %.1f us/frame of %.1f us/frame\n' % (1e6 * pipe.host_s / n_frames, 1e6 * e2e_s / n_frames))
     h2d, d2h = pipe.h2d, pipe.d2h  # per frame
     return dict(ms=ms, n_frames=n_frames, stage_ms=stage_ms, stage_iso=stage_iso, R=float(np.mean(Rs)), V=V,
-                launches=int(launches), e2e_s=e2e_s, h2d=h2d * FRAMES_PER_STEP, d2h=d2h * FRAMES_PER_STEP)
+                launches=int(launches), e2e_s=e2e_s, h2d=h2d * FRAMES_PER_STEP, d2h=d2h * FRAMES_PER_STEP,
+                one_stream_fps=one_steps * FRAMES_PER_STEP / (one_ms * 1e-3), host_us=1e6 * pipe.host_s / n_frames)
 
 
 def run_reference(wl, steps, warmup, world):
@@ -462,7 +477,11 @@ def run_train_ours(wl, steps, warmup, world):
     p = {k: v.clone().requires_grad_(True) for k, v in wl.params.items()}
     means2D = torch.zeros_like(p["means3D"], requires_grad=True)
     leaves = list(p.values()) + [means2D]
+    # the rasterizer's backward writes / adds straight into the all-reduce bucket (no autograd sums, no pack copy)
     bucket = fdist.GradBucket(leaves)
+    if os.environ.get("FDLS_BENCH_SINK", "1") != "0":
+        bucket.register()
+    bucket.timing = []
     Rs = []
 
     def render(v):
@@ -482,8 +501,13 @@ def run_train_ours(wl, steps, warmup, world):
         loss, nbytes = fdist.sharded_step(render, loss_of, wl.n_views, bucket)
         return loss, nbytes
 
+    def reset_timing():
+        torch.cuda.synchronize()
+        bucket.timing = []
+
     for _ in range(warmup):
         step()
+    reset_timing()
     barrier(world)
     launches0 = lib.fdls_kernel_launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -494,6 +518,8 @@ def run_train_ours(wl, steps, warmup, world):
     barrier(world)
     launches = lib.fdls_kernel_launches() - launches0
     ms = max_over_ranks(e0.elapsed_time(e1), world)
+    allreduce_ms = max_over_ranks(bucket.allreduce_ms(), world)
+    bucket.timing = None
     # stage split of one more (untimed) iteration, for the roofline line
     fwd_ev, bwd_ev = EventPool(fd._lib.FDLS_FWD_EVENTS, 1), EventPool(fd._lib.FDLS_BWD_EVENTS, 1)
     fd._C.profile["fwd"], fd._C.profile["bwd"] = fwd_ev.arrays[0], bwd_ev.arrays[0]
@@ -528,7 +554,7 @@ def run_train_ours(wl, steps, warmup, world):
     e2e_s = max_over_ranks(t1 - t0, world)
     V = int((torch.as_tensor(0)).item())
     return dict(ms=ms, n_frames=steps, stage_ms=fwd_ev.stage_ms(1), bwd_stage_ms=bwd_ev.stage_ms(1), R=float(R), V=V,
-                launches=int(launches), e2e_s=e2e_s, h2d=h2d, d2h=4, allreduce_bytes=nbytes)
+                launches=int(launches), e2e_s=e2e_s, h2d=h2d, d2h=4, allreduce_bytes=nbytes, allreduce_ms=allreduce_ms)
 
 
 def run_train_reference(wl, steps, warmup, world):
@@ -675,6 +701,7 @@ def main_train(a, rank, world, local, warmup):
         line["stages_ms"] = dict(zip(names, [round(float(x), 4) for x in r["stage_ms"]]))
         line["stages_ms"].update({"bwd_zero": round(bwd[0], 4), "render_bwd": round(bwd[1], 4), "preprocess_bwd": round(bwd[2], 4)})
         line["allreduce_bytes_per_step"] = r["allreduce_bytes"]
+        line["allreduce_ms"] = round(r["allreduce_ms"], 4)  # compute stream held by the collective, max over ranks
     else:
         line["impl"] = "reference"
         line["cpu_baseline"] = {"value": line["value"], "unit": "iters/s", "cores": 1, "kind": "reference",

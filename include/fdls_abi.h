@@ -168,6 +168,13 @@ typedef struct FdlsBwdArgs {
   float* dL_ddepths;   /* (P) optional */
   /* optional: FDLS_BWD_EVENTS cudaEvent_t handles: [0] start, [1] zero-fill, [2] compositor bwd, [3] preprocess bwd */
   void** stage_events;
+  /* compositor backward: 0 = tensor-core reduction of the per-pixel terms (render_bwd.cu, default),
+   * 1 = round-1 warp-shuffle butterfly (render_bwd_shfl.cu), kept for A/B measurements.  Same results to rounding. */
+  int32_t bwd_algo;
+  /* non-zero: ADD this view's gradients to the output arrays instead of overwriting them (the caller zero-fills
+   * before the first view).  Lets a rank sum the views of its shard directly inside its all-reduce bucket
+   *  -- no autograd accumulation pass, no pack copy.  The reference always overwrites. */
+  int32_t accumulate;
 } FdlsBwdArgs;
 #define FDLS_BWD_EVENTS 4
 

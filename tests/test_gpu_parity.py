@@ -506,6 +506,55 @@ def test_autograd_function_matches_native_backward(synth, fdls):
     _assert_grad(lang2.grad, g2.lang, "frozen-inputs dL_dlang")
 
 
+def test_gradient_bucket_sink_equals_autograd_accumulation(synth, fdls):
+    """dist.GradBucket.register(): the backward kernels of a rank's views write / add straight into the all-reduce
+    bucket (FdlsBwdArgs.accumulate) instead of autograd summing per-view gradient tensors.  Three views of one scene:
+    the bucket must hold the sum autograd produces, .grad must alias the bucket, and a second iteration must not
+    see the first one's content."""
+    import importlib
+    fdist = importlib.import_module("4dlangsplat_b200.dist")
+    dgr = fdls.diff_gaussian_rasterization
+    views = [synth.scene("small", view_index=v, n_views=3) for v in range(3)]
+    s = views[0]
+    t = lambda a, rg=False: torch.tensor(a, device="cuda", requires_grad=rg)
+
+    def leaves():
+        p = dict(means3D=t(s.means3D, True), shs=t(s.shs, True), lang=t(s.language_feature, True),
+                 opac=t(s.opacities, True), scales=t(s.scales, True), rots=t(s.rotations, True))
+        p["means2D"] = torch.zeros_like(p["means3D"], requires_grad=True)
+        return p
+
+    ups = [synth.upstream_grads(sv, n_views=3, seed=11 + i) for i, sv in enumerate(views)]
+
+    def loss(p):
+        total = None
+        for sv, (dcol, dlang, _) in zip(views, ups):
+            rs = dgr.GaussianRasterizationSettings(sv.H, sv.W, sv.tanfovx, sv.tanfovy, t(sv.bg), 1.0, t(sv.viewmatrix),
+                                                   t(sv.projmatrix), sv.sh_degree, t(sv.campos), False, False, True)
+            color, feat, radii, depth = dgr.GaussianRasterizer(rs)(
+                p["means3D"], p["means2D"], p["opac"], shs=p["shs"], language_feature_precomp=p["lang"],
+                scales=p["scales"], rotations=p["rots"])
+            l = (color * t(dcol)).sum() + (feat * t(dlang)).sum()
+            total = l if total is None else total + l
+        return total
+
+    ref = leaves()
+    loss(ref).backward()
+    p = leaves()
+    bucket = fdist.GradBucket(list(p.values())).register()
+    try:
+        for it in range(2):
+            bucket.begin()
+            loss(p).backward()
+            bucket.all_reduce()
+            for k in p:
+                assert p[k].grad is not None and p[k].grad.data_ptr() == bucket.views[list(p).index(k)].data_ptr()
+                _assert_grad(p[k].grad, ref[k].grad, "sink dL_d%s (iteration %d)" % (k, it))
+    finally:
+        bucket.unregister()
+    assert not fdls._C.grad_sinks
+
+
 @pytest.mark.parametrize("F", [3, 6])
 def test_against_committed_golden_vectors(synth, F):
     """The product path against tests/golden/ref_tiny_f{F}.npz (outputs of the reference CUDA build, committed): the
