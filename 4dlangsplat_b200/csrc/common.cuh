@@ -162,18 +162,18 @@ __device__ __forceinline__ float2 strip_summary(float gx_, float gy_, float A, f
 // the near horizontal edge at dx = clamp(-B dy / A).  (The bounding box of the level set, used by strip_summary, keeps
 // ~40 % more (warp, Gaussian) pairs for rotated, elongated Gaussians.)  Same slack terms as strip_summary; only ever
 // used to SKIP work the exact reference tests would discard.
+// `bx` selects the block column evaluated by this call (two lanes share a Gaussian and OR their results).
 __device__ __forceinline__ uint32_t block_summary(float gx_, float gy_, float A, float B, float Cc, float op, float tile_x0,
-                                                  float tile_y0) {
+                                                  float tile_y0, int bx) {
   const float thr = -__logf(255.0f * op) - 0.01f;
   if (thr >= 0.0f) return 0u;  // opacity below 1/255
   const float det = A * Cc - B * B;
-  if (!(det > 0.0f && A > 0.0f && Cc > 0.0f)) return 0xffu;  // degenerate / NaN conic: keep every block
+  if (!(det > 0.0f && A > 0.0f && Cc > 0.0f)) return 0x55u << bx;  // degenerate / NaN conic: keep every block
   const float K = -2.0f * thr * 1.001f;
   const float gxr = gx_ - tile_x0, gyr = gy_ - tile_y0;
   const float nB_A = -B / A, nB_C = -B / Cc;
   uint32_t bits = 0;
-#pragma unroll
-  for (int bx = 0; bx < 2; ++bx) {
+  {
     const float a0 = gxr - (float)(8 * bx + 7) - 0.05f, a1 = gxr - (float)(8 * bx) + 0.05f;  // d = gauss - pixel
     const float dxc = fminf(fmaxf(0.f, a0), a1);
 #pragma unroll

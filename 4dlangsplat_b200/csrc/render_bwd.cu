@@ -30,6 +30,7 @@
 //  * warps in which no pixel is touched by the Gaussian skip it with one ballot; the traversal starts at the tile's
 //    deepest contributor (tile_max_contrib, written by render_fwd); records are gathered with cp.async into a
 //    double-buffered shared ring exactly like the forward.
+#include <cstddef>
 #include "common.cuh"
 
 namespace fdls {
@@ -74,21 +75,20 @@ __device__ __forceinline__ void rb_cp_async_wait() {
 // bank groups, and the per-step stores (32 lanes, one row) stay a permutation of the banks.  No padding: 3 CTAs / SM.
 __device__ __forceinline__ int rb_col(int g, int s) { return s ^ ((g & 7) << 2); }
 
-__device__ __forceinline__ uint32_t to_tf32(float x) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-  return r;
-}
-// x = hi + lo with hi, lo both TF32-representable up to 2^-22 |x|
+// TF32 operand splits.  The tensor core reads only the upper 19 bits of an operand register, so `x & 0xffffe000` IS
+// the TF32 value the hardware would see, and x minus it is exact in fp32.  (cvt.rna.tf32.f32 has no single-instruction
+// form on sm_100a -- ptxas expands it to ~5 integer instructions -- so rounding the split cost 4x more than the MMAs.)
+//   2-way: x = hi + lo, lo passed as is (the hardware truncates it to 11 bits: error < 2^-20 |x|)
+//   3-way: x = h1 + h2 + h3 EXACTLY (11 + 11 + 2 significant bits)
 __device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
-  hi = to_tf32(x);
-  lo = to_tf32(x - __uint_as_float(hi));
+  hi = __float_as_uint(x) & 0xffffe000u;
+  lo = __float_as_uint(x - __uint_as_float(hi));
 }
 __device__ __forceinline__ void split3_tf32(float x, uint32_t& h1, uint32_t& h2, uint32_t& h3) {
-  h1 = to_tf32(x);
+  h1 = __float_as_uint(x) & 0xffffe000u;
   const float r1 = x - __uint_as_float(h1);
-  h2 = to_tf32(r1);
-  h3 = __float_as_uint(r1 - __uint_as_float(h2));  // <= 2 significant bits left: already a TF32 value
+  h2 = __float_as_uint(r1) & 0xffffe000u;
+  h3 = __float_as_uint(r1 - __uint_as_float(h2));
 }
 __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile(
@@ -198,6 +198,13 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   const float cx = (float)(tx * TILE + bx0) + 3.5f, cy = (float)(ty * TILE + by0) + 1.5f;
   const float half_W = 0.5f * W, half_H = 0.5f * H;  // ddelx_dx, ddely_dy (backward.cu:507-508)
 
+  // byte offset of this lane inside a parked row, kept opaque so that it stays in a register (under the 80-register
+  // cap the compiler otherwise re-derives it from %tid every step)
+  uint32_t lane4, park_w;  // park_w: shared-window address of this warp's first parked row (sm.u is sizeof(sm.w) above)
+  asm volatile("mov.u32 %0, %1;" : "=r"(lane4) : "r"(lane * 4));
+  asm volatile("mov.u32 %0, %1;" : "=r"(park_w) : "r"((uint32_t)__cvta_generic_to_shared(sm.w[warp])));
+  static_assert(offsetof(RbSmem<NCH>, u) - offsetof(RbSmem<NCH>, w) == sizeof(float) * RB_WARPS * RB_GROUP * RB_ASTRIDE,
+                "sm.u must follow sm.w");
   int n_pend = 0;  // rows parked in sm.w / sm.u of this warp (warp-uniform)
   int my_j = 0;    // lane r < n_pend: where row r's Gaussian lives (index into the current batch, or RB_STASHED)
   float* const row_w = sm.w[warp];
@@ -326,11 +333,17 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     } else {
       rb_cp_async_wait<0>();
     }
-    __syncthreads();  // both halves of every record have landed
+    __syncwarp();  // the two lanes that gathered a record see each other's half
     const int cnt = min(RB_BATCH, M - i * RB_BATCH);
-    if (tid < cnt) {
-      const float4 r0 = sm.rec[buf][0][tid], r1 = sm.rec[buf][1][tid];
-      sm.blocks[buf][tid] = block_summary(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, (float)(tx * TILE), (float)(ty * TILE));
+    {
+      const int slot = tid >> 1;
+      uint32_t bits = 0;
+      if (slot < cnt) {
+        const float4 r0 = sm.rec[buf][0][slot], r1 = sm.rec[buf][1][slot];
+        bits = block_summary(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, (float)(tx * TILE), (float)(ty * TILE), tid & 1);
+      }
+      bits |= __shfl_xor_sync(RB_FULL, bits, 1);  // lane pair = block columns bx 0 and 1
+      if ((tid & 1) == 0) sm.blocks[buf][slot] = bits;
     }
     __syncthreads();
     // per-warp compaction of the batch to the Gaussians that can reach this warp's block (as in render_fwd.cu)
@@ -386,10 +399,12 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         A += alpha * diff;  // accum_rec <- alpha * c + (1 - alpha) * accum_rec, dotted with dL_dpixel
         u = G * dL_dalpha;
       }
-      const int col = n_pend * RB_ASTRIDE + rb_col(n_pend, lane);
-      row_w[col] = w;
-      row_u[col] = u;
-      if (lane == n_pend) my_j = j;
+      // row n_pend, word rb_col(n_pend, lane)
+      const uint32_t addr = park_w + (uint32_t)n_pend * (RB_ASTRIDE * 4) + (lane4 ^ ((uint32_t)(n_pend & 7) << 4));
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(w) : "memory");
+      asm volatile("st.shared.f32 [%0+%2], %1;" ::"r"(addr), "f"(u), "n"(sizeof(float) * RB_WARPS * RB_GROUP * RB_ASTRIDE)
+                   : "memory");
+      if (lane4 == (uint32_t)n_pend * 4) my_j = j;
       if (++n_pend == RB_GROUP) {
         __syncwarp();
         flush_group(RB_GROUP, buf);
