@@ -10,9 +10,10 @@
 //    double-buffered 2 x 16 KB shared-memory ring, so the gather of batch i+1 overlaps the blend of batch i.
 //    The reference instead gathers colour / language / depth from GLOBAL memory per contributing (pixel, Gaussian)
 //    pair (forward.cu:362-369).
-//  * each warp owns a 16x2-pixel strip; the staging thread computes a conservative strip mask per Gaussian and every
-//    warp compacts the batch to the Gaussians that can touch its strip before blending (most of a tile's list misses
-//    any given strip, and skipping them one by one was the dominant instruction cost).
+//  * each warp owns an 8x4-pixel block; the staging thread computes an exact per-block visibility mask per Gaussian
+//    (common.cuh block_summary: minimum of the conic form over the block's rectangle) and every warp compacts the
+//    batch to the Gaussians that can touch its block before blending (most of a tile's list misses any given block,
+//    and skipping them one by one was the dominant instruction cost).
 //  * a conservative log-domain pre-test skips the expf for pairs whose alpha is certainly below 1/255; the exact
 //    reference test still decides every pair near the threshold, so results do not change.
 //  * F is a template parameter dispatched at run time (the reference needs a rebuild per F: setup.py:18,32).
@@ -40,19 +41,21 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   float* __restrict__ out_color, float* __restrict__ out_lang, float* __restrict__ out_depth) {
   // [buf][slot 0..3][thread]: conflict-free cp.async writes, broadcast reads
   __shared__ float4 s_rec[2][4][RF_THREADS];
-  __shared__ float2 s_aux[2][RF_THREADS];  // strip_summary() of each staged Gaussian
+  __shared__ float2 s_aux[2][RF_THREADS];  // {alpha-threshold in the log domain, block_summary()} of each staged Gaussian
   __shared__ uint8_t s_list[RF_THREADS / 32][RF_THREADS];  // per-warp compacted indices into the staged batch
   __shared__ uint32_t s_max;
 
   const int tid = threadIdx.x;
   const uint32_t tile = blockIdx.x;
   const uint32_t tx = tile % gx, ty = tile / gx;
-  const uint2 pix = {tx * TILE + (tid & (TILE - 1)), ty * TILE + (tid >> 4)};
+  const int lane = tid & 31, warp = tid >> 5;
+  // warp w owns the 8x4-pixel block bx = w & 1, by = w >> 1 of the tile (a compact footprint: fewer Gaussians reach it
+  // than reach a 16x2 strip, and block_summary() tests the block exactly)
+  const uint2 pix = {tx * TILE + (warp & 1) * 8 + (lane & 7), ty * TILE + (warp >> 1) * 4 + (lane >> 3)};
   const uint32_t pix_id = W * pix.y + pix.x;
   const float2 pixf = {(float)pix.x, (float)pix.y};
   const bool inside = pix.x < (uint32_t)W && pix.y < (uint32_t)H;
   bool done = !inside;
-  const int lane = tid & 31, warp = tid >> 5;
   const uint32_t strip_bit = 1u << warp;
   const uint32_t lt_mask = (1u << lane) - 1u;
 
@@ -90,12 +93,15 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     }
     {  // my own staged record (own cp.async data is visible to the issuing thread after the wait)
       const float4 r0 = s_rec[buf][0][tid], r1 = s_rec[buf][1][tid];
-      s_aux[buf][tid] = strip_summary(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, (float)(tx * TILE), (float)(ty * TILE));
+      const float x0 = (float)(tx * TILE), y0 = (float)(ty * TILE);
+      const uint32_t bits = block_summary(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, x0, y0, 0) |
+                            block_summary(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, x0, y0, 1);
+      s_aux[buf][tid] = make_float2(-__logf(255.0f * r1.y) - 0.01f, __uint_as_float(bits));  // .x: see strip_summary
     }
     __syncthreads();
 
     const int cnt = min(RF_THREADS, toDo);
-    // Per-warp compaction: the indices of the staged Gaussians that can reach this warp's 16x2 strip are gathered
+    // Per-warp compaction: the indices of the staged Gaussians that can reach this warp's 8x4 block are gathered
     // (in order) into a private list, so the blend loop never iterates over a Gaussian the whole warp would skip.
     // `contributor` is the 1-based position in the tile's range, exactly the reference's running counter.
     int n_hit = 0;

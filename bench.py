@@ -532,6 +532,19 @@ def run_train_ours(wl, steps, warmup, world):
     torch.cuda.synchronize()
     st = fd._C._dev_state(torch.device("cuda", torch.cuda.current_device()))
     R = st["last_R"] or 0
+    # instances the backward stages: its traversal of a tile starts at the tile's deepest contributor
+    R_staged = 0
+    if wl.mine:
+        c = wl.views[wl.mine[0]]
+        E = torch.Tensor([])
+        with torch.no_grad():
+            o = fd._C.rasterize_gaussians(wl.bg, p["means3D"].detach(), E, p["lang"].detach(), p["opac"].detach(),
+                                          p["scales"].detach(), p["rots"].detach(), 1.0, E, c["view"], c["proj"],
+                                          s.tanfovx, s.tanfovy, s.H, s.W, p["shs"].detach(), s.sh_degree, c["campos"],
+                                          False, False, True)
+        L = fd._lib.workspace_layout(s.P, s.W, s.H, 0)
+        tiles = ((s.W + 15) // 16) * ((s.H + 15) // 16)
+        R_staged = int(o[7][L.tile_max_contrib:L.tile_max_contrib + 4 * tiles].view(torch.int32).sum())
     # e2e: same step, camera + upstream image gradients arrive from pinned host memory, the loss is read back
     host = {v: {k: x.cpu().pin_memory() for k, x in c.items()} for v, c in wl.views.items()}
     h2d = sum(x.numel() * 4 for c in host.values() for x in c.values())
@@ -554,7 +567,8 @@ def run_train_ours(wl, steps, warmup, world):
     e2e_s = max_over_ranks(t1 - t0, world)
     V = int((torch.as_tensor(0)).item())
     return dict(ms=ms, n_frames=steps, stage_ms=fwd_ev.stage_ms(1), bwd_stage_ms=bwd_ev.stage_ms(1), R=float(R), V=V,
-                launches=int(launches), e2e_s=e2e_s, h2d=h2d, d2h=4, allreduce_bytes=nbytes, allreduce_ms=allreduce_ms)
+                launches=int(launches), e2e_s=e2e_s, h2d=h2d, d2h=4, allreduce_bytes=nbytes, allreduce_ms=allreduce_ms,
+                R_staged=R_staged)
 
 
 def run_train_reference(wl, steps, warmup, world):
@@ -661,29 +675,30 @@ def stage_bytes(P, V, R, HW, T, F):
             "tile_ranges": 8 * R + 8 * T, "render": (44 + 4 * F) * R + (24 + 4 * F) * HW}
 
 
-def main_train(a, rank, world, local, warmup):
-    """BASELINE.json configs[2]: training step (rasterizer fwd+bwd) over a batch of views sharded over the ranks,
-    per-Gaussian gradients all-reduced once per iteration.  The batch is fixed => strong scaling."""
-    name = a.workload if a.workload != "cfg2" else "cfg3"
-    wl = TrainWorkload(name, rank, world)
+def train_line(a, rank, world, local, warmup, name, n_views, steps):
+    """One JSON object for the training step: BASELINE.json configs[2] (cfg3: batch of views of the cfg2-shaped scene,
+    rasterizer forward+backward, views sharded over the ranks, per-Gaussian gradients all-reduced once per iteration;
+    the batch is fixed => strong scaling) or configs[4] (cfg5)."""
+    wl = TrainWorkload(name, rank, world, n_views=n_views)
     s = wl.s
     sampler = ClockSampler(local)
     sampler.start()
-    r = (run_train_ours if a.impl == "ours" else run_train_reference)(wl, a.steps, warmup, world)
+    r = (run_train_ours if a.impl == "ours" else run_train_reference)(wl, steps, warmup, world)
     clocks = sampler.result()
-    value = a.steps / (r["ms"] * 1e-3)
+    value = steps / (r["ms"] * 1e-3)
     line = {
-        "metric": "train_iters_per_s", "value": round(value, 3), "unit": "iters/s", "n_gpus": world, "steps": a.steps,
-        "warmup": warmup, "ms_per_step": round(r["ms"] / a.steps, 4), "higher_is_better": True, "scaling": "strong",
+        "metric": "train_iters_per_s", "value": round(value, 3), "unit": "iters/s", "n_gpus": world, "steps": steps,
+        "warmup": warmup, "ms_per_step": round(r["ms"] / steps, 4), "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "%s: %d Gaussians, %dx%d, F=%d, rasterizer forward+backward, batch of %d views "
                                "(deformation network out of scope, SURVEY 8f N1)" % (name, s.P, s.W, s.H, s.F, wl.n_views),
-                   "views_per_rank": len(wl.mine), "instances_per_view": round(r["R"]),
-                   "sharding": "views round-robin over ranks; one flat fp32 all-reduce of the leaf gradients per step",
+                   "batch_views": wl.n_views, "views_per_rank": len(wl.mine), "instances_per_view": round(r["R"]),
+                   "sharding": "views round-robin over ranks; the backward kernels accumulate into one flat fp32 "
+                               "bucket per rank, all-reduced (NCCL) once per step",
                    "l2": "per-view working set (records 19 MB + instance lists + 5 images) is re-streamed for every view; "
-                         "4 views x (SH 58 MB + gradient outputs 90 MB) exceed the 126 MB L2 between reuses"},
+                         "the views' SH reads (58 MB) and gradient outputs (78 MB) exceed the 126 MB L2 between reuses"},
         "clocks": clocks,
-        "e2e": {"value": round(a.steps / r["e2e_s"], 3), "unit": "iters/s", "h2d_bytes_per_step": r["h2d"],
+        "e2e": {"value": round(steps / r["e2e_s"], 3), "unit": "iters/s", "h2d_bytes_per_step": r["h2d"],
                 "d2h_bytes_per_step": r["d2h"]},
         "gpu_launches": r["launches"],
     }
@@ -691,12 +706,14 @@ def main_train(a, rank, world, local, warmup):
         pk, pk_kind = peaks()
         HW = s.W * s.H
         bwd = [float(x) for x in r["bwd_stage_ms"]]  # zero-fill, compositor bwd, preprocess bwd
-        bytes_rb = (44 + 4 * s.F) * r["R"] + (24 + 4 * s.F) * HW + (48 + 4 * s.F) * s.P
+        # instances the backward actually stages: the traversal starts at each tile's deepest contributor
+        R_staged = r.get("R_staged") or r["R"]
+        bytes_rb = (44 + 4 * s.F) * R_staged + (24 + 4 * s.F) * HW + (48 + 4 * s.F) * s.P
         ach = bytes_rb / (bwd[1] * 1e-3) / 1e9 if bwd[1] > 0 else 0.0
         line["roofline"] = {"bound": "hbm", "kernel": "render_bwd", "achieved": round(ach, 1), "peak": pk["hbm_gbs"],
                             "unit": "GB/s", "frac": round(ach / pk["hbm_gbs"], 4), "traffic": None,
                             "peak_source": pk_kind, "algorithmic_bytes_per_launch": int(bytes_rb),
-                            "avg_launch_ms": round(bwd[1], 4)}
+                            "instances_staged": int(R_staged), "avg_launch_ms": round(bwd[1], 4)}
         names = ["preprocess", "scan", "duplicate", "sort", "tile_ranges", "render"]
         line["stages_ms"] = dict(zip(names, [round(float(x), 4) for x in r["stage_ms"]]))
         line["stages_ms"].update({"bwd_zero": round(bwd[0], 4), "render_bwd": round(bwd[1], 4), "preprocess_bwd": round(bwd[2], 4)})
@@ -706,6 +723,15 @@ def main_train(a, rank, world, local, warmup):
         line["impl"] = "reference"
         line["cpu_baseline"] = {"value": line["value"], "unit": "iters/s", "cores": 1, "kind": "reference",
                                 "sample": "reference CUDA rasterizer fwd+bwd (oracle/_ref) on one B200, all %d views" % wl.n_views}
+    del wl
+    torch.cuda.empty_cache()
+    return line
+
+
+def main_train(a, rank, world, local, warmup):
+    name = a.workload if a.workload != "cfg2" else "cfg3"
+    n_views = int(os.environ.get("FDLS_TRAIN_VIEWS", "0")) or ({"cfg5": 8}.get(name, max(TRAIN_VIEWS, a.gpus)))
+    line = train_line(a, rank, world, local, warmup, name, n_views, a.steps)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -909,15 +935,27 @@ def main():
         line["stages_gbs"] = {k: round(sb[k] / (st[k] * 1e-3) / 1e9, 1) if st[k] > 0 else None for k in names}
         line["whole_path"] = {"algorithmic_bytes_per_frame": int(total_b),
                               "achieved_gbs": round(total_b / (r["ms"] / r["n_frames"] * 1e-3) / 1e9, 1)}
+        # what render.py gets without the pipelined sweep: one frame at a time on the current stream
+        line["value_one_stream"] = round(r["one_stream_fps"] * world, 2)
+        line["e2e_host_issue_us_per_frame"] = round(r["host_us"], 1)
         if rank == 0 and world == 1 and not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl)
     else:
+        line["value_one_stream"] = line["value"]  # the reference has one path: the legacy default stream
         line["impl"] = "reference"
         line["cpu_baseline"] = {"value": line["value"], "unit": "frames/s", "cores": 1, "kind": "reference",
                                 "sample": "the reference has no CPU rasterizer: its own CUDA rasterizer "
                                           "(cuda_rasterizer/*.cu, unmodified, rebuilt for sm_100a into oracle/_ref) is "
                                           "timed on the same B200 over the same %d frames; 1 host thread drives it"
                                           % r["n_frames"]}
+    # the other half of BASELINE.json's metric: training iterations/s (cfg3, batch = max(4, N) views) at this N
+    if a.workload == "cfg2" and os.environ.get("FDLS_BENCH_TRAIN", "1") != "0":
+        del wl
+        torch.cuda.empty_cache()
+        t = train_line(a, rank, world, local, warmup, "cfg3", max(TRAIN_VIEWS, a.gpus), a.steps)
+        line["train"] = {k: t[k] for k in ("metric", "value", "unit", "ms_per_step", "scaling", "config", "e2e",
+                                            "gpu_launches", "roofline", "stages_ms", "allreduce_bytes_per_step",
+                                            "allreduce_ms", "clocks") if k in t}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
