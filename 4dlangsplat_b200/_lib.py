@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfdls.so")
+LIB_PATH = os.environ.get("FDLS_LIB", os.path.join(_HERE, "libfdls.so"))  # FDLS_LIB: an A/B build of the same ABI
 
 FDLS_MAX_LANG_CHANNELS = 6
 FDLS_TILE = 16

@@ -9,7 +9,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "libfdls.so")
+LIB = os.environ.get("FDLS_LIB", os.path.join(HERE, "libfdls.so"))  # FDLS_LIB / FDLS_NVCC_EXTRA: A/B builds
 SOURCES = ["api.cu", "preprocess_fwd.cu", "binning.cu", "binning_partition.cu", "radix_sort.cu", "render_fwd.cu", "render_bwd.cu", "render_bwd_shfl.cu",
            "preprocess_bwd.cu", "knn.cu", "hexplane.cu"]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler",
@@ -22,7 +22,8 @@ def _stale(out, deps):
 
 def build(force=False, verbose=False):
     """Compile each translation unit to an object (in parallel) and link the shared library.  Returns its path."""
-    objdir = os.path.join(HERE, "build")
+    extra = os.environ.get("FDLS_NVCC_EXTRA", "").split()
+    objdir = os.path.join(HERE, "build" + ("_" + "".join(c for c in "".join(extra) if c.isalnum()) if extra else ""))
     os.makedirs(objdir, exist_ok=True)
     hdrs = [os.path.join(CSRC, "common.cuh"), os.path.join(HERE, "..", "include", "fdls_abi.h"), os.path.abspath(__file__)]
     procs, objs = [], []
@@ -31,7 +32,7 @@ def build(force=False, verbose=False):
         obj = os.path.join(objdir, s.replace(".cu", ".o"))
         objs.append(obj)
         if force or _stale(obj, [src] + hdrs):
-            cmd = ["nvcc", "-c", "-o", obj, src] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else [])
+            cmd = ["nvcc", "-c", "-o", obj, src] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else [])
             procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     failed = False
     for s, p in procs:

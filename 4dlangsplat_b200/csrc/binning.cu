@@ -49,6 +49,7 @@ __global__ void __launch_bounds__(SCAN_THREADS)
 scan_reduce_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __restrict__ order,
                    uint32_t* __restrict__ block_sums, uint32_t* __restrict__ num_rendered, long long capacity,
                    uint32_t* host_mirror) {
+  pdl_grid_sync();
   __shared__ uint32_t s_warp[33];
   __shared__ uint32_t s_last;
   const int base = blockIdx.x * SCAN_TILE;
@@ -95,6 +96,7 @@ scan_reduce_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __res
 __global__ void __launch_bounds__(1024)
 scan_spine_kernel(int nblocks, uint32_t* __restrict__ block_sums, uint32_t* __restrict__ num_rendered,
                   long long capacity, uint32_t* host_mirror) {
+  pdl_grid_sync();
   __shared__ uint32_t s_warp[33];
   uint32_t carry = 0;
   for (int base = 0; base < nblocks; base += 1024) {
@@ -120,6 +122,7 @@ scan_spine_kernel(int nblocks, uint32_t* __restrict__ block_sums, uint32_t* __re
 __global__ void __launch_bounds__(SCAN_THREADS)
 scan_apply_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __restrict__ order,
                   const uint32_t* __restrict__ block_sums, uint32_t* __restrict__ out) {
+  pdl_grid_sync();
   __shared__ uint32_t s_warp[33];
   // blocked arrangement: thread t owns items [t*ITEMS, t*ITEMS+ITEMS) of the block tile
   const int base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
@@ -187,6 +190,7 @@ duplicate_keys_kernel(int P, const float4* __restrict__ rec, const uint32_t* __r
                       const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
                       uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, int gx, int gy, long long capacity,
                       uint32_t* __restrict__ global_hist, int passes) {
+  pdl_grid_sync();
   __shared__ uint32_t s_hist[DUP_MAX_PASSES][256];
   for (int i = threadIdx.x; i < DUP_MAX_PASSES * 256; i += blockDim.x) (&s_hist[0][0])[i] = 0;
   __syncthreads();
@@ -267,6 +271,7 @@ duplicate_keys_kernel(int P, const float4* __restrict__ rec, const uint32_t* __r
 __global__ void __launch_bounds__(256)
 tile_ranges_kernel(const uint32_t* __restrict__ num_rendered, long long capacity, const uint64_t* __restrict__ keys,
                    uint2* __restrict__ ranges) {
+  pdl_grid_sync();
   const long long L = min((long long)num_rendered[0], capacity);
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= L) return;
@@ -290,13 +295,12 @@ cudaError_t launch_scan(int P, const uint32_t* tiles_touched, const uint32_t* or
                         cudaStream_t st) {
   const int nb = cdiv(P, SCAN_TILE);
   if (P > 0) {
-    scan_reduce_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, order, block_sums, num_rendered, capacity,
-                                                    host_mirror);
+    launch_pdl(scan_reduce_kernel, dim3(nb), dim3(SCAN_THREADS), 0, st, P, tiles_touched, order, block_sums, num_rendered, capacity, host_mirror);
     count_launch();
   } else {
-    scan_spine_kernel<<<1, 1024, 0, st>>>(nb, block_sums, num_rendered, capacity, host_mirror); count_launch();
+    launch_pdl(scan_spine_kernel, dim3(1), dim3(1024), 0, st, nb, block_sums, num_rendered, capacity, host_mirror); count_launch();
   }
-  if (P > 0) { scan_apply_kernel<<<nb, SCAN_THREADS, 0, st>>>(P, tiles_touched, order, block_sums, offsets); count_launch(); }
+  if (P > 0) { launch_pdl(scan_apply_kernel, dim3(nb), dim3(SCAN_THREADS), 0, st, P, tiles_touched, order, block_sums, offsets); count_launch(); }
   return cudaGetLastError();
 }
 
@@ -305,8 +309,7 @@ cudaError_t launch_duplicate(int P, const float4* rec, const uint32_t* order, co
                              uint32_t* global_hist, int passes, cudaStream_t st) {
   if (P == 0) return cudaSuccess;
   if (passes > DUP_MAX_PASSES) return cudaErrorInvalidValue;
-  duplicate_keys_kernel<<<cdiv(P, 256), 256, 0, st>>>(P, rec, order, offsets, radii, keys, vals, gx, gy, capacity,
-                                                      global_hist, passes); count_launch();
+  launch_pdl(duplicate_keys_kernel, dim3(cdiv(P, 256)), dim3(256), 0, st, P, rec, order, offsets, radii, keys, vals, gx, gy, capacity, global_hist, passes); count_launch();
   return cudaGetLastError();
 }
 
@@ -314,7 +317,7 @@ cudaError_t launch_tile_ranges(const uint32_t* num_rendered, long long n_grid, l
                                uint2* ranges, int tiles, cudaStream_t st) {
   cudaError_t e = cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), st);
   if (e != cudaSuccess) return e;
-  if (n_grid > 0) { tile_ranges_kernel<<<cdiv(n_grid, 256), 256, 0, st>>>(num_rendered, capacity, keys, ranges); count_launch(); }
+  if (n_grid > 0) { launch_pdl(tile_ranges_kernel, dim3(cdiv(n_grid, 256)), dim3(256), 0, st, num_rendered, capacity, keys, ranges); count_launch(); }
   return cudaGetLastError();
 }
 

@@ -224,6 +224,7 @@ part_count_kernel(int P, int T, const uint32_t* __restrict__ num_rendered,
                   const uint32_t* __restrict__ depth_hist, const uint32_t* __restrict__ order,
                   const uint32_t* __restrict__ offsets, const int* __restrict__ radii, const float4* __restrict__ rec,
                   int gx, int gy, uint32_t* __restrict__ table) {
+  pdl_grid_sync();
   extern __shared__ uint32_t pt_smem[];
   const int words = (T + 1) / 2;  // per-warp counter words
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -256,6 +257,7 @@ __global__ void __launch_bounds__(1024)
 part_colscan_kernel(int T, int ctas, uint32_t* __restrict__ table, uint32_t* __restrict__ tile_total,
                     uint32_t* __restrict__ tile_start, uint2* __restrict__ ranges,
                     uint32_t* __restrict__ num_rendered, long long capacity) {
+  pdl_grid_sync();
   // CTA = 8 tiles x 128 row groups (a warp reads 4 row groups x 32 bytes: whole sectors); T/8 CTAs fill the GPU
   __shared__ uint32_t s_sum[128][9];
   __shared__ uint32_t s_last;
@@ -295,6 +297,7 @@ part_scatter_kernel(int P, int T, const uint32_t* __restrict__ num_rendered,
                     const float4* __restrict__ rec, int gx, int gy, const uint32_t* __restrict__ table,
                     const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ point_list,
                     uint64_t* __restrict__ keys, long long capacity) {
+  pdl_grid_sync();
   extern __shared__ uint32_t pt_smem[];
   const int words = (T + 1) / 2;
   uint32_t* blockbase = pt_smem + PT_WARPS * words;
@@ -398,13 +401,11 @@ cudaError_t launch_partition(int P, int gx, int gy, const uint32_t* order, const
   const size_t sa = pt_smem_bytes(T, false), sb = pt_smem_bytes(T, true);
   if (cudaError_t e = optin_a.ensure(part_count_kernel, sa)) return e;
   if (cudaError_t e = optin_b.ensure(part_scatter_kernel, sb)) return e;
-  part_count_kernel<<<ctas, PT_THREADS, sa, st>>>(P, T, num_rendered, depth_hist, order, offsets, radii, rec, gx, gy, table);
+  launch_pdl(part_count_kernel, dim3(ctas), dim3(PT_THREADS), sa, st, P, T, num_rendered, depth_hist, order, offsets, radii, rec, gx, gy, table);
   count_launch();
-  part_colscan_kernel<<<cdiv(T, 8), 1024, 0, st>>>(T, ctas, table, tile_total, tile_start, ranges, num_rendered,
-                                                    capacity);
+  launch_pdl(part_colscan_kernel, dim3(cdiv(T, 8)), dim3(1024), 0, st, T, ctas, table, tile_total, tile_start, ranges, num_rendered, capacity);
   count_launch();
-  part_scatter_kernel<<<ctas, PT_THREADS, sb, st>>>(P, T, num_rendered, depth_hist, order, offsets, radii, rec, gx, gy, table,
-                                                    tile_start, point_list, keys, capacity);
+  launch_pdl(part_scatter_kernel, dim3(ctas), dim3(PT_THREADS), sb, st, P, T, num_rendered, depth_hist, order, offsets, radii, rec, gx, gy, table, tile_start, point_list, keys, capacity);
   count_launch();
   return cudaGetLastError();
 }

@@ -8,6 +8,7 @@
 #pragma once
 #include <atomic>
 #include <cstdint>
+#include <cstdlib>
 #include <mutex>
 #include <cuda_runtime.h>
 #include "../../include/fdls_abi.h"
@@ -220,6 +221,45 @@ struct SmemOptIn {
     return e;
   }
 };
+
+// ---- Programmatic dependent launch (sm_90+, PTX griddepcontrol) -------------------------------------------------------
+// A frame is a chain of 11 short dependent kernels (preprocess -> 4 sort passes -> 2 scans -> 3 partition kernels ->
+// compositor), several of them latency-bound; between two plain launches the GPU drains the first grid completely
+// before it even starts setting up the second one (~2-3 us per boundary).  Every kernel of the chain is launched with
+// programmaticStreamSerializationAllowed and begins with pdl_grid_sync() = griddepcontrol.wait: the launch of kernel
+// k+1 is processed while kernel k still runs, and its CTAs start the moment k has completed and flushed.
+// Transitivity holds because every kernel waits before it does anything else (a kernel that skipped the wait could
+// finish, and release its successor, before an older grid is done).  Launched without the attribute it is a no-op.
+// Measured on cfg2 (scripts/ab_pdl.sh, profiles/r02_ab_pdl.txt): one-stream sweep 3287 -> 3601 frames/s, cfg3
+// training step 369 -> 385 iters/s.  Also issuing griddepcontrol.launch_dependents at the top of every kernel
+// (FDLS_PDL_EARLY=1: successor CTAs become resident and wait on the SM while the predecessor drains) LOST:
+// 2882 frames/s -- the resident waiters of up to four younger kernels take slots and shared memory from the one
+// that is running.
+#ifndef FDLS_PDL_EARLY
+#define FDLS_PDL_EARLY 0
+#endif
+__device__ __forceinline__ void pdl_grid_sync() {
+#if FDLS_PDL_EARLY
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+template <class... KArgs, class... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                     Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  static const int pdl = [] { const char* e = getenv("FDLS_PDL"); return e ? atoi(e) : 1; }();  // A/B switch
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 static inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }

@@ -55,6 +55,7 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
                       const float* __restrict__ scales, const float* __restrict__ rotations,
                       const float* __restrict__ cov3D_precomp, ViewParams vp, const float4* __restrict__ grad_rec,
                       BwdOut o) {
+  pdl_grid_sync();
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   if (threadIdx.x < 16) s_view[threadIdx.x] = vp.view[threadIdx.x];
   else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = vp.proj[threadIdx.x - 16];
@@ -357,9 +358,9 @@ cudaError_t launch_preprocess_bwd(const FdlsBwdArgs* a, const ViewParams& vp, co
               a->dL_dscales, a->dL_drotations, a->dL_dcov3D, a->dL_dconic, a->dL_ddepths};
   const int grid = cdiv(a->P, 256);
   count_launch();
-#define PB_LAUNCH(VEC, ACCUM)                                                                                        \
-  preprocess_bwd_kernel<VEC, ACCUM><<<grid, 256, 0, st>>>(a->P, a->D, a->M, a->F, a->means3D, a->radii, a->shs, clamped, \
-                                                          a->scales, a->rotations, a->cov3D_precomp, vp, grad_rec, o)
+#define PB_LAUNCH(VEC, ACCUM)                                                                                      \
+  launch_pdl(preprocess_bwd_kernel<VEC, ACCUM>, dim3(grid), dim3(256), 0, st, a->P, a->D, a->M, a->F, a->means3D, \
+             a->radii, a->shs, clamped, a->scales, a->rotations, a->cov3D_precomp, vp, grad_rec, o)
   if (a->M == 16) {
     if (a->accumulate) PB_LAUNCH(true, true); else PB_LAUNCH(true, false);
   } else {

@@ -92,6 +92,7 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
                       uint8_t* __restrict__ clamped, uint64_t* __restrict__ depth_keys,
                       uint32_t* __restrict__ depth_vals, int prefiltered, uint32_t sh_magic,
                       uint32_t* __restrict__ depth_hist, uint32_t* __restrict__ tickets) {
+  pdl_grid_sync();
   extern __shared__ float s_sh[];
   // num_rendered[2..3]: "last block done" tickets of the scan / partition kernels that follow on this stream
   if (tickets != nullptr && blockIdx.x == 0 && threadIdx.x < 2) tickets[threadIdx.x] = 0;  // [256][3M+1] when SH are staged (sh_magic != 0), else empty
@@ -263,10 +264,7 @@ cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, fl
   const uint32_t magic = stage ? (uint32_t)(0xffffffffu / (uint32_t)(3 * a->M) + 1u) : 0u;
   static SmemOptIn optin;  // per device (common.cuh)
   if (cudaError_t e = optin.ensure(preprocess_fwd_kernel, smem)) return e;
-  preprocess_fwd_kernel<<<cdiv(a->P, 256), 256, smem, st>>>(
-      a->P, a->D, a->M, a->F, a->means3D, a->scales, a->rotations, a->opacities, a->shs, a->cov3D_precomp,
-      a->colors_precomp, a->language_feature, vp, a->radii, rec, tiles_touched, clamped, depth_keys, depth_vals,
-      a->prefiltered, magic, depth_hist, tickets); count_launch();
+  launch_pdl(preprocess_fwd_kernel, dim3(cdiv(a->P, 256)), dim3(256), smem, st, a->P, a->D, a->M, a->F, a->means3D, a->scales, a->rotations, a->opacities, a->shs, a->cov3D_precomp, a->colors_precomp, a->language_feature, vp, a->radii, rec, tiles_touched, clamped, depth_keys, depth_vals, a->prefiltered, magic, depth_hist, tickets); count_launch();
   return cudaGetLastError();
 }
 

@@ -94,6 +94,7 @@ __device__ __forceinline__ uint32_t rs_block_excl(uint32_t v, uint32_t* s_warp) 
 __global__ void __launch_bounds__(RS_THREADS)
 rs_histogram_kernel(const uint64_t* __restrict__ keys, long long n_max, const uint32_t* __restrict__ n_dev, int passes,
                     int begin_bit, int end_bit, uint32_t* __restrict__ global_hist) {
+  pdl_grid_sync();
   constexpr int HT = RS_THREADS * 8;
   __shared__ uint32_t s_hist[RS_MAX_PASSES][RS_BINS];
   const long long n = n_dev ? min((long long)n_dev[0], n_max) : n_max;
@@ -130,6 +131,7 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ 
                    const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out, long long n_max,
                    const uint32_t* __restrict__ n_dev, int shift, int bits, const uint32_t* __restrict__ global_hist,
                    uint32_t* __restrict__ tile_state, uint32_t* __restrict__ ticket, uint32_t* __restrict__ error_flag) {
+  pdl_grid_sync();
   constexpr int TILE_KEYS = RS_THREADS * IPT;
   extern __shared__ __align__(16) unsigned char rs_smem_raw[];
   RsSmem<IPT>& s = *reinterpret_cast<RsSmem<IPT>*>(rs_smem_raw);
@@ -327,9 +329,7 @@ static int rs_launch_passes(uint64_t* kin, uint64_t* kout, uint32_t* vin, uint32
   for (int p = 0; p < passes; ++p) {
     const int shift = begin_bit + p * 8;
     const int bits = end_bit - shift < 8 ? end_bit - shift : 8;
-    rs_onesweep_kernel<IPT><<<tiles, RS_THREADS, sizeof(RsSmem<IPT>), st>>>(
-        kin, kout, vin, vout, n_max, n_dev, shift, bits, sc.global_hist + p * RS_BINS,
-        sc.tile_state + (size_t)p * tiles * RS_BINS, sc.tickets + p, sc.error_flag);
+    launch_pdl(rs_onesweep_kernel<IPT>, dim3(tiles), dim3(RS_THREADS), sizeof(RsSmem<IPT>), st, kin, kout, vin, vout, n_max, n_dev, shift, bits, sc.global_hist + p * RS_BINS, sc.tile_state + (size_t)p * tiles * RS_BINS, sc.tickets + p, sc.error_flag);
     count_launch();
     uint64_t* tk = kin; kin = kout; kout = tk;
     uint32_t* tv = vin; vin = vout; vout = tv;
@@ -348,8 +348,7 @@ int sort_run(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* val
   RsScratch sc = rs_carve(scratch, n_max, passes);
   if (scratch_bytes < sc.total_bytes) return FDLS_EWORKSPACE;
   if (!have_hist) {
-    rs_histogram_kernel<<<cdiv(n_max, RS_THREADS * 8), RS_THREADS, 0, st>>>(keys_a, n_max, n_dev, passes, begin_bit,
-                                                                           end_bit, sc.global_hist);
+    launch_pdl(rs_histogram_kernel, dim3(cdiv(n_max, RS_THREADS * 8)), dim3(RS_THREADS), 0, st, keys_a, n_max, n_dev, passes, begin_bit, end_bit, sc.global_hist);
     count_launch();
   }
   int rc = rs_ipt(n_max) == 4

@@ -110,6 +110,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const uint32_t* __restrict__ tile_max_contrib, const float* __restrict__ dL_dpixels,
                   const float* __restrict__ dL_dpixels_F, const float* __restrict__ dL_dpixel_depths,
                   float* __restrict__ grad_rec) {
+  pdl_grid_sync();
   constexpr bool TWO_BLOCKS = F > 4;  // language channels 4, 5 need a second 8-column block
   constexpr int NCH = TWO_BLOCKS ? 10 : 8;
   constexpr int N_CH = F > 0 ? 4 + (F < 4 ? F : 4) : (DEPTH_GRAD ? 4 : 3);  // used columns of the first block
@@ -441,13 +442,11 @@ static cudaError_t launch_rb(bool depth_grad, const uint2* ranges, const uint32_
   if (depth_grad) {
     cudaError_t e = opt_d.ensure(render_bwd_kernel<F, true>, smem);
     if (e != cudaSuccess) return e;
-    render_bwd_kernel<F, true><<<gx * gy, RB_THREADS, smem, st>>>(ranges, point_list, rec, W, H, gx, bg, final_T,
-                                                                  n_contrib, tile_max, dpix, dpix_F, dpix_D, grad_rec);
+    launch_pdl(render_bwd_kernel<F, true>, dim3(gx * gy), dim3(RB_THREADS), smem, st, ranges, point_list, rec, W, H, gx, bg, final_T, n_contrib, tile_max, dpix, dpix_F, dpix_D, grad_rec);
   } else {
     cudaError_t e = opt_n.ensure(render_bwd_kernel<F, false>, smem);
     if (e != cudaSuccess) return e;
-    render_bwd_kernel<F, false><<<gx * gy, RB_THREADS, smem, st>>>(ranges, point_list, rec, W, H, gx, bg, final_T,
-                                                                   n_contrib, tile_max, dpix, dpix_F, dpix_D, grad_rec);
+    launch_pdl(render_bwd_kernel<F, false>, dim3(gx * gy), dim3(RB_THREADS), smem, st, ranges, point_list, rec, W, H, gx, bg, final_T, n_contrib, tile_max, dpix, dpix_F, dpix_D, grad_rec);
   }
   return cudaGetLastError();
 }

@@ -82,6 +82,7 @@ render_bwd_shfl_kernel(const uint2* __restrict__ ranges, const uint32_t* __restr
                   const uint32_t* __restrict__ tile_max_contrib, const float* __restrict__ dL_dpixels,
                   const float* __restrict__ dL_dpixels_F, const float* __restrict__ dL_dpixel_depths,
                   float* __restrict__ grad_rec) {
+  pdl_grid_sync();
   __shared__ float4 s_rec[2][4][RB_THREADS];
   __shared__ uint32_t s_id[2][RB_THREADS];
   __shared__ uint32_t s_strips[2][RB_THREADS];  // strip_summary().y of each staged Gaussian
@@ -259,11 +260,9 @@ static cudaError_t launch_rb_shfl(bool depth_grad, const uint2* ranges, const ui
                              float* grad_rec, cudaStream_t st) {
   count_launch();
   if (depth_grad)
-    render_bwd_shfl_kernel<F, true><<<gx * gy, RB_THREADS, 0, st>>>(ranges, point_list, rec, W, H, gx, bg, final_T,
-                                                               n_contrib, tile_max, dpix, dpix_F, dpix_D, grad_rec);
+    launch_pdl(render_bwd_shfl_kernel<F, true>, dim3(gx * gy), dim3(RB_THREADS), 0, st, ranges, point_list, rec, W, H, gx, bg, final_T, n_contrib, tile_max, dpix, dpix_F, dpix_D, grad_rec);
   else
-    render_bwd_shfl_kernel<F, false><<<gx * gy, RB_THREADS, 0, st>>>(ranges, point_list, rec, W, H, gx, bg, final_T,
-                                                                n_contrib, tile_max, dpix, dpix_F, dpix_D, grad_rec);
+    launch_pdl(render_bwd_shfl_kernel<F, false>, dim3(gx * gy), dim3(RB_THREADS), 0, st, ranges, point_list, rec, W, H, gx, bg, final_T, n_contrib, tile_max, dpix, dpix_F, dpix_D, grad_rec);
   return cudaGetLastError();
 }
 

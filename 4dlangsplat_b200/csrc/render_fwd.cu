@@ -39,6 +39,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float4* __restrict__ rec, int W, int H, int gx, const float* __restrict__ bg_color,
                   float* __restrict__ final_T, uint32_t* __restrict__ n_contrib, uint32_t* __restrict__ tile_max_contrib,
                   float* __restrict__ out_color, float* __restrict__ out_lang, float* __restrict__ out_depth) {
+  pdl_grid_sync();
   // [buf][slot 0..3][thread]: conflict-free cp.async writes, broadcast reads
   __shared__ float4 s_rec[2][4][RF_THREADS];
   __shared__ float2 s_aux[2][RF_THREADS];  // {alpha-threshold in the log domain, block_summary()} of each staged Gaussian
@@ -174,8 +175,7 @@ template <int F>
 static cudaError_t launch_rf(const uint2* ranges, const uint32_t* point_list, const float4* rec, int W, int H, int gx,
                              int gy, const float* bg, float* final_T, uint32_t* n_contrib, uint32_t* tile_max,
                              float* out_color, float* out_lang, float* out_depth, cudaStream_t st) {
-  render_fwd_kernel<F><<<gx * gy, RF_THREADS, 0, st>>>(ranges, point_list, rec, W, H, gx, bg, final_T, n_contrib,
-                                                       tile_max, out_color, out_lang, out_depth); count_launch();
+  launch_pdl(render_fwd_kernel<F>, dim3(gx * gy), dim3(RF_THREADS), 0, st, ranges, point_list, rec, W, H, gx, bg, final_T, n_contrib, tile_max, out_color, out_lang, out_depth); count_launch();
   return cudaGetLastError();
 }
 
