@@ -225,13 +225,15 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, language_fe
                                  scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
                                  dL_dout_color, dL_dout_language_feature, dL_dout_depth, sh, degree, campos, geomBuffer,
                                  R, binningBuffer, imageBuffer, debug, include_feature, want=None, out=None,
-                                 accumulate=False):
+                                 accumulate=False, sh_rgb_out=None):
     """RasterizeGaussiansBackwardCUDA (rasterize_points.cu:131-235).  Returns (dL_dmeans2D, dL_dcolors,
     dL_dlanguage_feature, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations).
     `want` (an addition; None = all, like the reference): 9 booleans in that order -- gradients not wanted are neither
     allocated nor written (the C ABI takes a null pointer for them) and come back as None.
     `out` (an addition): 9 optional tensors in that order to write into instead of allocating; with `accumulate` the
-    kernels add to every output (caller-provided ones must hold the running sum, fresh ones are zero-filled here)."""
+    kernels add to every output (caller-provided ones must hold the running sum, fresh ones are zero-filled here).
+    `sh_rgb_out`: optional (P,3) tensor that receives the masked colour gradient (FdlsBwdArgs.dL_dsh_rgb), the
+    view-dependent factor of the rank-1 SH gradient; see sh_grad_expand."""
     lib = _lib.load()
     means3D = _prep(means3D, "means3D")
     dev = means3D.device
@@ -289,12 +291,25 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, language_fe
     a.dL_dconic, a.dL_ddepths = None, None
     a.bwd_algo = 1 if os.environ.get("FDLS_RENDER_BWD", "mma") == "shfl" else 0
     a.accumulate = int(bool(accumulate))
+    a.dL_dsh_rgb = dp(sh_rgb_out)
     if profile["bwd"] is not None:
         a.stage_events = profile["bwd"]
     _lib.check(lib.fdls_backward(C.byref(a), _stream(dev)), "fdls_backward")
     if debug:
         torch.cuda.current_stream(dev).synchronize()
     return g_means2D, g_colors, g_lang, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rot
+
+
+def sh_grad_expand(means3D, slots, degree, out, accumulate=False):
+    """out (P,M,3) (+)= sum over the view slots of basis(view direction) (x) dL_dRGB (fdls_sh_grad_expand).
+    slots: (B, 4 + 3P) float32: camera position, valid flag, the (P,3) array written through sh_rgb_out."""
+    lib = _lib.load()
+    P, M = out.size(0), out.size(1)
+    assert slots.is_contiguous() and out.is_contiguous() and slots.size(1) >= 4 + 3 * P
+    _lib.check(lib.fdls_sh_grad_expand(P, int(degree), M, slots.size(0), _prep(means3D, "means3D").data_ptr(),
+                                       slots.data_ptr(), slots.size(1), out.data_ptr(), int(bool(accumulate)),
+                                       _stream(out.device)), "fdls_sh_grad_expand")
+    return out
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):

@@ -68,6 +68,7 @@ class FdlsBwdArgs(C.Structure):
         ("stage_events", C.POINTER(C.c_void_p)),
         ("bwd_algo", C.c_int32),
         ("accumulate", C.c_int32),
+        ("dL_dsh_rgb", _f32p),
     ]
 
 
@@ -100,6 +101,8 @@ SYMBOLS = {
     "fdls_bin_and_render": (C.c_int, [C.POINTER(FdlsFwdArgs), C.c_void_p]),
     "fdls_forward": (C.c_int, [C.POINTER(FdlsFwdArgs), C.c_void_p]),
     "fdls_backward": (C.c_int, [C.POINTER(FdlsBwdArgs), C.c_void_p]),
+    "fdls_sh_grad_expand": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t,
+                                      C.c_void_p, C.c_int32, C.c_void_p]),
     "fdls_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fdls_knn_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "fdls_knn_dist2": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),

@@ -57,6 +57,8 @@ cudaError_t launch_render_bwd_shfl(int F, const uint2* ranges, const uint32_t* p
                                    const float* dpix_F, const float* dpix_D, float* grad_rec, cudaStream_t st);
 cudaError_t launch_preprocess_bwd(const FdlsBwdArgs* a, const ViewParams& vp, const uint8_t* clamped,
                                   const float4* grad_rec, cudaStream_t st);
+cudaError_t launch_sh_grad_expand(int P, int D, int M, int B, const float* means3D, const float* slots, size_t stride,
+                                  float* dL_dsh, int accumulate, cudaStream_t st);
 // knn.cu
 size_t knn_workspace_bytes(int N);
 int knn_dist2(int N, const float* xyz, float* out, void* ws, size_t ws_bytes, cudaStream_t st);
@@ -338,6 +340,14 @@ FDLS_API int fdls_backward(const FdlsBwdArgs* a, void* stream) {
     return FDLS_ECUDA;
   rec(a->stage_events, 3, st);
   return FDLS_OK;
+}
+
+FDLS_API int fdls_sh_grad_expand(int32_t P, int32_t D, int32_t M, int32_t B, const float* means3D, const float* slots,
+                                 size_t stride, float* dL_dsh, int32_t accumulate, void* stream) {
+  if (P < 0 || B < 0 || D < 0 || D > 3 || M < (D + 1) * (D + 1)) return FDLS_EINVAL;
+  if (P > 0 && B > 0 && (!means3D || !slots || !dL_dsh || stride < (size_t)4 + 3 * (size_t)P)) return FDLS_EINVAL;
+  return launch_sh_grad_expand(P, D, M, B, means3D, slots, stride, dL_dsh, accumulate, (cudaStream_t)stream) ==
+                 cudaSuccess ? FDLS_OK : FDLS_ECUDA;
 }
 
 FDLS_API int fdls_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,

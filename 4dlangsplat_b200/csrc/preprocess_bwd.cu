@@ -10,6 +10,7 @@ namespace fdls {
 struct BwdOut {
   float* means3D; float* means2D; float* sh; float* colors; float* lang; float* opacity; float* scales; float* rots;
   float* cov3D; float* conic; float* depths;
+  float* sh_rgb;  // (P,3) dL_dRGB after the clamp mask: the view-dependent factor of the rank-1 SH gradient (never ACC)
 };
 
 // forward.cu:118-152 recomputed (the forward does not keep cov3D; it is 30 flops)
@@ -64,7 +65,6 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P) return;
   const bool vis = radii[idx] > 0;
-  if (ACC && !vis) return;  // adds nothing
 
   float g[16];
   if (vis) {
@@ -76,6 +76,13 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
 #pragma unroll
     for (int k = 0; k < 16; ++k) g[k] = 0.f;
   }
+  if (o.sh_rgb) {  // backward.cu:53-56: clamped channels pass no gradient to the SH coefficients
+    const uint8_t cl = vis ? clamped[idx] : (uint8_t)0;
+    o.sh_rgb[3 * idx] = (cl & 1) ? 0.f : g[G_RGB];
+    o.sh_rgb[3 * idx + 1] = (cl & 2) ? 0.f : g[G_RGB + 1];
+    o.sh_rgb[3 * idx + 2] = (cl & 4) ? 0.f : g[G_RGB + 2];
+  }
+  if (ACC && !vis) return;  // adds nothing
   // pass-through gradients (zeros when culled)
   if (o.means2D) {
     put<ACC>(o.means2D + 3 * idx, g[G_MX]);
@@ -351,11 +358,95 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
   if (o.rots) put4<ACC>(reinterpret_cast<float4*>(o.rots) + idx, drot);
 }
 
+// dL_dsh = sum over views of basis(dir_v) (x) dL_dRGB_v: the SH gradient of one view is an outer product of the 16
+// view-dependent basis values (backward.cu:41-126) and the masked colour gradient, so a batch of B views needs
+// 3 floats per view and Gaussian, not 48 per Gaussian and rank, to cross the interconnect (dist.GradBucket lowrank_sh).
+// slots: B records of `stride` floats: [0..2] camera position, [3] 1.0 if the slot holds a view, [4..] (P,3) dL_dRGB.
+__global__ void __launch_bounds__(256)
+sh_grad_expand_kernel(int P, int D, int M, int B, const float* __restrict__ means3D, const float* __restrict__ slots,
+                      size_t stride, float* __restrict__ dL_dsh, int accumulate) {
+  pdl_grid_sync();
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P) return;
+  const V3 pos = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+  V3 dsh[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) dsh[k] = {0, 0, 0};
+  for (int v = 0; v < B; ++v) {
+    const float* sl = slots + (size_t)v * stride;
+    if (sl[3] == 0.f) continue;
+    const V3 g = {sl[4 + 3 * idx], sl[4 + 3 * idx + 1], sl[4 + 3 * idx + 2]};
+    if (g.x == 0.f && g.y == 0.f && g.z == 0.f) continue;  // culled in this view (its direction may be degenerate)
+    const V3 cam = {sl[0], sl[1], sl[2]};
+    const V3 dir_orig = pos - cam;
+    const V3 dir = dir_orig / sqrt(dot3(dir_orig, dir_orig));
+    const float x = dir.x, y = dir.y, z = dir.z;
+    dsh[0] += SH_C0 * g;
+    if (D > 0) {
+      dsh[1] += (-SH_C1 * y) * g;
+      dsh[2] += (SH_C1 * z) * g;
+      dsh[3] += (-SH_C1 * x) * g;
+      if (D > 1) {
+        const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+        dsh[4] += (SH_C2[0] * xy) * g;
+        dsh[5] += (SH_C2[1] * yz) * g;
+        dsh[6] += (SH_C2[2] * (2.f * zz - xx - yy)) * g;
+        dsh[7] += (SH_C2[3] * xz) * g;
+        dsh[8] += (SH_C2[4] * (xx - yy)) * g;
+        if (D > 2) {
+          dsh[9] += (SH_C3[0] * y * (3.f * xx - yy)) * g;
+          dsh[10] += (SH_C3[1] * xy * z) * g;
+          dsh[11] += (SH_C3[2] * y * (4.f * zz - xx - yy)) * g;
+          dsh[12] += (SH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy)) * g;
+          dsh[13] += (SH_C3[4] * x * (4.f * zz - xx - yy)) * g;
+          dsh[14] += (SH_C3[5] * z * (xx - yy)) * g;
+          dsh[15] += (SH_C3[6] * x * (xx - 3.f * yy)) * g;
+        }
+      }
+    }
+  }
+  float* out = dL_dsh + (size_t)idx * M * 3;
+  if (M == 16) {  // 12 x 16-byte accesses per Gaussian, like preprocess_bwd's own SH stores
+    float4* o4 = reinterpret_cast<float4*>(out);
+    const float* f = reinterpret_cast<const float*>(dsh);
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+      float4 v = make_float4(f[4 * k], f[4 * k + 1], f[4 * k + 2], f[4 * k + 3]);
+      if (accumulate) {
+        const float4 c = o4[k];
+        v = make_float4(c.x + v.x, c.y + v.y, c.z + v.z, c.w + v.w);
+      }
+      o4[k] = v;
+    }
+    return;
+  }
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    if (k >= M) break;
+    if (accumulate) {
+      out[3 * k] += dsh[k].x; out[3 * k + 1] += dsh[k].y; out[3 * k + 2] += dsh[k].z;
+    } else {
+      out[3 * k] = dsh[k].x; out[3 * k + 1] = dsh[k].y; out[3 * k + 2] = dsh[k].z;
+    }
+  }
+  for (int k = 16; k < M; ++k)
+    if (!accumulate) out[3 * k] = out[3 * k + 1] = out[3 * k + 2] = 0.f;
+}
+
+cudaError_t launch_sh_grad_expand(int P, int D, int M, int B, const float* means3D, const float* slots, size_t stride,
+                                  float* dL_dsh, int accumulate, cudaStream_t st) {
+  if (P == 0 || B == 0) return cudaSuccess;
+  count_launch();
+  launch_pdl(sh_grad_expand_kernel, dim3(cdiv(P, 256)), dim3(256), 0, st, P, D, M, B, means3D, slots, stride, dL_dsh,
+             accumulate);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_preprocess_bwd(const FdlsBwdArgs* a, const ViewParams& vp, const uint8_t* clamped,
                                   const float4* grad_rec, cudaStream_t st) {
   if (a->P == 0) return cudaSuccess;
   BwdOut o = {a->dL_dmeans3D, a->dL_dmeans2D, a->dL_dsh, a->dL_dcolors, a->dL_dlanguage, a->dL_dopacity,
-              a->dL_dscales, a->dL_drotations, a->dL_dcov3D, a->dL_dconic, a->dL_ddepths};
+              a->dL_dscales, a->dL_drotations, a->dL_dcov3D, a->dL_dconic, a->dL_ddepths, a->dL_dsh_rgb};
   const int grid = cdiv(a->P, 256);
   count_launch();
 #define PB_LAUNCH(VEC, ACCUM)                                                                                      \

@@ -103,17 +103,26 @@ class _RasterizeGaussians(torch.autograd.Function):
         # (means3D, means2D, sh, colors, lang, opacities, scales, rotations, cov3D, settings)
         n = ctx.needs_input_grad
         want = (n[1], n[3], n[4], n[5], n[0], n[8], n[2], n[6], n[7])
-        out, acc, owners = None, False, ()
+        out, acc, owners, sh_rgb = None, False, (), None
         if ctx.sinks is not None:
+            sk_sh = ctx.sinks[6]
+            if sk_sh is not None and sk_sh.view is None:
+                # low-rank SH sink (dist.GradBucket(lowrank_sh=...)): this view leaves its masked colour gradient and
+                # camera position in a slot; the bucket expands all views' slots into dL_dsh once per iteration
+                if want[6]:
+                    sh_rgb = sk_sh.owner.take_sh_slot(rs.campos, means3D, rs.sh_degree)
+                want = want[:6] + (False,) + want[7:]
             # (means2D, colors, lang, opacities, means3D, cov3D, sh, scales, rotations): the native return order
-            out = tuple(k.view if (k is not None and wnt) else None for k, wnt in zip(ctx.sinks, want))
+            out = tuple(k.view if (k is not None and wnt and k.view is not None) else None
+                        for k, wnt in zip(ctx.sinks, want))
             owners = {id(k.owner): k.owner for k in ctx.sinks if k is not None}.values()
             acc = not all(b.fresh for b in owners)  # the iteration's first view overwrites, later ones add
             if acc:
                 for b in owners:
                     b.zero_if_fresh()
         grads = _guarded(
-            lambda *args: _C.rasterize_gaussians_backward(*args, want=want, out=out, accumulate=acc), native_args,
+            lambda *args: _C.rasterize_gaussians_backward(*args, want=want, out=out, accumulate=acc,
+                                                          sh_rgb_out=sh_rgb), native_args,
             rs.debug, "snapshot_bw.dump", "\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
         for b in owners:
             b.fresh = False

@@ -42,17 +42,40 @@ class GradBucket:
     copy before the collective -- the kernel's output buffer IS the collective's buffer.  Without register() (gloo
     tests on CPU tensors, or leaves that reach the rasterizer through other autograd nodes) pack() copies .grad in."""
 
-    def __init__(self, params):
+    def __init__(self, params, lowrank_sh=None, n_views=0):
+        """lowrank_sh: the SH-coefficient leaf (P,M,3), NOT listed in `params`.  Its gradient is 3*M of the ~(17+3*M)
+        floats a Gaussian contributes to the all-reduce, yet per view it is only an outer product: 16 basis values
+        of the view direction times the masked colour gradient (3 floats).  With lowrank_sh the backward of each view
+        leaves those 3 floats + the camera position in a slot, the slots of all `n_views` views are ALL-GATHERED
+        (3*B floats per Gaussian instead of 3*M per rank: 4x fewer bytes at B = 4, M = 16) and every rank expands
+        them into dL_dsh itself (fdls_sh_grad_expand).  It also removes the per-view 192-byte/Gaussian gradient
+        read-modify-write from preprocess_bwd.  Needs register()."""
         self.params = [p for p in params if p is not None]
         self.numel = sum(p.numel() for p in self.params)
         dev = self.params[0].device if self.params else torch.device("cpu")
-        self.flat = torch.zeros(self.numel, dtype=torch.float32, device=dev)
+        n_slots = 0
+        if lowrank_sh is not None:
+            rank, ws = world()
+            self.sh_local_n = max(1, (int(n_views) + ws - 1) // ws)  # slots per rank (ragged shards are padded)
+            self.sh_stride = 4 + 3 * lowrank_sh.size(0)
+            n_slots = ws * self.sh_local_n
+        # the view slots live behind the parameters' gradients in the SAME flat buffer: every rank fills its own slots,
+        # the others stay zero, and the one all-reduce(sum) of the step doubles as the all-gather of the slots
+        # (a second collective costs more in launch latency than the extra bytes do in bandwidth)
+        self.flat = torch.zeros(self.numel + n_slots * (self.sh_stride if n_slots else 0), dtype=torch.float32, device=dev)
         self.views, o = [], 0
         for p in self.params:
             self.views.append(self.flat[o:o + p.numel()].view_as(p))
             o += p.numel()
         self.fresh = True       # nothing written this iteration (the first backward overwrites, later ones add)
         self.registered = False
+        self.sh = lowrank_sh
+        if lowrank_sh is not None:
+            self.sh_all = self.flat[self.numel:].view(n_slots, self.sh_stride)
+            self.sh_local = self.sh_all[rank * self.sh_local_n:(rank + 1) * self.sh_local_n]
+            self.sh_grad = torch.zeros_like(lowrank_sh)
+            self.sh_used, self.sh_means, self.sh_degree, self.sh_work = 0, None, 0, None
+            self._one = torch.ones(1, dtype=torch.float32, device=dev)
         self.work = None
         self.timing = None      # set to a list to collect (start, end) CUDA event pairs around the collective
 
@@ -61,12 +84,14 @@ class GradBucket:
         from . import _C
         for p, v in zip(self.params, self.views):
             _C.grad_sinks[p.data_ptr()] = _C._Sink(v, self)
+        if self.sh is not None:
+            _C.grad_sinks[self.sh.data_ptr()] = _C._Sink(None, self)  # view None = low-rank SH sink
         self.registered = True
         return self
 
     def unregister(self):
         from . import _C
-        for p in self.params:
+        for p in self.params + ([self.sh] if self.sh is not None else []):
             _C.grad_sinks.pop(p.data_ptr(), None)
         self.registered = False
 
@@ -76,10 +101,24 @@ class GradBucket:
         if self.registered:
             for p in self.params:
                 p.grad = None
+        if self.sh is not None:
+            self.sh.grad = None
+            self.sh_all.zero_()  # no slot holds a view yet; the other ranks' slots must be zero for the sum
+            self.sh_used = 0
+
+    def take_sh_slot(self, campos, means3D, degree):
+        """Called by the rasterizer's backward: the (P,3) array of this rank's next view slot; records the camera."""
+        if self.sh_used >= self.sh_local_n:
+            raise RuntimeError("GradBucket(lowrank_sh): more views on this rank than n_views / world_size allows")
+        slot = self.sh_local[self.sh_used]
+        slot[:4].copy_(torch.cat([campos.reshape(3), self._one]))  # header: camera position, valid flag
+        self.sh_used += 1
+        self.sh_means, self.sh_degree = means3D, int(degree)
+        return slot[4:].view(-1, 3)
 
     def zero_if_fresh(self):
         if self.fresh:
-            self.flat.zero_()
+            self.flat[:self.numel].zero_()
             self.fresh = False
 
     # ---- copy mode -----------------------------------------------------------------------------------------------
@@ -104,6 +143,7 @@ class GradBucket:
             self.zero_if_fresh()  # a rank without a view this iteration contributes zeros
         else:
             self.pack()
+        nbytes = self.flat.numel() * 4
         if world()[1] > 1:
             if self.timing is not None and self.flat.is_cuda:
                 e0 = torch.cuda.Event(enable_timing=True)
@@ -113,8 +153,23 @@ class GradBucket:
             if not async_op:
                 self.wait()
         else:
+            self._expand_sh()
             self.unpack()
-        return self.flat.numel() * 4
+        return nbytes
+
+    def _expand_sh(self):
+        if self.sh is None:
+            return
+        from . import _C
+        if self.sh_means is None:  # this rank never rendered: any leaf of the right shape serves as positions
+            raise RuntimeError("GradBucket(lowrank_sh): no view was rendered on this rank yet; call "
+                               "set_sh_geometry(means3D, degree) once")
+        _C.sh_grad_expand(self.sh_means, self.sh_all, self.sh_degree, self.sh_grad, accumulate=False)
+        self.sh.grad = self.sh_grad
+
+    def set_sh_geometry(self, means3D, degree):
+        """For a rank that may have no view in some iteration (more GPUs than views): positions + active SH degree."""
+        self.sh_means, self.sh_degree = means3D, int(degree)
 
     def wait(self):
         if self.work is not None:
@@ -124,6 +179,7 @@ class GradBucket:
                 e1 = torch.cuda.Event(enable_timing=True)
                 e1.record()
                 self.timing[-1][1] = e1
+            self._expand_sh()
         self.unpack()
 
     def allreduce_ms(self):

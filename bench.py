@@ -385,10 +385,23 @@ def run_ours(wl, steps, warmup, world):
         if not torch.equal(h, o.cpu()):
             raise SystemExit("end-to-end pipeline delivered images that differ from a direct render of the same frame")
     sys.stderr.write('e2e: host issue time %.1f us/frame of %.1f us/frame\n' % (1e6 * pipe.host_s / n_frames, 1e6 * e2e_s / n_frames))
+    # the PCIe ceiling of this arm: the same per-frame copies (3 images down, means + camera up) with no rendering
+    torch.cuda.synchronize()
+    tc0 = time.perf_counter()
+    for i in range(FRAMES_PER_STEP):
+        with torch.cuda.stream(pipe.up):
+            pipe.cam_block.to("cuda", non_blocking=True)
+            wl.means_host[i % N_TIMESTAMPS].to("cuda", non_blocking=True)
+        with torch.cuda.stream(pipe.down):
+            for h, o in zip(pipe.outs_host, chk):
+                h.copy_(o, non_blocking=True)
+    torch.cuda.synchronize()
+    copy_only_fps = FRAMES_PER_STEP / (time.perf_counter() - tc0)
     h2d, d2h = pipe.h2d, pipe.d2h  # per frame
     return dict(ms=ms, n_frames=n_frames, stage_ms=stage_ms, stage_iso=stage_iso, R=float(np.mean(Rs)), V=V,
                 launches=int(launches), e2e_s=e2e_s, h2d=h2d * FRAMES_PER_STEP, d2h=d2h * FRAMES_PER_STEP,
-                one_stream_fps=one_steps * FRAMES_PER_STEP / (one_ms * 1e-3), host_us=1e6 * pipe.host_s / n_frames)
+                one_stream_fps=one_steps * FRAMES_PER_STEP / (one_ms * 1e-3), host_us=1e6 * pipe.host_s / n_frames,
+                copy_only_fps=copy_only_fps)
 
 
 def run_reference(wl, steps, warmup, world):
@@ -478,7 +491,12 @@ def run_train_ours(wl, steps, warmup, world):
     means2D = torch.zeros_like(p["means3D"], requires_grad=True)
     leaves = list(p.values()) + [means2D]
     # the rasterizer's backward writes / adds straight into the all-reduce bucket (no autograd sums, no pack copy)
-    bucket = fdist.GradBucket(leaves)
+    lowrank = os.environ.get("FDLS_BENCH_SINK", "1") != "0" and os.environ.get("FDLS_BENCH_LOWRANK_SH", "1") != "0"
+    if lowrank:  # SH gradients travel as per-view colour gradients (3 floats) and are expanded locally (dist.py)
+        bucket = fdist.GradBucket([t for t in leaves if t is not p["shs"]], lowrank_sh=p["shs"], n_views=wl.n_views)
+        bucket.set_sh_geometry(p["means3D"], s.sh_degree)
+    else:
+        bucket = fdist.GradBucket(leaves)
     if os.environ.get("FDLS_BENCH_SINK", "1") != "0":
         bucket.register()
     bucket.timing = []
@@ -525,6 +543,7 @@ def run_train_ours(wl, steps, warmup, world):
     fd._C.profile["fwd"], fd._C.profile["bwd"] = fwd_ev.arrays[0], bwd_ev.arrays[0]
     for t in leaves:
         t.grad = None
+    bucket.begin()
     if wl.mine:
         v = wl.mine[0]
         loss_of(v, render(v)).backward()
@@ -545,26 +564,55 @@ def run_train_ours(wl, steps, warmup, world):
         L = fd._lib.workspace_layout(s.P, s.W, s.H, 0)
         tiles = ((s.W + 15) // 16) * ((s.H + 15) // 16)
         R_staged = int(o[7][L.tile_max_contrib:L.tile_max_contrib + 4 * tiles].view(torch.int32).sum())
-    # e2e: same step, camera + upstream image gradients arrive from pinned host memory, the loss is read back
+    # e2e: same step, camera + upstream image gradients (the ground-truth side of the loss) arrive from pinned host
+    # memory every step and the loss is read back.  Like a data loader that prefetches the next batch, step k+1's
+    # upload runs on a copy stream while step k computes (two device-side sets); every copy is inside the timed region.
     host = {v: {k: x.cpu().pin_memory() for k, x in c.items()} for v, c in wl.views.items()}
     h2d = sum(x.numel() * 4 for c in host.values() for x in c.values())
+    up = torch.cuda.Stream()
+    sets = [{v: {k: torch.empty_like(x) for k, x in c.items()} for v, c in wl.views.items()} for _ in range(2)]
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    freed = [torch.cuda.Event(), torch.cuda.Event()]
+    loss_host = torch.zeros(1).pin_memory()
+
+    def upload(k):
+        with torch.cuda.stream(up):
+            up.wait_event(freed[k % 2])  # the step that last used this set has finished
+            for v, c in host.items():
+                for kk, x in c.items():
+                    sets[k % 2][v][kk].copy_(x, non_blocking=True)
+            ready[k % 2].record(up)
+
+    for ev in freed:
+        ev.record()
+    state = {"k": 0}
+    upload(0)
 
     def e2e_step():
-        for v, c in host.items():
-            wl.views[v] = {k: x.to("cuda", non_blocking=True) for k, x in c.items()}
+        k = state["k"]
+        upload(k + 1)
+        torch.cuda.current_stream().wait_event(ready[k % 2])
+        for v in wl.views:
+            wl.views[v] = sets[k % 2][v]
         loss, _ = step()
-        return float(loss)  # D2H read of the loss
+        freed[k % 2].record()
+        loss_host.copy_(loss.reshape(1), non_blocking=True)  # D2H read of the loss
+        state["k"] = k + 1
 
     for _ in range(max(1, warmup)):
         e2e_step()
+    torch.cuda.synchronize()
     barrier(world)
     t0 = time.perf_counter()
     for _ in range(steps):
         e2e_step()
     torch.cuda.synchronize()
+    final_loss = float(loss_host[0])
     t1 = time.perf_counter()
     barrier(world)
     e2e_s = max_over_ranks(t1 - t0, world)
+    if not np.isfinite(final_loss):
+        raise SystemExit("end-to-end training step produced a non-finite loss")
     V = int((torch.as_tensor(0)).item())
     return dict(ms=ms, n_frames=steps, stage_ms=fwd_ev.stage_ms(1), bwd_stage_ms=bwd_ev.stage_ms(1), R=float(R), V=V,
                 launches=int(launches), e2e_s=e2e_s, h2d=h2d, d2h=4, allreduce_bytes=nbytes, allreduce_ms=allreduce_ms,
@@ -938,6 +986,8 @@ def main():
         # what render.py gets without the pipelined sweep: one frame at a time on the current stream
         line["value_one_stream"] = round(r["one_stream_fps"] * world, 2)
         line["e2e_host_issue_us_per_frame"] = round(r["host_us"], 1)
+        # frames/s of the e2e arm's host<->device copies alone (no rendering): the PCIe ceiling of `e2e` on this box
+        line["e2e"]["copies_only_frames_per_s"] = round(r["copy_only_fps"] * world, 1)
         if rank == 0 and world == 1 and not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl)
     else:

@@ -175,6 +175,11 @@ typedef struct FdlsBwdArgs {
    * before the first view).  Lets a rank sum the views of its shard directly inside its all-reduce bucket
    *  -- no autograd accumulation pass, no pack copy.  The reference always overwrites. */
   int32_t accumulate;
+  /* optional (P,3), always overwritten: dL_dRGB after the clamp mask (backward.cu:53-56).  With `shs` given, the SH
+   * gradient of ONE view is the outer product of the 16 basis values of the view direction and this vector, so a
+   * multi-view / multi-GPU step can keep 3 floats per view and Gaussian and expand them once with
+   * fdls_sh_grad_expand instead of writing, accumulating and all-reducing 3*M floats per Gaussian; pass dL_dsh = null. */
+  float* dL_dsh_rgb;
 } FdlsBwdArgs;
 #define FDLS_BWD_EVENTS 4
 
@@ -196,6 +201,13 @@ int fdls_bin_and_render(const FdlsFwdArgs* a, void* stream);
 int fdls_forward(const FdlsFwdArgs* a, void* stream);
 
 int fdls_backward(const FdlsBwdArgs* a, void* stream);
+
+/* dL_dsh (P,M,3) (+)= sum over B view slots of basis(normalize(means3D - campos_v)) (x) dL_dRGB_v (degree D).
+ * `slots`: B records of `stride` floats: [0..2] camera position of the view, [3] 1.0f if the slot holds a view (0 =
+ * skip), [4 .. 4+3P) the (P,3) array fdls_backward wrote through dL_dsh_rgb.  Replaces, for a batch, the per-view
+ * dL_dsh writes of computeColorFromSH backward (backward.cu:41-126); the slots are what crosses NVLink. */
+int fdls_sh_grad_expand(int32_t P, int32_t D, int32_t M, int32_t B, const float* means3D, const float* slots,
+                        size_t stride, float* dL_dsh, int32_t accumulate, void* stream);
 
 int fdls_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                       uint8_t* present, void* stream);

@@ -506,11 +506,13 @@ def test_autograd_function_matches_native_backward(synth, fdls):
     _assert_grad(lang2.grad, g2.lang, "frozen-inputs dL_dlang")
 
 
-def test_gradient_bucket_sink_equals_autograd_accumulation(synth, fdls):
+@pytest.mark.parametrize("lowrank", [False, True])
+def test_gradient_bucket_sink_equals_autograd_accumulation(synth, fdls, lowrank):
     """dist.GradBucket.register(): the backward kernels of a rank's views write / add straight into the all-reduce
     bucket (FdlsBwdArgs.accumulate) instead of autograd summing per-view gradient tensors.  Three views of one scene:
     the bucket must hold the sum autograd produces, .grad must alias the bucket, and a second iteration must not
-    see the first one's content."""
+    see the first one's content.  lowrank: the SH gradient is not accumulated at all -- each view leaves its masked colour
+    gradient (3 floats per Gaussian) in a slot and fdls_sh_grad_expand rebuilds dL_dsh from the slots and the cameras."""
     import importlib
     fdist = importlib.import_module("4dlangsplat_b200.dist")
     dgr = fdls.diff_gaussian_rasterization
@@ -541,14 +543,21 @@ def test_gradient_bucket_sink_equals_autograd_accumulation(synth, fdls):
     ref = leaves()
     loss(ref).backward()
     p = leaves()
-    bucket = fdist.GradBucket(list(p.values())).register()
+    if lowrank:
+        flat = [k for k in p if k != "shs"]
+        bucket = fdist.GradBucket([p[k] for k in flat], lowrank_sh=p["shs"], n_views=3).register()
+    else:
+        flat = list(p)
+        bucket = fdist.GradBucket([p[k] for k in flat]).register()
     try:
         for it in range(2):
             bucket.begin()
             loss(p).backward()
             bucket.all_reduce()
             for k in p:
-                assert p[k].grad is not None and p[k].grad.data_ptr() == bucket.views[list(p).index(k)].data_ptr()
+                assert p[k].grad is not None
+                if k in flat:
+                    assert p[k].grad.data_ptr() == bucket.views[flat.index(k)].data_ptr()
                 _assert_grad(p[k].grad, ref[k].grad, "sink dL_d%s (iteration %d)" % (k, it))
     finally:
         bucket.unregister()
