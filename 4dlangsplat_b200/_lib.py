@@ -103,6 +103,8 @@ SYMBOLS = {
     "fdls_backward": (C.c_int, [C.POINTER(FdlsBwdArgs), C.c_void_p]),
     "fdls_sh_grad_expand": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t,
                                       C.c_void_p, C.c_int32, C.c_void_p]),
+    "fdls_umma_linear": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_int32, C.c_void_p]),
     "fdls_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fdls_knn_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "fdls_knn_dist2": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),

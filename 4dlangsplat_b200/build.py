@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.environ.get("FDLS_LIB", os.path.join(HERE, "libfdls.so"))  # FDLS_LIB / FDLS_NVCC_EXTRA: A/B builds
 SOURCES = ["api.cu", "preprocess_fwd.cu", "binning.cu", "binning_partition.cu", "radix_sort.cu", "render_fwd.cu", "render_bwd.cu", "render_bwd_shfl.cu",
-           "preprocess_bwd.cu", "knn.cu", "hexplane.cu"]
+           "preprocess_bwd.cu", "knn.cu", "hexplane.cu", "deform_mlp.cu"]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler",
               "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr"]
 
@@ -25,7 +25,7 @@ def build(force=False, verbose=False):
     extra = os.environ.get("FDLS_NVCC_EXTRA", "").split()
     objdir = os.path.join(HERE, "build" + ("_" + "".join(c for c in "".join(extra) if c.isalnum()) if extra else ""))
     os.makedirs(objdir, exist_ok=True)
-    hdrs = [os.path.join(CSRC, "common.cuh"), os.path.join(HERE, "..", "include", "fdls_abi.h"), os.path.abspath(__file__)]
+    hdrs = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "umma.cuh"), os.path.join(HERE, "..", "include", "fdls_abi.h"), os.path.abspath(__file__)]
     procs, objs = [], []
     for s in SOURCES:
         src = os.path.join(CSRC, s)

@@ -59,6 +59,9 @@ cudaError_t launch_preprocess_bwd(const FdlsBwdArgs* a, const ViewParams& vp, co
                                   const float4* grad_rec, cudaStream_t st);
 cudaError_t launch_sh_grad_expand(int P, int D, int M, int B, const float* means3D, const float* slots, size_t stride,
                                   float* dL_dsh, int accumulate, cudaStream_t st);
+// deform_mlp.cu
+int umma_linear(int rows, int N, int K, const float* X, const float* W, const float* bias, float* Y, int relu,
+                cudaStream_t st);
 // knn.cu
 size_t knn_workspace_bytes(int N);
 int knn_dist2(int N, const float* xyz, float* out, void* ws, size_t ws_bytes, cudaStream_t st);
@@ -393,6 +396,12 @@ FDLS_API int fdls_hexplane_pack_batch(int32_t n, int32_t C, const int64_t* HW, c
 FDLS_API int fdls_hexplane_unpack_grad_batch(int32_t n, int32_t C, const int64_t* HW, const float* const* hwc,
                                              float* const* chw, void* stream) {
   return hexplane_transpose(false, n, C, HW, hwc, chw, (cudaStream_t)stream);
+}
+
+FDLS_API int fdls_umma_linear(int32_t rows, int32_t N, int32_t K, const float* X, const float* W, const float* bias,
+                              float* Y, int32_t relu, void* stream) {
+  if (rows > 0 && (!X || !W || !Y)) return FDLS_EINVAL;
+  return umma_linear(rows, N, K, X, W, bias, Y, relu, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -1,0 +1,137 @@
+// umma.cuh -- the few tcgen05 / TMEM / mbarrier PTX wrappers the deformation MLP needs (sm_100a), and the bf16x3
+// operand format that gives fp32-grade products on the 5th-generation tensor cores.
+//
+// Operand layout ("canonical K-major, no swizzle", the INTERLEAVE form of the UMMA shared-memory descriptor): a
+// matrix of R rows x K columns of 16-bit elements is stored as K/8 SLABS; a slab holds 8 consecutive k of every row,
+// row r at byte r*16 (16 bytes = 8 bf16), so a slab is R*16 bytes and consecutive 8-row groups ("core matrices",
+// 8 rows x 16 bytes = 128 bytes) follow each other at SBO = 128 bytes; the next slab (the next 8 k) starts LBO = R*16
+// bytes later.  One tcgen05.mma.kind::f16 consumes K = 16 = two slabs.
+//
+// fp32 from bf16: x = b1 + b2 + b3 with three bf16 (8 + 8 + 8 significant bits, each the round-to-nearest of what
+// is left), and a product a*b is taken as the six terms a1b1 + a1b2 + a2b1 + a2b2 + a1b3 + a3b1 accumulated in
+// fp32 inside the tensor core: everything dropped is below 2^-24 of |a||b|.
+#pragma once
+#include <cstdint>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+namespace fdls {
+namespace umma {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// ---- mbarrier ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t a = smem_u32(bar);
+  for (uint32_t spins = 0;; ++spins) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(done)
+        : "r"(a), "r"(parity)
+        : "memory");
+    if (done) return;
+    if (spins > (1u << 24)) __trap();  // an MMA that never completes must fail loudly, not hang the GPU
+  }
+}
+
+// ---- proxies and tcgen05 fences -------------------------------------------------------------------------------------
+// shared memory written with ordinary stores / cp.async must be fenced before the tensor core (async proxy) reads it
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// ---- TMEM -----------------------------------------------------------------------------------------------------------
+// one warp allocates `cols` (power of two >= 32) columns and writes the base address to *slot (shared memory)
+template <int COLS>
+__device__ __forceinline__ void tmem_alloc(uint32_t* slot) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "n"(COLS)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_dealloc(uint32_t base) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(base), "n"(COLS) : "memory");
+}
+// 32 lanes x 32 bit x 8 columns: thread i of warp w receives columns [c, c+8) of TMEM lane 32*(w%4)+i
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
+  uint32_t r[8];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// ---- descriptors ----------------------------------------------------------------------------------------------------
+// shared-memory matrix descriptor, K-major, no swizzle (cute/arch/mma_sm100_desc.hpp SmemDescriptor):
+//   [0,14) start address >> 4 | [16,30) leading byte offset >> 4 (between the two 8-k slabs of one MMA)
+//   | [32,46) stride byte offset >> 4 (between 8-row groups) | [46,48) version = 1 | [61,64) layout type = 0
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3fffu);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
+// instruction descriptor for kind::f16, bf16 x bf16 -> fp32, both operands K-major (InstrDescriptor, same header):
+//   [4,6) D format 1 = f32 | [7,10) A format 1 = bf16 | [10,13) B format 1 = bf16 | [17,23) N >> 3 | [24,29) M >> 4
+__host__ __device__ constexpr uint32_t instr_desc_bf16(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, issued by ONE thread
+__device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, bool accumulate) {
+  const uint32_t acc = accumulate ? 1u : 0u;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(acc)
+      : "memory");
+}
+// all MMAs issued so far by this thread arrive on the mbarrier when they have completed
+__device__ __forceinline__ void mma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+
+// ---- bf16 x 3 ---------------------------------------------------------------------------------------------------------
+struct Bf3 {
+  uint16_t a, b, c;
+};
+__device__ __forceinline__ Bf3 split_bf3(float x) {
+  const __nv_bfloat16 h1 = __float2bfloat16_rn(x);
+  const float r1 = x - __bfloat162float(h1);
+  const __nv_bfloat16 h2 = __float2bfloat16_rn(r1);
+  const float r2 = r1 - __bfloat162float(h2);
+  const __nv_bfloat16 h3 = __float2bfloat16_rn(r2);
+  return {__bfloat16_as_ushort(h1), __bfloat16_as_ushort(h2), __bfloat16_as_ushort(h3)};
+}
+// split 8 consecutive k of one row and store them as one 16-byte piece per part: part p at dst + p * part_bytes
+__device__ __forceinline__ void store_row8_bf3(char* dst, size_t part_bytes, const float (&v)[8]) {
+  uint32_t w[3][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const Bf3 lo = split_bf3(v[2 * i]), hi = split_bf3(v[2 * i + 1]);
+    w[0][i] = (uint32_t)lo.a | ((uint32_t)hi.a << 16);
+    w[1][i] = (uint32_t)lo.b | ((uint32_t)hi.b << 16);
+    w[2][i] = (uint32_t)lo.c | ((uint32_t)hi.c << 16);
+  }
+#pragma unroll
+  for (int p = 0; p < 3; ++p)
+    *reinterpret_cast<uint4*>(dst + p * part_bytes) = make_uint4(w[p][0], w[p][1], w[p][2], w[p][3]);
+}
+
+}  // namespace umma
+}  // namespace fdls

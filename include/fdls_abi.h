@@ -266,6 +266,14 @@ int fdls_hexplane_pack_batch(int32_t n, int32_t C, const int64_t* HW, const floa
 int fdls_hexplane_unpack_grad_batch(int32_t n, int32_t C, const int64_t* HW, const float* const* hwc,
                                     float* const* chw, void* stream);
 
+/* ---- SURVEY 8f N1, second step: the MLP half of the deformation network on the tcgen05 tensor cores -------------
+ * Y[rows x N] = act(X[rows x K] W[N x K]^T + bias), fp32 in and out, W in torch's nn.Linear layout (out, in).
+ * The product runs as bf16 x 3 operand splits (six tcgen05.mma.kind::f16 terms, fp32 accumulation in TMEM), which
+ * reproduces the fp32 result to ~1e-7 relative.  K % 16 == 0, N % 8 == 0, both <= 128.  The building block of
+ * fdls_deform_forward; exported so that the descriptor conventions are pinned by a test of their own. */
+int fdls_umma_linear(int32_t rows, int32_t N, int32_t K, const float* X, const float* W, const float* bias, float* Y,
+                     int32_t relu, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
