@@ -18,5 +18,6 @@ diff_gaussian_rasterization = _il.import_module(__name__ + ".diff_gaussian_raste
 simple_knn = _il.import_module(__name__ + ".simple_knn")
 hexplane = _il.import_module(__name__ + ".hexplane")
 sweep = _il.import_module(__name__ + ".sweep")
+deformation = _il.import_module(__name__ + ".deformation")
 
-__all__ = ["_lib", "_C", "diff_gaussian_rasterization", "simple_knn", "hexplane", "sweep"]
+__all__ = ["_lib", "_C", "diff_gaussian_rasterization", "simple_knn", "hexplane", "sweep", "deformation"]

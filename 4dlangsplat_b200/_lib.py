@@ -90,6 +90,22 @@ class FdlsHexArgs(C.Structure):
     ]
 
 
+FDLS_DEFORM_MAX_HEADS = 6
+FDLS_DEFORM_ACT_NONE, FDLS_DEFORM_ACT_EXP, FDLS_DEFORM_ACT_NORMALIZE, FDLS_DEFORM_ACT_SIGMOID = 0, 1, 2, 3
+
+
+class FdlsDeformHead(C.Structure):
+    _fields_ = [("k", C.c_int32), ("act", C.c_int32), ("w1", _f32p), ("b1", _f32p), ("w2", _f32p), ("b2", _f32p),
+                ("base", _f32p), ("out", _f32p)]
+
+
+class FdlsDeformArgs(C.Structure):
+    _fields_ = [("P", C.c_int32), ("G", C.c_int32), ("W", C.c_int32), ("H", C.c_int32),
+                ("feat", _f32p), ("w0", _f32p), ("b0", _f32p),
+                ("head", FdlsDeformHead * FDLS_DEFORM_MAX_HEADS),
+                ("prep", C.c_void_p), ("prep_bytes", C.c_size_t)]
+
+
 SYMBOLS = {
     "fdls_abi_version": (C.c_int, []),
     "fdls_kernel_launches": (C.c_uint64, []),
@@ -105,6 +121,9 @@ SYMBOLS = {
                                       C.c_void_p, C.c_int32, C.c_void_p]),
     "fdls_umma_linear": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_int32, C.c_void_p]),
+    "fdls_deform_prep_bytes": (C.c_size_t, [C.POINTER(FdlsDeformArgs)]),
+    "fdls_deform_prepare": (C.c_int, [C.POINTER(FdlsDeformArgs), C.c_void_p]),
+    "fdls_deform_forward": (C.c_int, [C.POINTER(FdlsDeformArgs), C.c_void_p]),
     "fdls_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fdls_knn_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "fdls_knn_dist2": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),

@@ -62,6 +62,9 @@ cudaError_t launch_sh_grad_expand(int P, int D, int M, int B, const float* means
 // deform_mlp.cu
 int umma_linear(int rows, int N, int K, const float* X, const float* W, const float* bias, float* Y, int relu,
                 cudaStream_t st);
+size_t deform_prep_bytes(const FdlsDeformArgs* a);
+int deform_prepare(const FdlsDeformArgs* a, cudaStream_t st);
+int deform_forward(const FdlsDeformArgs* a, cudaStream_t st);
 // knn.cu
 size_t knn_workspace_bytes(int N);
 int knn_dist2(int N, const float* xyz, float* out, void* ws, size_t ws_bytes, cudaStream_t st);
@@ -403,5 +406,9 @@ FDLS_API int fdls_umma_linear(int32_t rows, int32_t N, int32_t K, const float* X
   if (rows > 0 && (!X || !W || !Y)) return FDLS_EINVAL;
   return umma_linear(rows, N, K, X, W, bias, Y, relu, (cudaStream_t)stream);
 }
+
+FDLS_API size_t fdls_deform_prep_bytes(const FdlsDeformArgs* a) { return deform_prep_bytes(a); }
+FDLS_API int fdls_deform_prepare(const FdlsDeformArgs* a, void* stream) { return deform_prepare(a, (cudaStream_t)stream); }
+FDLS_API int fdls_deform_forward(const FdlsDeformArgs* a, void* stream) { return deform_forward(a, (cudaStream_t)stream); }
 
 }  // extern "C"

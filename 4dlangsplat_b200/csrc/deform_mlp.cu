@@ -112,4 +112,303 @@ int umma_linear(int rows, int N, int K, const float* X, const float* W, const fl
   return cudaGetLastError() == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
 }
 
+
+// ======================================================================================================================
+// Part 2: the fused network.
+//
+// Per 128-point tile (thread = point = TMEM lane):
+//   X tile -> bf16x3 slabs (sX)                                   trunk GEMM  X W0^T          -> TMEM cols [0, W)
+//   for every head:  ReLU(trunk + b0) -> sA                       layer-1 GEMM sA W1^T        -> TMEM cols [W, 2W)
+//                    ReLU(hidden + b1) -> sA                      layer-2 GEMM sA W2^T        -> TMEM cols [2W, 2W + Npad)
+//                    act(base + out + b2) -> global
+// The trunk accumulator stays in TMEM for the whole tile and is re-read per head (shared memory holds ONE activation
+// buffer: 3 parts x 32 KB at W = 128).  Weights arrive as a fixed cyclic sequence of <= 24 KB operand chunks through a
+// three-slot cp.async ring: while the tensor core works on chunk g the copy of chunk g+1 is in flight, and slot
+// (g+1) % 3 is free because chunk g-2's MMAs have completed (mbarrier of its tcgen05.commit).
+// ======================================================================================================================
+constexpr int DM_CHUNK_BYTES = 24576;
+constexpr int DM_MAX_CHUNKS = 2 + FDLS_DEFORM_MAX_HEADS * (4 + 3);
+constexpr int DM_KIND_TRUNK = 0, DM_KIND_HIDDEN = 1, DM_KIND_OUT = 2;
+
+struct DmChunk {
+  uint32_t off;     // byte offset of the chunk in the prepared buffer
+  uint32_t bytes;   // 3 parts x slabs x N x 16
+  uint16_t N;       // rows of the B operand (= output columns, padded)
+  uint16_t slab0;   // first A slab (8 k each) this chunk multiplies
+  uint16_t slabs;   // slabs in this chunk (even)
+  uint8_t kind, head;
+  uint8_t first, last;  // first / last chunk of its GEMM
+};
+struct DmPlan {
+  int n_chunks;
+  int npad[FDLS_DEFORM_MAX_HEADS];
+  size_t total_bytes;
+  DmChunk c[DM_MAX_CHUNKS];
+};
+
+static int dm_npad(int k) { return ((k + 15) / 16) * 16; }
+
+static int dm_make_plan(const FdlsDeformArgs* a, DmPlan* pl) {
+  if (!a || a->G < 16 || a->G > 128 || (a->G % 16) || (a->W != 64 && a->W != 128) || a->H < 1 ||
+      a->H > FDLS_DEFORM_MAX_HEADS)
+    return FDLS_EUNSUPPORTED;
+  pl->n_chunks = 0;
+  size_t off = 0;
+  auto add = [&](int kind, int head, int N, int K) {
+    const int total = K / 8;
+    int per = DM_CHUNK_BYTES / (N * 48);  // slabs per chunk
+    per &= ~1;
+    if (per < 2) return false;
+    for (int s0 = 0; s0 < total; s0 += per) {
+      const int n = total - s0 < per ? total - s0 : per;
+      DmChunk& c = pl->c[pl->n_chunks++];
+      c.off = (uint32_t)off;
+      c.bytes = (uint32_t)(3 * n * N * 16);
+      c.N = (uint16_t)N; c.slab0 = (uint16_t)s0; c.slabs = (uint16_t)n;
+      c.kind = (uint8_t)kind; c.head = (uint8_t)head;
+      c.first = s0 == 0; c.last = s0 + n >= total;
+      off += align_up(c.bytes, 128);
+    }
+    return true;
+  };
+  if (!add(DM_KIND_TRUNK, 0, a->W, a->G)) return FDLS_EUNSUPPORTED;
+  for (int h = 0; h < a->H; ++h) {
+    const int k = a->head[h].k;
+    if (k < 1 || k > 48) return FDLS_EUNSUPPORTED;
+    pl->npad[h] = dm_npad(k);
+    if (!add(DM_KIND_HIDDEN, h, a->W, a->W)) return FDLS_EUNSUPPORTED;
+    if (!add(DM_KIND_OUT, h, pl->npad[h], a->W)) return FDLS_EUNSUPPORTED;
+  }
+  pl->total_bytes = off;
+  return FDLS_OK;
+}
+
+// one weight matrix (N x K fp32, torch layout) -> the chunks of its GEMM: part p of chunk c at
+// c.off + p * (c.slabs * Npad * 16) + (slab - c.slab0) * Npad * 16 + n * 16; rows n >= N are zero
+__global__ void __launch_bounds__(256)
+deform_prep_kernel(const float* __restrict__ Wm, int N, int Npad, int K, char* __restrict__ prep, DmPlan pl, int kind,
+                   int head) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Npad * (K / 8)) return;
+  const int n = i % Npad, slab = i / Npad;
+  float v[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) v[e] = n < N ? Wm[(size_t)n * K + slab * 8 + e] : 0.f;
+  for (int c = 0; c < pl.n_chunks; ++c) {
+    const DmChunk& ch = pl.c[c];
+    if (ch.kind == kind && ch.head == head && slab >= ch.slab0 && slab < ch.slab0 + ch.slabs) {
+      store_row8_bf3(prep + ch.off + (size_t)(slab - ch.slab0) * Npad * 16 + n * 16, (size_t)ch.slabs * Npad * 16, v);
+      return;
+    }
+  }
+}
+
+struct DmHeadDev {
+  const float* b1; const float* b2; const float* base; float* out;
+  int k, act, npad;
+};
+struct DmDev {
+  int P, G, W, H;
+  const float* feat; const float* b0; const char* prep;
+  DmHeadDev head[FDLS_DEFORM_MAX_HEADS];
+};
+
+template <int N>
+__device__ __forceinline__ void dm_cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+__global__ void __launch_bounds__(DM_ROWS, 1)
+deform_mlp_kernel(DmDev a, DmPlan pl) {
+  extern __shared__ __align__(128) unsigned char dm_smem[];
+  __shared__ uint64_t s_bar[3];
+  __shared__ uint32_t s_tmem;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int W = a.W, G = a.G;
+  const uint32_t x_part = (uint32_t)(G / 8) * DM_ROWS * 16, a_part = (uint32_t)(W / 8) * DM_ROWS * 16;
+  char* sX = reinterpret_cast<char*>(dm_smem);
+  char* sA = sX + 3 * x_part;
+  char* sW = sA + 3 * a_part;  // 3 ring slots of DM_CHUNK_BYTES
+
+  if (warp == 0) tmem_alloc<512>(&s_tmem);
+  if (tid == 0) {
+    for (int i = 0; i < 3; ++i) mbar_init(&s_bar[i], 1);
+    fence_mbar_init();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem = s_tmem;
+  const uint32_t lane_field = (uint32_t)(warp * 32) << 16;
+
+  const int n_tiles = (a.P + DM_ROWS - 1) / DM_ROWS;
+  const int my_tiles = blockIdx.x < n_tiles ? (n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  const long long total_steps = (long long)my_tiles * pl.n_chunks;
+  long long g = 0;  // chunks consumed so far by this CTA
+
+  auto copy_chunk = [&](int c, int slot) {  // all threads; one cp.async group
+    const DmChunk& ch = pl.c[c];
+    const char* src = a.prep + ch.off;
+    char* dst = sW + (size_t)slot * DM_CHUNK_BYTES;
+    for (uint32_t o = tid * 16; o < ch.bytes; o += DM_ROWS * 16) {
+      const uint32_t d = smem_u32(dst + o);
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src + o) : "memory");
+    }
+  };
+  auto wait_mma = [&](long long step) {  // the MMAs of chunk `step` (the latest use of its slot) have completed
+    mbar_wait(&s_bar[step % 3], (uint32_t)((step / 3) & 1));
+    tc_fence_after_sync();
+  };
+  // one chunk: keep the ring full, then issue this chunk's MMAs
+  auto step = [&](int c, uint32_t a_base, uint32_t a_prt, uint32_t d_col) {
+    if (g >= 2) wait_mma(g - 2);
+    if (g + 1 < total_steps) copy_chunk((c + 1) % pl.n_chunks, (int)((g + 1) % 3));
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    dm_cp_async_wait<1>();  // chunk g (committed one step ago) has landed
+    fence_proxy_async();
+    tc_fence_before_sync();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after_sync();
+      const DmChunk& ch = pl.c[c];
+      const uint32_t b_base = smem_u32(sW + (size_t)(g % 3) * DM_CHUNK_BYTES);
+      const uint32_t b_part = (uint32_t)ch.slabs * ch.N * 16;
+      dm_issue_gemm(tmem + d_col, a_base + (uint32_t)ch.slab0 * DM_ROWS * 16, a_prt, b_base, b_part, ch.N,
+                    ch.slabs / 2, !ch.first);
+      mma_commit(&s_bar[g % 3]);
+    }
+    ++g;
+  };
+  // TMEM columns [col, col + W) + bias, ReLU -> sA (the next GEMM's A operand)
+  auto relu_to_A = [&](uint32_t col, const float* __restrict__ bias) {
+    for (int c = 0; c < W; c += 8) {
+      float v[8];
+      tmem_ld8(tmem + lane_field + col + c, v);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e] + __ldg(bias + c + e), 0.f);
+      store_row8_bf3(sA + (size_t)(c / 8) * DM_ROWS * 16 + tid * 16, a_part, v);
+    }
+  };
+  auto write_out = [&](int h, int row) {
+    const DmHeadDev& hd = a.head[h];
+    float y[48];
+    for (int c = 0; c < hd.npad; c += 8) {
+      float v[8];
+      tmem_ld8(tmem + lane_field + 2 * W + c, v);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) y[c + e] = v[e];
+    }
+    if (row >= a.P) return;
+    float nrm = 0.f;
+    for (int e = 0; e < hd.k; ++e) {
+      float t = y[e] + __ldg(hd.b2 + e);
+      if (hd.base) t = hd.base[(size_t)row * hd.k + e] + t;
+      if (hd.act == FDLS_DEFORM_ACT_EXP) t = expf(t);
+      else if (hd.act == FDLS_DEFORM_ACT_SIGMOID) t = 1.f / (1.f + expf(-t));
+      y[e] = t;
+      nrm += t * t;
+    }
+    if (hd.act == FDLS_DEFORM_ACT_NORMALIZE) {
+      const float inv = 1.f / fmaxf(sqrtf(nrm), 1e-12f);
+      for (int e = 0; e < hd.k; ++e) y[e] *= inv;
+    }
+    for (int e = 0; e < hd.k; ++e) hd.out[(size_t)row * hd.k + e] = y[e];
+  };
+
+  if (total_steps > 0) copy_chunk(0, 0);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+
+  for (int t = 0; t < my_tiles; ++t) {
+    const int row = ((int)blockIdx.x + t * (int)gridDim.x) * DM_ROWS + tid;
+    // ---- X tile: the trunk MMAs of the previous tile completed long ago (every later chunk was waited for)
+    for (int slab = 0; slab < G / 8; ++slab) {
+      float v[8];
+      if (row < a.P) {
+        const float4 p = *reinterpret_cast<const float4*>(a.feat + (size_t)row * G + slab * 8);
+        const float4 q = *reinterpret_cast<const float4*>(a.feat + (size_t)row * G + slab * 8 + 4);
+        v[0] = p.x; v[1] = p.y; v[2] = p.z; v[3] = p.w; v[4] = q.x; v[5] = q.y; v[6] = q.z; v[7] = q.w;
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = 0.f;
+      }
+      store_row8_bf3(sX + (size_t)slab * DM_ROWS * 16 + tid * 16, x_part, v);
+    }
+    int c = 0;
+    for (; c < pl.n_chunks && pl.c[c].kind == DM_KIND_TRUNK; ++c) step(c, smem_u32(sX), x_part, 0);
+    for (int h = 0; h < a.H; ++h) {
+      wait_mma(g - 1);  // trunk (h = 0) or the previous head's layer 2: sA is free, its accumulator complete
+      if (h > 0) write_out(h - 1, row);
+      relu_to_A(0, a.b0);
+      for (; c < pl.n_chunks && pl.c[c].kind == DM_KIND_HIDDEN && pl.c[c].head == h; ++c)
+        step(c, smem_u32(sA), a_part, (uint32_t)W);
+      wait_mma(g - 1);
+      relu_to_A((uint32_t)W, a.head[h].b1);
+      for (; c < pl.n_chunks && pl.c[c].kind == DM_KIND_OUT && pl.c[c].head == h; ++c)
+        step(c, smem_u32(sA), a_part, (uint32_t)(2 * W));
+    }
+    wait_mma(g - 1);
+    write_out(a.H - 1, row);
+  }
+  dm_cp_async_wait<0>();
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc<512>(tmem);
+}
+
+static size_t dm_smem_bytes(int G, int W) {
+  return (size_t)3 * (G / 8) * DM_ROWS * 16 + (size_t)3 * (W / 8) * DM_ROWS * 16 + 3 * DM_CHUNK_BYTES;
+}
+
+size_t deform_prep_bytes(const FdlsDeformArgs* a) {
+  DmPlan pl;
+  return dm_make_plan(a, &pl) == FDLS_OK ? pl.total_bytes : 0;
+}
+
+int deform_prepare(const FdlsDeformArgs* a, cudaStream_t st) {
+  DmPlan pl;
+  int rc = dm_make_plan(a, &pl);
+  if (rc) return rc;
+  if (!a->prep || a->prep_bytes < pl.total_bytes || !a->w0) return FDLS_EINVAL;
+  char* prep = (char*)a->prep;
+  auto run = [&](const float* Wm, int N, int Npad, int K, int kind, int head) {
+    const int n = Npad * (K / 8);
+    deform_prep_kernel<<<cdiv(n, 256), 256, 0, st>>>(Wm, N, Npad, K, prep, pl, kind, head);
+    count_launch();
+  };
+  run(a->w0, a->W, a->W, a->G, DM_KIND_TRUNK, 0);
+  for (int h = 0; h < a->H; ++h) {
+    if (!a->head[h].w1 || !a->head[h].w2) return FDLS_EINVAL;
+    run(a->head[h].w1, a->W, a->W, a->W, DM_KIND_HIDDEN, h);
+    run(a->head[h].w2, a->head[h].k, pl.npad[h], a->W, DM_KIND_OUT, h);
+  }
+  return cudaGetLastError() == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
+}
+
+int deform_forward(const FdlsDeformArgs* a, cudaStream_t st) {
+  DmPlan pl;
+  int rc = dm_make_plan(a, &pl);
+  if (rc) return rc;
+  if (a->P < 0 || !a->prep || a->prep_bytes < pl.total_bytes) return FDLS_EINVAL;
+  if (a->P == 0) return FDLS_OK;
+  if (!a->feat || !a->b0) return FDLS_EINVAL;
+  DmDev d;
+  d.P = a->P; d.G = a->G; d.W = a->W; d.H = a->H;
+  d.feat = a->feat; d.b0 = a->b0; d.prep = (const char*)a->prep;
+  for (int h = 0; h < a->H; ++h) {
+    const FdlsDeformHead& s = a->head[h];
+    if (!s.b1 || !s.b2 || !s.out) return FDLS_EINVAL;
+    d.head[h] = {s.b1, s.b2, s.base, s.out, s.k, s.act, pl.npad[h]};
+  }
+  const size_t smem = dm_smem_bytes(a->G, a->W);
+  static SmemOptIn optin;
+  if (optin.ensure(deform_mlp_kernel, smem) != cudaSuccess) return FDLS_ECUDA;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int n_tiles = cdiv(a->P, DM_ROWS);
+  count_launch();
+  deform_mlp_kernel<<<n_tiles < sms ? n_tiles : sms, DM_ROWS, smem, st>>>(d, pl);
+  return cudaGetLastError() == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
+}
+
 }  // namespace fdls

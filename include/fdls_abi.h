@@ -274,6 +274,46 @@ int fdls_hexplane_unpack_grad_batch(int32_t n, int32_t C, const int64_t* HW, con
 int fdls_umma_linear(int32_t rows, int32_t N, int32_t K, const float* X, const float* W, const float* bias, float* Y,
                      int32_t relu, void* stream);
 
+/* The deformation MLP, fused (Deformation.query_time + forward_dynamic, scene/deformation.py:70-182, with the
+ * activations gaussian_renderer/__init__.py:191-193 applies afterwards):
+ *     hidden = feature_out(grid_feature)                       Linear(G, W)                       (:45-58, defor_depth <= 1)
+ *     head h: delta_h = Linear(W, k_h)(ReLU(Linear(W, W)(ReLU(hidden))))                           (:59-65)
+ *     out_h  = act_h(base_h + delta_h)                          base = the canonical attribute      (:118-147)
+ * for up to FDLS_DEFORM_MAX_HEADS heads (pos / scales / rotations / opacity / shs / discrete-coefficient heads; which
+ * ones exist is the caller's choice: the reference switches them with no_dx, no_ds, no_dr, no_do, no_dshs).
+ * One persistent kernel: 128 points per CTA tile, every GEMM on tcgen05 (bf16 x 3), accumulators in TMEM, activations
+ * kept in shared memory between layers; the weights stream from L2 as pre-split operand chunks (fdls_deform_prepare,
+ * once per parameter update).  G % 16 == 0, G <= 128, W in {64, 128}, k_h <= 48. */
+#define FDLS_DEFORM_MAX_HEADS 6
+#define FDLS_DEFORM_ACT_NONE 0
+#define FDLS_DEFORM_ACT_EXP 1       /* scaling_activation = torch.exp (scene/gaussian_model.py:48) */
+#define FDLS_DEFORM_ACT_NORMALIZE 2 /* rotation_activation = F.normalize: x / max(||x||, 1e-12) (:55) */
+#define FDLS_DEFORM_ACT_SIGMOID 3   /* opacity_activation = torch.sigmoid (:52) */
+typedef struct FdlsDeformHead {
+  int32_t k;         /* output width of the head (3, 3, 4, 1, 48, ...) */
+  int32_t act;       /* FDLS_DEFORM_ACT_* applied to base + delta */
+  const float* w1;   /* (W, W)  Linear weight, torch layout (out, in) */
+  const float* b1;   /* (W) */
+  const float* w2;   /* (k, W) */
+  const float* b2;   /* (k) */
+  const float* base; /* (P, k) canonical attribute added to the head's output, or null */
+  float* out;        /* (P, k) */
+} FdlsDeformHead;
+typedef struct FdlsDeformArgs {
+  int32_t P, G, W, H;
+  const float* feat; /* (P, G) grid features (fdls_hexplane_forward's output) */
+  const float* w0;   /* (W, G) feature_out[0].weight */
+  const float* b0;   /* (W) */
+  FdlsDeformHead head[FDLS_DEFORM_MAX_HEADS];
+  void* prep;        /* fdls_deform_prep_bytes() bytes, filled by fdls_deform_prepare, read by fdls_deform_forward */
+  size_t prep_bytes;
+} FdlsDeformArgs;
+size_t fdls_deform_prep_bytes(const FdlsDeformArgs* a);
+/* split every weight matrix into bf16 x 3 operand chunks (reads w0, w1, w2 of every head; P, feat, base, out unused) */
+int fdls_deform_prepare(const FdlsDeformArgs* a, void* stream);
+/* reads feat, biases, base and `prep`; writes out of every head */
+int fdls_deform_forward(const FdlsDeformArgs* a, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -29,7 +29,8 @@ def test_struct_layouts_match_header(fdls):
     hdr = open(os.path.join(ROOT, "include", "fdls_abi.h")).read()
     for cname, cls in (("FdlsFwdArgs", fdls._lib.FdlsFwdArgs), ("FdlsBwdArgs", fdls._lib.FdlsBwdArgs),
                        ("FdlsLayout", fdls._lib.FdlsLayout), ("FdlsWorkspaceSizes", fdls._lib.FdlsWorkspaceSizes),
-                       ("FdlsHexArgs", fdls._lib.FdlsHexArgs)):
+                       ("FdlsHexArgs", fdls._lib.FdlsHexArgs), ("FdlsDeformHead", fdls._lib.FdlsDeformHead),
+                       ("FdlsDeformArgs", fdls._lib.FdlsDeformArgs)):
         body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (cname, cname), hdr, re.S).group(1)
         body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
         names = []
