@@ -123,8 +123,9 @@ int umma_linear(int rows, int N, int K, const float* X, const float* W, const fl
 //                    act(base + out + b2) -> global
 // The trunk accumulator stays in TMEM for the whole tile and is re-read per head (shared memory holds ONE activation
 // buffer: 3 parts x 32 KB at W = 128).  Weights arrive as a fixed cyclic sequence of <= 24 KB operand chunks through a
-// three-slot cp.async ring: while the tensor core works on chunk g the copy of chunk g+1 is in flight, and slot
-// (g+1) % 3 is free because chunk g-2's MMAs have completed (mbarrier of its tcgen05.commit).
+// five-slot cp.async ring: while the tensor core works on chunk g the copies of chunks g+1 .. g+3 are in flight (an L2
+// round trip is longer than a chunk's MMAs), and slot (g+3) % 5 is free because chunk g-2's MMAs have completed
+// (mbarrier of its tcgen05.commit).  The input tile aliases the activation buffer.
 // ======================================================================================================================
 constexpr int DM_CHUNK_BYTES = 24576;
 constexpr int DM_MAX_CHUNKS = 2 + FDLS_DEFORM_MAX_HEADS * (4 + 3);
@@ -213,83 +214,126 @@ struct DmDev {
   DmHeadDev head[FDLS_DEFORM_MAX_HEADS];
 };
 
+constexpr int DM_THREADS = 256;  // two threads per point in the epilogues (columns split in halves); thread 0 issues MMAs
+constexpr int DM_SLOTS = 5;      // weight-chunk ring: chunk g+3 is copied while chunk g multiplies
+constexpr int DM_AHEAD = 3;
+
 template <int N>
 __device__ __forceinline__ void dm_cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-__global__ void __launch_bounds__(DM_ROWS, 1)
+// like dm_issue_gemm, with the descriptors advanced by adding to their address field (3 instructions per MMA)
+__device__ __forceinline__ void dm_issue_chunk(uint32_t tmem_d, uint32_t a_base, uint32_t a_part, uint32_t b_base,
+                                               uint32_t b_part, int N, int ksteps, bool accumulate_first) {
+  const uint32_t idesc = instr_desc_bf16(DM_ROWS, N);
+  const uint32_t a_slab = DM_ROWS * 16, b_slab = (uint32_t)N * 16;
+  uint64_t da[3], db[3];
+#pragma unroll
+  for (int p = 0; p < 3; ++p) {
+    da[p] = smem_desc(a_base + p * a_part, a_slab, 128);
+    db[p] = smem_desc(b_base + p * b_part, b_slab, 128);
+  }
+  const uint64_t a_inc = (2 * a_slab) >> 4, b_inc = (2 * b_slab) >> 4;  // one K = 16 step, in 16-byte units
+  bool acc = accumulate_first;
+  for (int ks = 0; ks < ksteps; ++ks) {
+#pragma unroll
+    for (int t = 0; t < 6; ++t) {
+      mma_bf16(tmem_d, da[DM_TERMS[t][0]], db[DM_TERMS[t][1]], idesc, acc);
+      acc = true;
+    }
+#pragma unroll
+    for (int p = 0; p < 3; ++p) {
+      da[p] += a_inc;
+      db[p] += b_inc;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(DM_THREADS, 1)
 deform_mlp_kernel(DmDev a, DmPlan pl) {
   extern __shared__ __align__(128) unsigned char dm_smem[];
-  __shared__ uint64_t s_bar[3];
+  __shared__ uint64_t s_bar[DM_SLOTS];
   __shared__ uint32_t s_tmem;
+  __shared__ float s_bias[(1 + FDLS_DEFORM_MAX_HEADS) * 128];  // b0, then b1 of every head
   const int tid = threadIdx.x, warp = tid >> 5;
+  const int prow = tid & (DM_ROWS - 1);  // point of the tile this thread works on = TMEM lane
+  const int half = tid >> 7;             // which half of the columns / slabs it takes in the epilogues
   const int W = a.W, G = a.G;
   const uint32_t x_part = (uint32_t)(G / 8) * DM_ROWS * 16, a_part = (uint32_t)(W / 8) * DM_ROWS * 16;
-  char* sX = reinterpret_cast<char*>(dm_smem);
-  char* sA = sX + 3 * x_part;
-  char* sW = sA + 3 * a_part;  // 3 ring slots of DM_CHUNK_BYTES
+  char* sA = reinterpret_cast<char*>(dm_smem);
+  char* sX = sA;  // the input tile is dead once the trunk GEMM has completed, which is when sA is first written
+  char* sW = sA + 3 * a_part;  // DM_SLOTS ring slots of DM_CHUNK_BYTES
 
   if (warp == 0) tmem_alloc<512>(&s_tmem);
   if (tid == 0) {
-    for (int i = 0; i < 3; ++i) mbar_init(&s_bar[i], 1);
+    for (int i = 0; i < DM_SLOTS; ++i) mbar_init(&s_bar[i], 1);
     fence_mbar_init();
   }
+  for (int i = tid; i < W; i += DM_THREADS) s_bias[i] = a.b0[i];
+  for (int h = 0; h < a.H; ++h)
+    for (int i = tid; i < W; i += DM_THREADS) s_bias[(1 + h) * 128 + i] = a.head[h].b1[i];
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem = s_tmem;
-  const uint32_t lane_field = (uint32_t)(warp * 32) << 16;
+  const uint32_t lane_field = (uint32_t)((warp & 3) * 32) << 16;  // a warp reads the TMEM lane quadrant warp % 4
 
   const int n_tiles = (a.P + DM_ROWS - 1) / DM_ROWS;
   const int my_tiles = blockIdx.x < n_tiles ? (n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
   const long long total_steps = (long long)my_tiles * pl.n_chunks;
   long long g = 0;  // chunks consumed so far by this CTA
 
-  auto copy_chunk = [&](int c, int slot) {  // all threads; one cp.async group
-    const DmChunk& ch = pl.c[c];
+  auto copy_chunk = [&](long long step) {  // all threads; the caller commits the cp.async group
+    if (step >= total_steps) return;
+    const DmChunk& ch = pl.c[step % pl.n_chunks];
     const char* src = a.prep + ch.off;
-    char* dst = sW + (size_t)slot * DM_CHUNK_BYTES;
-    for (uint32_t o = tid * 16; o < ch.bytes; o += DM_ROWS * 16) {
+    char* dst = sW + (size_t)(step % DM_SLOTS) * DM_CHUNK_BYTES;
+    for (uint32_t o = tid * 16; o < ch.bytes; o += DM_THREADS * 16) {
       const uint32_t d = smem_u32(dst + o);
       asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src + o) : "memory");
     }
   };
   auto wait_mma = [&](long long step) {  // the MMAs of chunk `step` (the latest use of its slot) have completed
-    mbar_wait(&s_bar[step % 3], (uint32_t)((step / 3) & 1));
+    mbar_wait(&s_bar[step % DM_SLOTS], (uint32_t)((step / DM_SLOTS) & 1));
     tc_fence_after_sync();
   };
   // one chunk: keep the ring full, then issue this chunk's MMAs
   auto step = [&](int c, uint32_t a_base, uint32_t a_prt, uint32_t d_col) {
-    if (g >= 2) wait_mma(g - 2);
-    if (g + 1 < total_steps) copy_chunk((c + 1) % pl.n_chunks, (int)((g + 1) % 3));
+    if (g >= 2) wait_mma(g - 2);  // slot (g + DM_AHEAD) % DM_SLOTS == (g - 2) % DM_SLOTS is free
+    copy_chunk(g + DM_AHEAD);
     asm volatile("cp.async.commit_group;" ::: "memory");
-    dm_cp_async_wait<1>();  // chunk g (committed one step ago) has landed
+    dm_cp_async_wait<DM_AHEAD>();  // chunk g has landed (the DM_AHEAD younger groups may still be in flight)
     fence_proxy_async();
     tc_fence_before_sync();
     __syncthreads();
     if (tid == 0) {
       tc_fence_after_sync();
       const DmChunk& ch = pl.c[c];
-      const uint32_t b_base = smem_u32(sW + (size_t)(g % 3) * DM_CHUNK_BYTES);
+      const uint32_t b_base = smem_u32(sW + (size_t)(g % DM_SLOTS) * DM_CHUNK_BYTES);
       const uint32_t b_part = (uint32_t)ch.slabs * ch.N * 16;
-      dm_issue_gemm(tmem + d_col, a_base + (uint32_t)ch.slab0 * DM_ROWS * 16, a_prt, b_base, b_part, ch.N,
-                    ch.slabs / 2, !ch.first);
-      mma_commit(&s_bar[g % 3]);
+      dm_issue_chunk(tmem + d_col, a_base + (uint32_t)ch.slab0 * DM_ROWS * 16, a_prt, b_base, b_part, ch.N,
+                     ch.slabs / 2, !ch.first);
+      mma_commit(&s_bar[g % DM_SLOTS]);
     }
     ++g;
   };
-  // TMEM columns [col, col + W) + bias, ReLU -> sA (the next GEMM's A operand)
+  // TMEM columns [col, col + W) + bias, ReLU -> sA (the next GEMM's A operand); this thread: W/2 columns of its point
   auto relu_to_A = [&](uint32_t col, const float* __restrict__ bias) {
-    for (int c = 0; c < W; c += 8) {
-      float v[8];
-      tmem_ld8(tmem + lane_field + col + c, v);
+    const int c0 = half * (W / 2);
+    for (int c = c0; c < c0 + W / 2; c += 32) {
+      float v[32];
+      tmem_ld32(tmem + lane_field + col + c, v);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e] + __ldg(bias + c + e), 0.f);
-      store_row8_bf3(sA + (size_t)(c / 8) * DM_ROWS * 16 + tid * 16, a_part, v);
+      for (int sl = 0; sl < 4; ++sl) {
+        float w8[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) w8[e] = fmaxf(v[sl * 8 + e] + bias[c + sl * 8 + e], 0.f);
+        store_row8_bf3(sA + (size_t)(c / 8 + sl) * DM_ROWS * 16 + prow * 16, a_part, w8);
+      }
     }
   };
-  auto write_out = [&](int h, int row) {
+  auto write_out = [&](int h, int row) {  // warps 0-3 only
     const DmHeadDev& hd = a.head[h];
     float y[48];
     for (int c = 0; c < hd.npad; c += 8) {
@@ -315,13 +359,15 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
     for (int e = 0; e < hd.k; ++e) hd.out[(size_t)row * hd.k + e] = y[e];
   };
 
-  if (total_steps > 0) copy_chunk(0, 0);
-  asm volatile("cp.async.commit_group;" ::: "memory");
+  for (int i = 0; i < DM_AHEAD; ++i) {  // prime the ring: chunks 0 .. DM_AHEAD-1, one group each
+    copy_chunk(i);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
 
   for (int t = 0; t < my_tiles; ++t) {
-    const int row = ((int)blockIdx.x + t * (int)gridDim.x) * DM_ROWS + tid;
-    // ---- X tile: the trunk MMAs of the previous tile completed long ago (every later chunk was waited for)
-    for (int slab = 0; slab < G / 8; ++slab) {
+    const int row = ((int)blockIdx.x + t * (int)gridDim.x) * DM_ROWS + prow;
+    // ---- X tile (aliases sA): every MMA that read sA for the previous tile has completed (wait_mma before write_out)
+    for (int slab = half; slab < G / 8; slab += 2) {
       float v[8];
       if (row < a.P) {
         const float4 p = *reinterpret_cast<const float4*>(a.feat + (size_t)row * G + slab * 8);
@@ -331,23 +377,25 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) v[e] = 0.f;
       }
-      store_row8_bf3(sX + (size_t)slab * DM_ROWS * 16 + tid * 16, x_part, v);
+      store_row8_bf3(sX + (size_t)slab * DM_ROWS * 16 + prow * 16, x_part, v);
     }
     int c = 0;
     for (; c < pl.n_chunks && pl.c[c].kind == DM_KIND_TRUNK; ++c) step(c, smem_u32(sX), x_part, 0);
     for (int h = 0; h < a.H; ++h) {
       wait_mma(g - 1);  // trunk (h = 0) or the previous head's layer 2: sA is free, its accumulator complete
-      if (h > 0) write_out(h - 1, row);
-      relu_to_A(0, a.b0);
+      if (h > 0 && half == 0) write_out(h - 1, row);
+      relu_to_A(0, s_bias);
       for (; c < pl.n_chunks && pl.c[c].kind == DM_KIND_HIDDEN && pl.c[c].head == h; ++c)
         step(c, smem_u32(sA), a_part, (uint32_t)W);
       wait_mma(g - 1);
-      relu_to_A((uint32_t)W, a.head[h].b1);
+      relu_to_A((uint32_t)W, s_bias + (1 + h) * 128);
       for (; c < pl.n_chunks && pl.c[c].kind == DM_KIND_OUT && pl.c[c].head == h; ++c)
         step(c, smem_u32(sA), a_part, (uint32_t)(2 * W));
     }
     wait_mma(g - 1);
-    write_out(a.H - 1, row);
+    if (half == 0) write_out(a.H - 1, row);
+    tc_fence_before_sync();
+    __syncthreads();  // the next tile's X store may not overtake another warp's write_out ... of TMEM? no: of nothing
   }
   dm_cp_async_wait<0>();
   tc_fence_before_sync();
@@ -356,7 +404,8 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
 }
 
 static size_t dm_smem_bytes(int G, int W) {
-  return (size_t)3 * (G / 8) * DM_ROWS * 16 + (size_t)3 * (W / 8) * DM_ROWS * 16 + 3 * DM_CHUNK_BYTES;
+  const int K = G > W ? G : W;  // the input tile aliases the activation buffer
+  return (size_t)3 * (K / 8) * DM_ROWS * 16 + (size_t)DM_SLOTS * DM_CHUNK_BYTES;
 }
 
 size_t deform_prep_bytes(const FdlsDeformArgs* a) {
@@ -407,7 +456,7 @@ int deform_forward(const FdlsDeformArgs* a, cudaStream_t st) {
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int n_tiles = cdiv(a->P, DM_ROWS);
   count_launch();
-  deform_mlp_kernel<<<n_tiles < sms ? n_tiles : sms, DM_ROWS, smem, st>>>(d, pl);
+  deform_mlp_kernel<<<n_tiles < sms ? n_tiles : sms, DM_THREADS, smem, st>>>(d, pl);
   return cudaGetLastError() == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
 }
 

@@ -906,6 +906,191 @@ def main_hexplane(a, rank, world, local, warmup):
         dist.destroy_process_group()
 
 
+def main_deform(a, rank, world, local, warmup):
+    """SURVEY 8f N1 / 8d metric (i) "end to end incl. deformation": cfg2's sweep where every frame first moves the
+    300k Gaussians to its timestamp with the deformation network (arguments/hypernerf/default.py: 16-channel HexPlane
+    [64,64,64,150] x multires [1,2,4], net_width 128, defor_depth 1, heads pos / scales / rotations) and then
+    rasterizes.  ours: HexPlane kernel + one tcgen05 MLP kernel (activations fused) + the rasterizer;
+    --impl reference: the reference's op sequence (18 grid_sample + 18 products + cat, F.linear layers, exp / normalize
+    / sigmoid) on stock torch kernels + the unmodified reference rasterizer (oracle/_ref), same GPU.
+    value = frames/s of deformation + render; `deform` = the deformation alone with its tensor-core roofline."""
+    import itertools
+    from types import SimpleNamespace
+    import torch.nn.functional as F
+    fd = importlib.import_module("4dlangsplat_b200")
+    lib = fd._lib.load()
+    wl = Workload("cfg2", rank, world)
+    s = wl.s
+    torch.manual_seed(7)
+    args = SimpleNamespace(net_width=128, timebase_pe=4, defor_depth=1, posebase_pe=10, scale_rotation_pe=2, opacity_pe=2,
+                           timenet_width=64, timenet_output=32, bounds=1.6, no_dx=False, no_grid=False, no_ds=False,
+                           no_dr=False, no_do=True, no_dshs=True, no_dlang=1, empty_voxel=False, grid_pe=0,
+                           static_mlp=False, apply_rotation=False, multires=[1, 2, 4],
+                           kplanes_config=dict(grid_dimensions=2, input_coordinate_dim=4, output_coordinate_dim=16,
+                                               resolution=[64, 64, 64, 150]))
+    net = fd.deformation.deform_network(args).cuda()
+    with torch.no_grad():
+        for n, q in net.named_parameters():
+            if "grid" in n:
+                q.add_(0.05 * torch.randn_like(q))
+            elif any(h in n for h in ("pos_deform.3", "scales_deform.3", "rotations_deform.3")):
+                q.mul_(0.02)  # small deltas: the deformed scene keeps cfg2's shape
+    dn = net.deformation_net
+    pts_min, pts_max = wl.means[0].min(0).values, wl.means[0].max(0).values
+    dn.set_aabb((pts_max + 0.1).tolist(), (pts_min - 0.1).tolist())
+    P = s.P
+    p0 = wl.sets[0]
+    xyz = wl.means[0].contiguous()
+    log_scales, raw_opac = torch.log(p0["scales"]), torch.logit(p0["opac"].clamp(1e-4, 1 - 1e-4))
+    times = [torch.full((P, 1), float(t), device="cuda") for t in wl.times]
+    combs = list(itertools.combinations(range(4), 2))
+    E = torch.Tensor([])
+
+    def deform_ours(i):
+        return net.forward_dynamic(xyz, log_scales, p0["rots"], raw_opac, p0["shs"], p0["lang"],
+                                   times[i % N_TIMESTAMPS], activations=True)
+
+    def deform_ref(i):  # the reference op sequence, stock torch kernels (scene/hexplane.py:65-106, deformation.py)
+        tm = times[i % N_TIMESTAMPS]
+        fdm = fd.deformation
+        point_emb, scales_emb = fdm.poc_fre(xyz, net.pos_poc), fdm.poc_fre(log_scales, net.rotation_scaling_poc)
+        rot_emb, _ = fdm.poc_fre(p0["rots"], net.rotation_scaling_poc), fdm.poc_fre(tm, net.time_poc)
+        aabb = dn.grid.aabb
+        q = torch.cat([(point_emb[:, :3] - aabb[0]) * (2.0 / (aabb[1] - aabb[0])) - 1.0, tm], dim=-1)
+        feats = []
+        for level in dn.grid.grids:
+            space = 1.0
+            for ci, comb in enumerate(combs):
+                o = F.grid_sample(level[ci], q[..., list(comb)].view(1, 1, -1, 2), align_corners=True, mode="bilinear",
+                                  padding_mode="border")
+                space = space * o.view(level[ci].shape[1], -1).t()
+            feats.append(space)
+        hidden = dn.feature_out(torch.cat(feats, dim=-1))
+        pts = point_emb[:, :3] + dn.pos_deform(hidden)
+        sc = scales_emb[:, :3] + dn.scales_deform(hidden)
+        rt = rot_emb[:, :4] + dn.rotations_deform(hidden)
+        return pts, torch.exp(sc), F.normalize(rt), torch.sigmoid(raw_opac), p0["shs"], p0["lang"], None
+
+    if a.impl == "ours":
+        def frame(i, with_render=True):
+            with torch.no_grad():
+                pts, sc, rt, op, shs, lang, _ = deform_ours(i)
+                if with_render:
+                    return fd._C.rasterize_gaussians(wl.bg, pts, E, lang, op, sc, rt, 1.0, E, wl.view, wl.proj, s.tanfovx,
+                                                     s.tanfovy, s.H, s.W, shs, s.sh_degree, wl.campos, False, False, True)
+    else:
+        import refcuda
+        ref = refcuda.Ref(s.F)
+        f32 = dict(dtype=torch.float32, device="cuda")
+        o = dict(color=torch.empty((3, s.H, s.W), **f32), lang=torch.empty((s.F, s.H, s.W), **f32),
+                 depth=torch.empty((1, s.H, s.W), **f32))
+        radii = torch.empty(P, dtype=torch.int32, device="cuda")
+
+        def frame(i, with_render=True):
+            with torch.no_grad():
+                pts, sc, rt, op, shs, lang, _ = deform_ref(i)
+                if with_render:
+                    o["color"].zero_(); o["lang"].zero_(); o["depth"].zero_(); radii.zero_()
+                    return ref.forward_raw(P, s.sh_degree, s.shs.shape[1], s.W, s.H, wl.bg, pts.contiguous(), shs, lang,
+                                           op.contiguous(), sc.contiguous(), rt.contiguous(), wl.view, wl.proj,
+                                           wl.campos, s.tanfovx, s.tanfovy, o["color"], o["lang"], o["depth"], radii)
+
+    res = {}
+    for with_render in (False, True):
+        for i in range(warmup * FRAMES_PER_STEP // 4 + 8):
+            frame(i, with_render)
+        barrier(world)
+        l0 = lib.fdls_kernel_launches()
+        sampler = ClockSampler(local)
+        sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(a.steps * FRAMES_PER_STEP):
+            frame(i, with_render)
+        e1.record()
+        barrier(world)
+        res[with_render] = (max_over_ranks(e0.elapsed_time(e1), world), lib.fdls_kernel_launches() - l0, sampler.result())
+    n_frames = a.steps * FRAMES_PER_STEP
+    # parity inside the bench: the fused deformation equals the op sequence on this very network
+    with torch.no_grad():
+        mine, theirs = deform_ours(3), deform_ref(3)
+    for x, y, nm in zip(mine[:3], theirs[:3], ("pts", "scales", "rotations")):
+        err = float((x - y).abs().max())
+        if not err <= 2e-5 * max(1.0, float(y.abs().max())):
+            raise SystemExit("fused deformation differs from the reference op sequence on %s: %g" % (nm, err))
+    # end to end: per frame the timestamp (4 bytes) goes up, the three images come down
+    outs_host = [torch.empty((3, s.H, s.W)).pin_memory(), torch.empty((s.F, s.H, s.W)).pin_memory(),
+                 torch.empty((1, s.H, s.W)).pin_memory()]
+    t_host = torch.zeros(1).pin_memory()
+    barrier(world)
+    t0 = time.perf_counter()
+    for i in range(n_frames):
+        t_host[0] = wl.times[i % N_TIMESTAMPS]
+        times[i % N_TIMESTAMPS].copy_(t_host.to("cuda", non_blocking=True).expand(P, 1))
+        r = frame(i, True)
+        imgs = (r[1], r[2], r[3]) if a.impl == "ours" else (o["color"], o["lang"], o["depth"])
+        for h, im in zip(outs_host, imgs):
+            h.copy_(im, non_blocking=True)
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0, world)
+    barrier(world)
+    ms_d, launches_d, _ = res[False]
+    ms, launches, clocks = res[True]
+    pk, pk_kind = peaks()
+    W_, G_ = args.net_width, dn.grid.feat_dim
+    flops = 2.0 * P * (G_ * W_ + 3 * W_ * W_ + W_ * (3 + 3 + 4))
+    line = {"metric": "render_with_deformation_frames_per_s", "value": round(n_frames * world / (ms * 1e-3), 2),
+            "unit": "frames/s", "n_gpus": world, "steps": a.steps, "warmup": warmup, "ms_per_step": round(ms / a.steps, 4),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "cfg2 incl. deformation: %d Gaussians moved to each of %d timestamps per step by the "
+                                   "HyperNeRF-configured deformation network (HexPlane 16 ch [64,64,64,150] x [1,2,4], "
+                                   "net_width 128, heads pos/scales/rotations), then rendered at %dx%d with %d language "
+                                   "channels" % (P, FRAMES_PER_STEP, s.W, s.H, s.F),
+                       "l2": "per frame 58 MB of features + 19 MB of records + the images stream through HBM; weights "
+                             "(0.7 MB as bf16x3 chunks) and planes (30 MB) are L2-resident by design"},
+            "clocks": clocks,
+            "e2e": {"value": round(n_frames * world / e2e_s, 2), "unit": "frames/s", "h2d_bytes_per_step": 4 * FRAMES_PER_STEP,
+                    "d2h_bytes_per_step": sum(h.numel() * 4 for h in outs_host) * FRAMES_PER_STEP},
+            "gpu_launches": int(launches),
+            "deform": {"frames_per_s": round(n_frames * world / (ms_d * 1e-3), 2), "ms_per_frame": round(ms_d / n_frames, 4),
+                       "gpu_launches": int(launches_d)}}
+    if a.impl == "ours":
+        # MLP kernel alone: CUDA events around repeated launches of the fused kernel on fixed features
+        with torch.no_grad():
+            feat = dn.grid(xyz, times[0])
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            dn.grid.forward = lambda *_: feat  # instance attribute shadows the method: the MLP kernel alone
+            try:
+                for _ in range(5):
+                    deform_ours(0)
+                ev0.record()
+                for _ in range(50):
+                    deform_ours(0)
+                ev1.record()
+            finally:
+                del dn.grid.forward
+            torch.cuda.synchronize()
+        mlp_ms = ev0.elapsed_time(ev1) / 50
+        ach = flops / (mlp_ms * 1e-3) / 1e12
+        peak = pk.get("bf16_tflops_sustained", 1400.0)
+        line["roofline"] = {"bound": "tensor", "kernel": "deform_mlp_kernel", "achieved": round(ach, 1), "peak": peak,
+                            "unit": "TFLOP/s", "frac": round(ach / peak, 4), "traffic": None, "peak_source": pk_kind,
+                            "algorithmic_flops_per_launch": int(flops), "avg_launch_ms": round(mlp_ms, 4),
+                            "note": "algorithmic fp32 FLOPs of the network; the tensor cores execute 6 bf16 products per "
+                                    "fp32 product (bf16x3 split) plus head padding to N = 16, i.e. %.1f TFLOP/s of bf16 "
+                                    "work" % (6 * ach * (G_ * W_ + 3 * W_ * W_ + 3 * W_ * 16) / (G_ * W_ + 3 * W_ * W_ + W_ * 10))}
+    else:
+        line["impl"] = "reference"
+        line["cpu_baseline"] = {"value": line["value"], "unit": "frames/s", "cores": 1, "kind": "port",
+                                "sample": "the reference's op sequence for the deformation on stock torch CUDA kernels + "
+                                          "the unmodified reference CUDA rasterizer, same GPU, same %d frames" % n_frames}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -914,7 +1099,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--mode", default="render", choices=["render", "train", "hexplane"],
+    ap.add_argument("--mode", default="render", choices=["render", "train", "hexplane", "deform"],
                     help="render: forward sweep (headline, cfg2); train: fwd+bwd over a batch of 4 views (cfg3)")
     a = ap.parse_args()
     if not torch.cuda.is_available():
@@ -928,6 +1113,8 @@ def main():
     warmup = max(3, a.warmup)
     if a.mode == "hexplane":
         return main_hexplane(a, rank, world, local, warmup)
+    if a.mode == "deform":
+        return main_deform(a, rank, world, local, warmup)
     if a.mode == "train" or a.workload in ("cfg3",):
         return main_train(a, rank, world, local, warmup)
     wl = Workload(a.workload, rank, world)
