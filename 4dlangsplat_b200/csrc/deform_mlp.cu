@@ -1,5 +1,5 @@
 // deform_mlp.cu -- the MLP half of the deformation network (scene/deformation.py:45-182) on the 5th-generation tensor
-// cores: tcgen05.mma (kind::f16, bf16 x 3 operand split => fp32-grade products, see umma.cuh), accumulators in TMEM,
+// cores: tcgen05.mma (kind::f16, fp16 x 2 operand split => fp32-grade products, see umma.cuh), accumulators in TMEM,
 // activations never leave the SM between layers.
 //
 // Part 1 (this file, first): ONE linear layer Y = act(X W^T + b) as a stand-alone kernel -- the probe that pins the
@@ -14,22 +14,23 @@ using namespace umma;
 
 constexpr int DM_ROWS = 128;  // points per CTA tile = TMEM lanes = UMMA M
 
-// the six bf16 x bf16 terms of an fp32-grade product, smallest first: (part of A, part of B)
-__device__ constexpr int DM_TERMS[6][2] = {{2, 0}, {0, 2}, {1, 1}, {1, 0}, {0, 1}, {0, 0}};
+// the three fp16 x fp16 terms of an fp32-grade product, smallest first: (part of A, part of B)
+constexpr int DM_NTERMS = 3;
+__device__ constexpr int DM_TERMS[DM_NTERMS][2] = {{1, 0}, {0, 1}, {0, 0}};
 
 // Issue D[128 x N] (+)= A[128 x K] * B[N x K]^T over `ksteps` K=16 steps.  A, B: three parts each, `a_part` / `b_part`
 // bytes apart, canonical slabs (umma.cuh).  One thread.
 __device__ __forceinline__ void dm_issue_gemm(uint32_t tmem_d, uint32_t a_base, uint32_t a_part, uint32_t b_base,
                                               uint32_t b_part, int N, int ksteps, bool accumulate_first) {
-  const uint32_t idesc = instr_desc_bf16(DM_ROWS, N);
+  const uint32_t idesc = instr_desc_f16(DM_ROWS, N);
   const uint32_t a_slab = DM_ROWS * 16, b_slab = (uint32_t)N * 16;
   bool acc = accumulate_first;
   for (int ks = 0; ks < ksteps; ++ks) {
 #pragma unroll
-    for (int t = 0; t < 6; ++t) {
+    for (int t = 0; t < DM_NTERMS; ++t) {
       const uint64_t da = smem_desc(a_base + DM_TERMS[t][0] * a_part + ks * 2 * a_slab, a_slab, 128);
       const uint64_t db = smem_desc(b_base + DM_TERMS[t][1] * b_part + ks * 2 * b_slab, b_slab, 128);
-      mma_bf16(tmem_d, da, db, idesc, acc);
+      mma_f16(tmem_d, da, db, idesc, acc);
       acc = true;
     }
   }
@@ -43,10 +44,10 @@ umma_linear_kernel(int rows, int N, int K, const float* __restrict__ X, const fl
   __shared__ uint64_t s_bar;
   __shared__ uint32_t s_tmem;
   const int tid = threadIdx.x, warp = tid >> 5;
-  const uint32_t a_part = (uint32_t)(K / 8) * DM_ROWS * 16;  // bytes of one bf16 part of the activation tile
+  const uint32_t a_part = (uint32_t)(K / 8) * DM_ROWS * 16;  // bytes of one fp16 part of the activation tile
   const uint32_t b_part = (uint32_t)(K / 8) * N * 16;
   char* sA = reinterpret_cast<char*>(dm_smem);
-  char* sB = sA + 3 * a_part;
+  char* sB = sA + PARTS * a_part;
 
   if (warp == 0) tmem_alloc<128>(&s_tmem);
   if (tid == 0) {
@@ -64,7 +65,7 @@ umma_linear_kernel(int rows, int N, int K, const float* __restrict__ X, const fl
     float v[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) v[e] = W[(size_t)n * K + slab * 8 + e];
-    store_row8_bf3(sB + (size_t)slab * N * 16 + n * 16, b_part, v);
+    store_row8_split(sB + (size_t)slab * N * 16 + n * 16, b_part, v);
   }
   // activations: thread = row
   const int row = blockIdx.x * DM_ROWS + tid;
@@ -72,7 +73,7 @@ umma_linear_kernel(int rows, int N, int K, const float* __restrict__ X, const fl
     float v[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) v[e] = row < rows ? X[(size_t)row * K + slab * 8 + e] : 0.f;
-    store_row8_bf3(sA + (size_t)slab * DM_ROWS * 16 + tid * 16, a_part, v);
+    store_row8_split(sA + (size_t)slab * DM_ROWS * 16 + tid * 16, a_part, v);
   }
   fence_proxy_async();
   __syncthreads();
@@ -104,7 +105,7 @@ int umma_linear(int rows, int N, int K, const float* X, const float* W, const fl
                 cudaStream_t st) {
   if (rows < 0 || N < 8 || N > 128 || (N % 8) || K < 16 || K > 128 || (K % 16)) return FDLS_EINVAL;
   if (rows == 0) return FDLS_OK;
-  const size_t smem = (size_t)3 * (K / 8) * 16 * (DM_ROWS + N);
+  const size_t smem = (size_t)PARTS * (K / 8) * 16 * (DM_ROWS + N);
   static SmemOptIn optin;
   if (optin.ensure(umma_linear_kernel, smem) != cudaSuccess) return FDLS_ECUDA;
   count_launch();
@@ -117,7 +118,7 @@ int umma_linear(int rows, int N, int K, const float* X, const float* W, const fl
 // Part 2: the fused network.
 //
 // Per 128-point tile (thread = point = TMEM lane):
-//   X tile -> bf16x3 slabs (sX)                                   trunk GEMM  X W0^T          -> TMEM cols [0, W)
+//   X tile -> fp16x2 slabs (sX)                                   trunk GEMM  X W0^T          -> TMEM cols [0, W)
 //   for every head:  ReLU(trunk + b0) -> sA                       layer-1 GEMM sA W1^T        -> TMEM cols [W, 2W)
 //                    ReLU(hidden + b1) -> sA                      layer-2 GEMM sA W2^T        -> TMEM cols [2W, 2W + Npad)
 //                    act(base + out + b2) -> global
@@ -127,13 +128,13 @@ int umma_linear(int rows, int N, int K, const float* X, const float* W, const fl
 // round trip is longer than a chunk's MMAs), and slot (g+3) % 5 is free because chunk g-2's MMAs have completed
 // (mbarrier of its tcgen05.commit).  The input tile aliases the activation buffer.
 // ======================================================================================================================
-constexpr int DM_CHUNK_BYTES = 24576;
+constexpr int DM_CHUNK_BYTES = 16384;  // 4 slabs x 128 rows x 16 B x PARTS
 constexpr int DM_MAX_CHUNKS = 2 + FDLS_DEFORM_MAX_HEADS * (4 + 3);
 constexpr int DM_KIND_TRUNK = 0, DM_KIND_HIDDEN = 1, DM_KIND_OUT = 2;
 
 struct DmChunk {
   uint32_t off;     // byte offset of the chunk in the prepared buffer
-  uint32_t bytes;   // 3 parts x slabs x N x 16
+  uint32_t bytes;   // PARTS x slabs x N x 16
   uint16_t N;       // rows of the B operand (= output columns, padded)
   uint16_t slab0;   // first A slab (8 k each) this chunk multiplies
   uint16_t slabs;   // slabs in this chunk (even)
@@ -157,14 +158,14 @@ static int dm_make_plan(const FdlsDeformArgs* a, DmPlan* pl) {
   size_t off = 0;
   auto add = [&](int kind, int head, int N, int K) {
     const int total = K / 8;
-    int per = DM_CHUNK_BYTES / (N * 48);  // slabs per chunk
+    int per = DM_CHUNK_BYTES / (N * 16 * PARTS);  // slabs per chunk
     per &= ~1;
     if (per < 2) return false;
     for (int s0 = 0; s0 < total; s0 += per) {
       const int n = total - s0 < per ? total - s0 : per;
       DmChunk& c = pl->c[pl->n_chunks++];
       c.off = (uint32_t)off;
-      c.bytes = (uint32_t)(3 * n * N * 16);
+      c.bytes = (uint32_t)(PARTS * n * N * 16);
       c.N = (uint16_t)N; c.slab0 = (uint16_t)s0; c.slabs = (uint16_t)n;
       c.kind = (uint8_t)kind; c.head = (uint8_t)head;
       c.first = s0 == 0; c.last = s0 + n >= total;
@@ -198,7 +199,7 @@ deform_prep_kernel(const float* __restrict__ Wm, int N, int Npad, int K, char* _
   for (int c = 0; c < pl.n_chunks; ++c) {
     const DmChunk& ch = pl.c[c];
     if (ch.kind == kind && ch.head == head && slab >= ch.slab0 && slab < ch.slab0 + ch.slabs) {
-      store_row8_bf3(prep + ch.off + (size_t)(slab - ch.slab0) * Npad * 16 + n * 16, (size_t)ch.slabs * Npad * 16, v);
+      store_row8_split(prep + ch.off + (size_t)(slab - ch.slab0) * Npad * 16 + n * 16, (size_t)ch.slabs * Npad * 16, v);
       return;
     }
   }
@@ -214,8 +215,9 @@ struct DmDev {
   DmHeadDev head[FDLS_DEFORM_MAX_HEADS];
 };
 
-constexpr int DM_THREADS = 256;  // two threads per point in the epilogues (columns split in halves); thread 0 issues MMAs
-constexpr int DM_SLOTS = 5;      // weight-chunk ring: chunk g+3 is copied while chunk g multiplies
+constexpr int DM_EPI_THREADS = 512;                 // 16 epilogue warps: four threads per point, W/4 columns each
+constexpr int DM_THREADS = DM_EPI_THREADS + 32;     // + one producer warp: weight copies and MMA issue
+constexpr int DM_SLOTS = 5;                         // weight-chunk ring: chunk g+3 is copied while chunk g multiplies
 constexpr int DM_AHEAD = 3;
 
 template <int N>
@@ -226,11 +228,11 @@ __device__ __forceinline__ void dm_cp_async_wait() {
 // like dm_issue_gemm, with the descriptors advanced by adding to their address field (3 instructions per MMA)
 __device__ __forceinline__ void dm_issue_chunk(uint32_t tmem_d, uint32_t a_base, uint32_t a_part, uint32_t b_base,
                                                uint32_t b_part, int N, int ksteps, bool accumulate_first) {
-  const uint32_t idesc = instr_desc_bf16(DM_ROWS, N);
+  const uint32_t idesc = instr_desc_f16(DM_ROWS, N);
   const uint32_t a_slab = DM_ROWS * 16, b_slab = (uint32_t)N * 16;
-  uint64_t da[3], db[3];
+  uint64_t da[PARTS], db[PARTS];
 #pragma unroll
-  for (int p = 0; p < 3; ++p) {
+  for (int p = 0; p < PARTS; ++p) {
     da[p] = smem_desc(a_base + p * a_part, a_slab, 128);
     db[p] = smem_desc(b_base + p * b_part, b_slab, 128);
   }
@@ -238,36 +240,43 @@ __device__ __forceinline__ void dm_issue_chunk(uint32_t tmem_d, uint32_t a_base,
   bool acc = accumulate_first;
   for (int ks = 0; ks < ksteps; ++ks) {
 #pragma unroll
-    for (int t = 0; t < 6; ++t) {
-      mma_bf16(tmem_d, da[DM_TERMS[t][0]], db[DM_TERMS[t][1]], idesc, acc);
+    for (int t = 0; t < DM_NTERMS; ++t) {
+      mma_f16(tmem_d, da[DM_TERMS[t][0]], db[DM_TERMS[t][1]], idesc, acc);
       acc = true;
     }
 #pragma unroll
-    for (int p = 0; p < 3; ++p) {
+    for (int p = 0; p < PARTS; ++p) {
       da[p] += a_inc;
       db[p] += b_inc;
     }
   }
 }
 
+// Warp-specialised: the PRODUCER warp streams the weight chunks (cp.async ring) and issues every MMA as soon as its
+// operands exist; the 16 EPILOGUE warps turn accumulators into the next GEMM's A operand (or the outputs).  They meet
+// only at GEMM boundaries, through two mbarriers that flip once per GEMM:
+//   a_ready   (512 arrivals): the A operand of GEMM q is in shared memory          epilogue -> producer
+//   acc_ready (tcgen05.commit): the accumulator of GEMM q is complete, and sA free  producer -> epilogue
+// so a chunk costs the producer no CTA-wide barrier, and copies / MMA issue run ahead of the epilogues.
 __global__ void __launch_bounds__(DM_THREADS, 1)
 deform_mlp_kernel(DmDev a, DmPlan pl) {
   extern __shared__ __align__(128) unsigned char dm_smem[];
-  __shared__ uint64_t s_bar[DM_SLOTS];
+  __shared__ uint64_t s_done[DM_SLOTS];  // MMAs of the chunk in ring slot s have completed
+  __shared__ uint64_t s_acc_ready, s_a_ready;
   __shared__ uint32_t s_tmem;
   __shared__ float s_bias[(1 + FDLS_DEFORM_MAX_HEADS) * 128];  // b0, then b1 of every head
-  const int tid = threadIdx.x, warp = tid >> 5;
-  const int prow = tid & (DM_ROWS - 1);  // point of the tile this thread works on = TMEM lane
-  const int half = tid >> 7;             // which half of the columns / slabs it takes in the epilogues
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int W = a.W, G = a.G;
   const uint32_t x_part = (uint32_t)(G / 8) * DM_ROWS * 16, a_part = (uint32_t)(W / 8) * DM_ROWS * 16;
   char* sA = reinterpret_cast<char*>(dm_smem);
   char* sX = sA;  // the input tile is dead once the trunk GEMM has completed, which is when sA is first written
-  char* sW = sA + 3 * a_part;  // DM_SLOTS ring slots of DM_CHUNK_BYTES
+  char* sW = sA + PARTS * a_part;  // DM_SLOTS ring slots of DM_CHUNK_BYTES
 
   if (warp == 0) tmem_alloc<512>(&s_tmem);
   if (tid == 0) {
-    for (int i = 0; i < DM_SLOTS; ++i) mbar_init(&s_bar[i], 1);
+    for (int i = 0; i < DM_SLOTS; ++i) mbar_init(&s_done[i], 1);
+    mbar_init(&s_acc_ready, 1);
+    mbar_init(&s_a_ready, DM_EPI_THREADS);
     fence_mbar_init();
   }
   for (int i = tid; i < W; i += DM_THREADS) s_bias[i] = a.b0[i];
@@ -277,127 +286,154 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem = s_tmem;
-  const uint32_t lane_field = (uint32_t)((warp & 3) * 32) << 16;  // a warp reads the TMEM lane quadrant warp % 4
 
   const int n_tiles = (a.P + DM_ROWS - 1) / DM_ROWS;
   const int my_tiles = blockIdx.x < n_tiles ? (n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
   const long long total_steps = (long long)my_tiles * pl.n_chunks;
-  long long g = 0;  // chunks consumed so far by this CTA
 
-  auto copy_chunk = [&](long long step) {  // all threads; the caller commits the cp.async group
-    if (step >= total_steps) return;
-    const DmChunk& ch = pl.c[step % pl.n_chunks];
-    const char* src = a.prep + ch.off;
-    char* dst = sW + (size_t)(step % DM_SLOTS) * DM_CHUNK_BYTES;
-    for (uint32_t o = tid * 16; o < ch.bytes; o += DM_THREADS * 16) {
-      const uint32_t d = smem_u32(dst + o);
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src + o) : "memory");
+  if (warp == DM_EPI_THREADS / 32) {
+    // =================================================== PRODUCER ===================================================
+    auto copy_chunk = [&](long long step) {  // 32 lanes; the caller commits the cp.async group
+      if (step >= total_steps) return;
+      const DmChunk& ch = pl.c[step % pl.n_chunks];
+      const char* src = a.prep + ch.off;
+      char* dst = sW + (size_t)(step % DM_SLOTS) * DM_CHUNK_BYTES;
+      for (uint32_t o = lane * 16; o < ch.bytes; o += 32 * 16) {
+        const uint32_t d = smem_u32(dst + o);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src + o) : "memory");
+      }
+    };
+    for (int i = 0; i < DM_AHEAD; ++i) {  // prime the ring: chunks 0 .. DM_AHEAD-1, one group each
+      copy_chunk(i);
+      asm volatile("cp.async.commit_group;" ::: "memory");
     }
-  };
-  auto wait_mma = [&](long long step) {  // the MMAs of chunk `step` (the latest use of its slot) have completed
-    mbar_wait(&s_bar[step % DM_SLOTS], (uint32_t)((step / DM_SLOTS) & 1));
-    tc_fence_after_sync();
-  };
-  // one chunk: keep the ring full, then issue this chunk's MMAs
-  auto step = [&](int c, uint32_t a_base, uint32_t a_prt, uint32_t d_col) {
-    if (g >= 2) wait_mma(g - 2);  // slot (g + DM_AHEAD) % DM_SLOTS == (g - 2) % DM_SLOTS is free
-    copy_chunk(g + DM_AHEAD);
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    dm_cp_async_wait<DM_AHEAD>();  // chunk g has landed (the DM_AHEAD younger groups may still be in flight)
-    fence_proxy_async();
-    tc_fence_before_sync();
-    __syncthreads();
-    if (tid == 0) {
+    long long g = 0;    // chunks issued so far
+    uint32_t gemm = 0;  // GEMMs started so far
+    for (int t = 0; t < my_tiles; ++t) {
+      for (int c = 0; c < pl.n_chunks; ++c, ++g) {
+        const DmChunk& ch = pl.c[c];
+        // refill the ring: slot (g + AHEAD) % SLOTS == (g - 2) % SLOTS is free once chunk g-2's MMAs are complete
+        if (g >= DM_SLOTS - DM_AHEAD) mbar_wait(&s_done[(g + DM_AHEAD) % DM_SLOTS],
+                                                (uint32_t)(((g + DM_AHEAD - DM_SLOTS) / DM_SLOTS) & 1));
+        copy_chunk(g + DM_AHEAD);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        dm_cp_async_wait<DM_AHEAD>();  // chunk g has landed (this lane's pieces)
+        fence_proxy_async();
+        if (ch.first) {  // this GEMM's A operand: written by the epilogue warps (fenced by them before arriving)
+          mbar_wait(&s_a_ready, gemm & 1);
+          ++gemm;
+        }
+        __syncwarp();
+        if (lane == 0) {
+          tc_fence_after_sync();
+          const uint32_t a_base = ch.kind == DM_KIND_TRUNK ? smem_u32(sX) : smem_u32(sA);
+          const uint32_t a_prt = ch.kind == DM_KIND_TRUNK ? x_part : a_part;
+          const uint32_t d_col = ch.kind == DM_KIND_TRUNK ? 0u : ch.kind == DM_KIND_HIDDEN ? (uint32_t)W : (uint32_t)(2 * W);
+          const uint32_t b_base = smem_u32(sW + (size_t)(g % DM_SLOTS) * DM_CHUNK_BYTES);
+          dm_issue_chunk(tmem + d_col, a_base + (uint32_t)ch.slab0 * DM_ROWS * 16, a_prt, b_base,
+                         (uint32_t)ch.slabs * ch.N * 16, ch.N, ch.slabs / 2, !ch.first);
+          mma_commit(&s_done[g % DM_SLOTS]);
+          if (ch.last) mma_commit(&s_acc_ready);
+        }
+        __syncwarp();
+      }
+    }
+    dm_cp_async_wait<0>();
+  } else {
+    // =================================================== EPILOGUE ===================================================
+    const int prow = tid & (DM_ROWS - 1);  // point of the tile = TMEM lane
+    const int quarter = tid >> 7;          // which quarter of the columns / slabs this thread takes
+    const uint32_t lane_field = (uint32_t)((warp & 3) * 32) << 16;  // a warp reads the TMEM lane quadrant warp % 4
+    uint32_t gemm = 0;  // accumulators consumed so far
+    auto operand_ready = [&]() {  // my part of the next GEMM's A operand is written
+      fence_proxy_async();
+      mbar_arrive(&s_a_ready);
+    };
+    auto wait_acc = [&]() {
+      mbar_wait(&s_acc_ready, gemm & 1);
+      ++gemm;
       tc_fence_after_sync();
-      const DmChunk& ch = pl.c[c];
-      const uint32_t b_base = smem_u32(sW + (size_t)(g % DM_SLOTS) * DM_CHUNK_BYTES);
-      const uint32_t b_part = (uint32_t)ch.slabs * ch.N * 16;
-      dm_issue_chunk(tmem + d_col, a_base + (uint32_t)ch.slab0 * DM_ROWS * 16, a_prt, b_base, b_part, ch.N,
-                     ch.slabs / 2, !ch.first);
-      mma_commit(&s_bar[g % DM_SLOTS]);
-    }
-    ++g;
-  };
-  // TMEM columns [col, col + W) + bias, ReLU -> sA (the next GEMM's A operand); this thread: W/2 columns of its point
-  auto relu_to_A = [&](uint32_t col, const float* __restrict__ bias) {
-    const int c0 = half * (W / 2);
-    for (int c = c0; c < c0 + W / 2; c += 32) {
-      float v[32];
-      tmem_ld32(tmem + lane_field + col + c, v);
+    };
+    // TMEM columns [col, col + W) + bias, ReLU -> sA; this thread: W/4 columns of its point
+    auto relu_to_A = [&](uint32_t col, const float* __restrict__ bias) {
+      const int c0 = quarter * (W / 4);
+      if (W == 128) {
+        float v[32];
+        tmem_ld32(tmem + lane_field + col + c0, v);
 #pragma unroll
-      for (int sl = 0; sl < 4; ++sl) {
-        float w8[8];
+        for (int sl = 0; sl < 4; ++sl) {
+          float w8[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) w8[e] = fmaxf(v[sl * 8 + e] + bias[c + sl * 8 + e], 0.f);
-        store_row8_bf3(sA + (size_t)(c / 8 + sl) * DM_ROWS * 16 + prow * 16, a_part, w8);
-      }
-    }
-  };
-  auto write_out = [&](int h, int row) {  // warps 0-3 only
-    const DmHeadDev& hd = a.head[h];
-    float y[48];
-    for (int c = 0; c < hd.npad; c += 8) {
-      float v[8];
-      tmem_ld8(tmem + lane_field + 2 * W + c, v);
-#pragma unroll
-      for (int e = 0; e < 8; ++e) y[c + e] = v[e];
-    }
-    if (row >= a.P) return;
-    float nrm = 0.f;
-    for (int e = 0; e < hd.k; ++e) {
-      float t = y[e] + __ldg(hd.b2 + e);
-      if (hd.base) t = hd.base[(size_t)row * hd.k + e] + t;
-      if (hd.act == FDLS_DEFORM_ACT_EXP) t = expf(t);
-      else if (hd.act == FDLS_DEFORM_ACT_SIGMOID) t = 1.f / (1.f + expf(-t));
-      y[e] = t;
-      nrm += t * t;
-    }
-    if (hd.act == FDLS_DEFORM_ACT_NORMALIZE) {
-      const float inv = 1.f / fmaxf(sqrtf(nrm), 1e-12f);
-      for (int e = 0; e < hd.k; ++e) y[e] *= inv;
-    }
-    for (int e = 0; e < hd.k; ++e) hd.out[(size_t)row * hd.k + e] = y[e];
-  };
-
-  for (int i = 0; i < DM_AHEAD; ++i) {  // prime the ring: chunks 0 .. DM_AHEAD-1, one group each
-    copy_chunk(i);
-    asm volatile("cp.async.commit_group;" ::: "memory");
-  }
-
-  for (int t = 0; t < my_tiles; ++t) {
-    const int row = ((int)blockIdx.x + t * (int)gridDim.x) * DM_ROWS + prow;
-    // ---- X tile (aliases sA): every MMA that read sA for the previous tile has completed (wait_mma before write_out)
-    for (int slab = half; slab < G / 8; slab += 2) {
-      float v[8];
-      if (row < a.P) {
-        const float4 p = *reinterpret_cast<const float4*>(a.feat + (size_t)row * G + slab * 8);
-        const float4 q = *reinterpret_cast<const float4*>(a.feat + (size_t)row * G + slab * 8 + 4);
-        v[0] = p.x; v[1] = p.y; v[2] = p.z; v[3] = p.w; v[4] = q.x; v[5] = q.y; v[6] = q.z; v[7] = q.w;
+          for (int e = 0; e < 8; ++e) w8[e] = fmaxf(v[sl * 8 + e] + bias[c0 + sl * 8 + e], 0.f);
+          store_row8_split(sA + (size_t)(c0 / 8 + sl) * DM_ROWS * 16 + prow * 16, a_part, w8);
+        }
       } else {
+        for (int c = c0; c < c0 + W / 4; c += 8) {
+          float v[8];
+          tmem_ld8(tmem + lane_field + col + c, v);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) v[e] = 0.f;
+          for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e] + bias[c + e], 0.f);
+          store_row8_split(sA + (size_t)(c / 8) * DM_ROWS * 16 + prow * 16, a_part, v);
+        }
       }
-      store_row8_bf3(sX + (size_t)slab * DM_ROWS * 16 + prow * 16, x_part, v);
+      tc_fence_before_sync();
+    };
+    auto write_out = [&](int h, int row) {  // warps 0-3 only (quarter 0)
+      const DmHeadDev& hd = a.head[h];
+      float y[48];
+      for (int c = 0; c < hd.npad; c += 8) {
+        float v[8];
+        tmem_ld8(tmem + lane_field + 2 * W + c, v);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) y[c + e] = v[e];
+      }
+      tc_fence_before_sync();
+      if (row >= a.P) return;
+      float nrm = 0.f;
+      for (int e = 0; e < hd.k; ++e) {
+        float t = y[e] + __ldg(hd.b2 + e);
+        if (hd.base) t = hd.base[(size_t)row * hd.k + e] + t;
+        if (hd.act == FDLS_DEFORM_ACT_EXP) t = expf(t);
+        else if (hd.act == FDLS_DEFORM_ACT_SIGMOID) t = 1.f / (1.f + expf(-t));
+        y[e] = t;
+        nrm += t * t;
+      }
+      if (hd.act == FDLS_DEFORM_ACT_NORMALIZE) {
+        const float inv = 1.f / fmaxf(sqrtf(nrm), 1e-12f);
+        for (int e = 0; e < hd.k; ++e) y[e] *= inv;
+      }
+      for (int e = 0; e < hd.k; ++e) hd.out[(size_t)row * hd.k + e] = y[e];
+    };
+
+    for (int t = 0; t < my_tiles; ++t) {
+      const int row = ((int)blockIdx.x + t * (int)gridDim.x) * DM_ROWS + prow;
+      // ---- X tile (aliases sA): every MMA that read sA for the previous tile has completed (last wait_acc below)
+      for (int slab = quarter; slab < G / 8; slab += 4) {
+        float v[8];
+        if (row < a.P) {
+          const float4 p = *reinterpret_cast<const float4*>(a.feat + (size_t)row * G + slab * 8);
+          const float4 q = *reinterpret_cast<const float4*>(a.feat + (size_t)row * G + slab * 8 + 4);
+          v[0] = p.x; v[1] = p.y; v[2] = p.z; v[3] = p.w; v[4] = q.x; v[5] = q.y; v[6] = q.z; v[7] = q.w;
+        } else {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[e] = 0.f;
+        }
+        store_row8_split(sX + (size_t)slab * DM_ROWS * 16 + prow * 16, x_part, v);
+      }
+      operand_ready();  // trunk GEMM may start
+      for (int h = 0; h < a.H; ++h) {
+        wait_acc();  // trunk (h = 0) or the previous head's layer 2: its accumulator is complete and sA is free
+        relu_to_A(0, s_bias);
+        operand_ready();  // layer 1 of head h
+        if (h > 0 && quarter == 0) write_out(h - 1, row);  // overlaps the layer-1 MMAs
+        wait_acc();  // layer 1
+        relu_to_A((uint32_t)W, s_bias + (1 + h) * 128);
+        operand_ready();  // layer 2 of head h
+      }
+      wait_acc();  // layer 2 of the last head
+      if (quarter == 0) write_out(a.H - 1, row);
     }
-    int c = 0;
-    for (; c < pl.n_chunks && pl.c[c].kind == DM_KIND_TRUNK; ++c) step(c, smem_u32(sX), x_part, 0);
-    for (int h = 0; h < a.H; ++h) {
-      wait_mma(g - 1);  // trunk (h = 0) or the previous head's layer 2: sA is free, its accumulator complete
-      if (h > 0 && half == 0) write_out(h - 1, row);
-      relu_to_A(0, s_bias);
-      for (; c < pl.n_chunks && pl.c[c].kind == DM_KIND_HIDDEN && pl.c[c].head == h; ++c)
-        step(c, smem_u32(sA), a_part, (uint32_t)W);
-      wait_mma(g - 1);
-      relu_to_A((uint32_t)W, s_bias + (1 + h) * 128);
-      for (; c < pl.n_chunks && pl.c[c].kind == DM_KIND_OUT && pl.c[c].head == h; ++c)
-        step(c, smem_u32(sA), a_part, (uint32_t)(2 * W));
-    }
-    wait_mma(g - 1);
-    if (half == 0) write_out(a.H - 1, row);
-    tc_fence_before_sync();
-    __syncthreads();  // the next tile's X store may not overtake another warp's write_out ... of TMEM? no: of nothing
   }
-  dm_cp_async_wait<0>();
   tc_fence_before_sync();
   __syncthreads();
   if (warp == 0) tmem_dealloc<512>(tmem);
@@ -405,7 +441,7 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
 
 static size_t dm_smem_bytes(int G, int W) {
   const int K = G > W ? G : W;  // the input tile aliases the activation buffer
-  return (size_t)3 * (K / 8) * DM_ROWS * 16 + (size_t)DM_SLOTS * DM_CHUNK_BYTES;
+  return (size_t)PARTS * (K / 8) * DM_ROWS * 16 + (size_t)DM_SLOTS * DM_CHUNK_BYTES;
 }
 
 size_t deform_prep_bytes(const FdlsDeformArgs* a) {

@@ -1,18 +1,21 @@
-// umma.cuh -- the few tcgen05 / TMEM / mbarrier PTX wrappers the deformation MLP needs (sm_100a), and the bf16x3
+// umma.cuh -- the few tcgen05 / TMEM / mbarrier PTX wrappers the deformation MLP needs (sm_100a), and the fp16x2
 // operand format that gives fp32-grade products on the 5th-generation tensor cores.
 //
 // Operand layout ("canonical K-major, no swizzle", the INTERLEAVE form of the UMMA shared-memory descriptor): a
 // matrix of R rows x K columns of 16-bit elements is stored as K/8 SLABS; a slab holds 8 consecutive k of every row,
-// row r at byte r*16 (16 bytes = 8 bf16), so a slab is R*16 bytes and consecutive 8-row groups ("core matrices",
+// row r at byte r*16 (16 bytes = 8 halves), so a slab is R*16 bytes and consecutive 8-row groups ("core matrices",
 // 8 rows x 16 bytes = 128 bytes) follow each other at SBO = 128 bytes; the next slab (the next 8 k) starts LBO = R*16
 // bytes later.  One tcgen05.mma.kind::f16 consumes K = 16 = two slabs.
 //
-// fp32 from bf16: x = b1 + b2 + b3 with three bf16 (8 + 8 + 8 significant bits, each the round-to-nearest of what
-// is left), and a product a*b is taken as the six terms a1b1 + a1b2 + a2b1 + a2b2 + a1b3 + a3b1 accumulated in
-// fp32 inside the tensor core: everything dropped is below 2^-24 of |a||b|.
+// fp32 from fp16: x = h1 + h2 with two halves (11 + 11 significant bits, each the round-to-nearest of what is left;
+// |x - h1 - h2| <= 2^-22 |x| + 2^-25, the second term being fp16's subnormal spacing), and a product a*b is taken
+// as the three terms a1b2 + a2b1 + a1b1 accumulated in fp32 inside the tensor core: what is dropped (a2b2) is below
+// 2^-22 |a||b|.  Half the MMAs and two thirds of the shared memory of a bf16 x 3 split of the same accuracy class
+// (measured first: 0.65 ms per 300k points with six bf16 terms, tensor pipe 57 % busy).  Range: |x| < 65504 -- the
+// conversions saturate instead of producing inf; network activations and weights are O(1).
 #pragma once
 #include <cstdint>
-#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
 namespace fdls {
@@ -41,6 +44,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (done) return;
     if (spins > (1u << 24)) __trap();  // an MMA that never completes must fail loudly, not hang the GPU
   }
+}
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
 // ---- proxies and tcgen05 fences -------------------------------------------------------------------------------------
@@ -100,13 +107,13 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
   d |= (uint64_t)1 << 46;
   return d;
 }
-// instruction descriptor for kind::f16, bf16 x bf16 -> fp32, both operands K-major (InstrDescriptor, same header):
-//   [4,6) D format 1 = f32 | [7,10) A format 1 = bf16 | [10,13) B format 1 = bf16 | [17,23) N >> 3 | [24,29) M >> 4
-__host__ __device__ constexpr uint32_t instr_desc_bf16(int M, int N) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+// instruction descriptor for kind::f16, fp16 x fp16 -> fp32, both operands K-major (InstrDescriptor, same header):
+//   [4,6) D format 1 = f32 | [7,10) A format 0 = f16 | [10,13) B format 0 = f16 | [17,23) N >> 3 | [24,29) M >> 4
+__host__ __device__ constexpr uint32_t instr_desc_f16(int M, int N) {
+  return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 // D[tmem] (+)= A[smem] * B[smem]^T, issued by ONE thread
-__device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, bool accumulate) {
+__device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, bool accumulate) {
   const uint32_t acc = accumulate ? 1u : 0u;
   asm volatile(
       "{\n\t"
@@ -122,30 +129,26 @@ __device__ __forceinline__ void mma_commit(uint64_t* bar) {
                : "memory");
 }
 
-// ---- bf16 x 3 ---------------------------------------------------------------------------------------------------------
-struct Bf3 {
-  uint16_t a, b, c;
-};
-__device__ __forceinline__ Bf3 split_bf3(float x) {
-  const __nv_bfloat16 h1 = __float2bfloat16_rn(x);
-  const float r1 = x - __bfloat162float(h1);
-  const __nv_bfloat16 h2 = __float2bfloat16_rn(r1);
-  const float r2 = r1 - __bfloat162float(h2);
-  const __nv_bfloat16 h3 = __float2bfloat16_rn(r2);
-  return {__bfloat16_as_ushort(h1), __bfloat16_as_ushort(h2), __bfloat16_as_ushort(h3)};
+// ---- fp16 x 2 ---------------------------------------------------------------------------------------------------------
+constexpr int PARTS = 2;
+// two floats -> their packed high halves (low 16 bits = x0) and packed remainders
+__device__ __forceinline__ void split_h2(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+  uint16_t a0, a1, b0, b1;
+  asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(a0) : "f"(x0));
+  asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(a1) : "f"(x1));
+  const float r0 = x0 - __half2float(__ushort_as_half(a0)), r1 = x1 - __half2float(__ushort_as_half(a1));
+  asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(b0) : "f"(r0));
+  asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(b1) : "f"(r1));
+  hi = (uint32_t)a0 | ((uint32_t)a1 << 16);
+  lo = (uint32_t)b0 | ((uint32_t)b1 << 16);
 }
 // split 8 consecutive k of one row and store them as one 16-byte piece per part: part p at dst + p * part_bytes
-__device__ __forceinline__ void store_row8_bf3(char* dst, size_t part_bytes, const float (&v)[8]) {
-  uint32_t w[3][4];
+__device__ __forceinline__ void store_row8_split(char* dst, size_t part_bytes, const float (&v)[8]) {
+  uint32_t w[2][4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const Bf3 lo = split_bf3(v[2 * i]), hi = split_bf3(v[2 * i + 1]);
-    w[0][i] = (uint32_t)lo.a | ((uint32_t)hi.a << 16);
-    w[1][i] = (uint32_t)lo.b | ((uint32_t)hi.b << 16);
-    w[2][i] = (uint32_t)lo.c | ((uint32_t)hi.c << 16);
-  }
+  for (int i = 0; i < 4; ++i) split_h2(v[2 * i], v[2 * i + 1], w[0][i], w[1][i]);
 #pragma unroll
-  for (int p = 0; p < 3; ++p)
+  for (int p = 0; p < 2; ++p)
     *reinterpret_cast<uint4*>(dst + p * part_bytes) = make_uint4(w[p][0], w[p][1], w[p][2], w[p][3]);
 }
 

@@ -5,7 +5,7 @@ checkpoint's state_dict loads), same forward signatures and return tuples.  SURV
 What runs underneath:
   * the HexPlane feature field is 4dlangsplat_b200.hexplane.HexPlaneField (one fused CUDA kernel per direction);
   * under torch.no_grad() (render.py's sweeps) the trunk + every active head is ONE persistent tcgen05 kernel
-    (csrc/deform_mlp.cu, include/fdls_abi.h fdls_deform_forward): bf16 x 3 operand splits give fp32-grade GEMMs on
+    (csrc/deform_mlp.cu, include/fdls_abi.h fdls_deform_forward): fp16 x 2 operand splits give fp32-grade GEMMs on
     the tensor cores, accumulators live in TMEM, activations stay on the SM between layers, and optionally the
     activations gaussian_renderer/__init__.py:191-193 applies afterwards (exp / normalize / sigmoid) are folded in;
   * with grad enabled the layers run as the reference's own op sequence (F.linear -> cuBLAS, plain library GEMMs)
@@ -178,7 +178,7 @@ class Deformation(nn.Module):
             a.prep, a.prep_bytes = prep.data_ptr(), prep.numel()
 
     def _prepared(self, heads, dev, stream):
-        """bf16 x 3 operand chunks of every weight matrix, rebuilt when a parameter changed (version counters)."""
+        """fp16 x 2 operand chunks of every weight matrix, rebuilt when a parameter changed (version counters)."""
         mats = [self.feature_out[0].weight] + [w for n, _, _ in heads for w in (getattr(self, n)[1].weight,
                                                                                getattr(self, n)[3].weight)]
         key = tuple((m.data_ptr(), m._version) for m in mats) + (tuple(n for n, _, _ in heads),)

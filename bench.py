@@ -1047,7 +1047,7 @@ def main_deform(a, rank, world, local, warmup):
                                    "net_width 128, heads pos/scales/rotations), then rendered at %dx%d with %d language "
                                    "channels" % (P, FRAMES_PER_STEP, s.W, s.H, s.F),
                        "l2": "per frame 58 MB of features + 19 MB of records + the images stream through HBM; weights "
-                             "(0.7 MB as bf16x3 chunks) and planes (30 MB) are L2-resident by design"},
+                             "(0.7 MB as fp16x2 chunks) and planes (30 MB) are L2-resident by design"},
             "clocks": clocks,
             "e2e": {"value": round(n_frames * world / e2e_s, 2), "unit": "frames/s", "h2d_bytes_per_step": 4 * FRAMES_PER_STEP,
                     "d2h_bytes_per_step": sum(h.numel() * 4 for h in outs_host) * FRAMES_PER_STEP},
@@ -1076,9 +1076,9 @@ def main_deform(a, rank, world, local, warmup):
         line["roofline"] = {"bound": "tensor", "kernel": "deform_mlp_kernel", "achieved": round(ach, 1), "peak": peak,
                             "unit": "TFLOP/s", "frac": round(ach / peak, 4), "traffic": None, "peak_source": pk_kind,
                             "algorithmic_flops_per_launch": int(flops), "avg_launch_ms": round(mlp_ms, 4),
-                            "note": "algorithmic fp32 FLOPs of the network; the tensor cores execute 6 bf16 products per "
-                                    "fp32 product (bf16x3 split) plus head padding to N = 16, i.e. %.1f TFLOP/s of bf16 "
-                                    "work" % (6 * ach * (G_ * W_ + 3 * W_ * W_ + 3 * W_ * 16) / (G_ * W_ + 3 * W_ * W_ + W_ * 10))}
+                            "note": "algorithmic fp32 FLOPs of the network; the tensor cores execute 3 fp16 products per "
+                                    "fp32 product (fp16x2 split) plus head padding to N = 16, i.e. %.1f TFLOP/s of fp16 "
+                                    "work" % (3 * ach * (G_ * W_ + 3 * W_ * W_ + 3 * W_ * 16) / (G_ * W_ + 3 * W_ * W_ + W_ * 10))}
     else:
         line["impl"] = "reference"
         line["cpu_baseline"] = {"value": line["value"], "unit": "frames/s", "cores": 1, "kind": "port",

@@ -268,7 +268,7 @@ int fdls_hexplane_unpack_grad_batch(int32_t n, int32_t C, const int64_t* HW, con
 
 /* ---- SURVEY 8f N1, second step: the MLP half of the deformation network on the tcgen05 tensor cores -------------
  * Y[rows x N] = act(X[rows x K] W[N x K]^T + bias), fp32 in and out, W in torch's nn.Linear layout (out, in).
- * The product runs as bf16 x 3 operand splits (six tcgen05.mma.kind::f16 terms, fp32 accumulation in TMEM), which
+ * The product runs as fp16 x 2 operand splits (three tcgen05.mma.kind::f16 terms, fp32 accumulation in TMEM), which
  * reproduces the fp32 result to ~1e-7 relative.  K % 16 == 0, N % 8 == 0, both <= 128.  The building block of
  * fdls_deform_forward; exported so that the descriptor conventions are pinned by a test of their own. */
 int fdls_umma_linear(int32_t rows, int32_t N, int32_t K, const float* X, const float* W, const float* bias, float* Y,
@@ -281,7 +281,7 @@ int fdls_umma_linear(int32_t rows, int32_t N, int32_t K, const float* X, const f
  *     out_h  = act_h(base_h + delta_h)                          base = the canonical attribute      (:118-147)
  * for up to FDLS_DEFORM_MAX_HEADS heads (pos / scales / rotations / opacity / shs / discrete-coefficient heads; which
  * ones exist is the caller's choice: the reference switches them with no_dx, no_ds, no_dr, no_do, no_dshs).
- * One persistent kernel: 128 points per CTA tile, every GEMM on tcgen05 (bf16 x 3), accumulators in TMEM, activations
+ * One persistent kernel: 128 points per CTA tile, every GEMM on tcgen05 (fp16 x 2), accumulators in TMEM, activations
  * kept in shared memory between layers; the weights stream from L2 as pre-split operand chunks (fdls_deform_prepare,
  * once per parameter update).  G % 16 == 0, G <= 128, W in {64, 128}, k_h <= 48. */
 #define FDLS_DEFORM_MAX_HEADS 6
@@ -309,7 +309,7 @@ typedef struct FdlsDeformArgs {
   size_t prep_bytes;
 } FdlsDeformArgs;
 size_t fdls_deform_prep_bytes(const FdlsDeformArgs* a);
-/* split every weight matrix into bf16 x 3 operand chunks (reads w0, w1, w2 of every head; P, feat, base, out unused) */
+/* split every weight matrix into fp16 x 2 operand chunks (reads w0, w1, w2 of every head; P, feat, base, out unused) */
 int fdls_deform_prepare(const FdlsDeformArgs* a, void* stream);
 /* reads feat, biases, base and `prep`; writes out of every head */
 int fdls_deform_forward(const FdlsDeformArgs* a, void* stream);
