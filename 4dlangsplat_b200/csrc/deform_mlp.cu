@@ -120,11 +120,11 @@ int umma_linear(int rows, int N, int K, const float* X, const float* W, const fl
 // Per 128-point tile (thread = point = TMEM lane):
 //   X tile -> fp16x2 slabs (sX)                                   trunk GEMM  X W0^T          -> TMEM cols [0, W)
 //   for every head:  ReLU(trunk + b0) -> sA                       layer-1 GEMM sA W1^T        -> TMEM cols [W, 2W)
-//                    ReLU(hidden + b1) -> sA                      layer-2 GEMM sA W2^T        -> TMEM cols [2W, 2W + Npad)
+//                    ReLU(hidden + b1) -> sA                      layer-2 GEMM sA W2^T        -> TMEM cols [W, W + Npad)
 //                    act(base + out + b2) -> global
 // The trunk accumulator stays in TMEM for the whole tile and is re-read per head (shared memory holds ONE activation
 // buffer: 3 parts x 32 KB at W = 128).  Weights arrive as a fixed cyclic sequence of <= 24 KB operand chunks through a
-// five-slot cp.async ring: while the tensor core works on chunk g the copies of chunks g+1 .. g+3 are in flight (an L2
+// five-slot TMA ring (cp.async.bulk): while the tensor core works on chunk g the copies of chunks g+1 .. g+3 are in flight (an L2
 // round trip is longer than a chunk's MMAs), and slot (g+3) % 5 is free because chunk g-2's MMAs have completed
 // (mbarrier of its tcgen05.commit).  The input tile aliases the activation buffer.
 // ======================================================================================================================
@@ -215,10 +215,12 @@ struct DmDev {
   DmHeadDev head[FDLS_DEFORM_MAX_HEADS];
 };
 
-constexpr int DM_EPI_THREADS = 512;                 // 16 epilogue warps: four threads per point, W/4 columns each
-constexpr int DM_THREADS = DM_EPI_THREADS + 32;     // + one producer warp: weight copies and MMA issue
-constexpr int DM_SLOTS = 5;                         // weight-chunk ring: chunk g+3 is copied while chunk g multiplies
+constexpr int DM_GROUP_THREADS = 256;                      // one epilogue group: two threads per point, W/2 columns each
+constexpr int DM_EPI_THREADS = 2 * DM_GROUP_THREADS;       // two groups = two tiles in flight per CTA
+constexpr int DM_THREADS = DM_EPI_THREADS + 32;            // + one producer warp: weight copies and MMA issue
+constexpr int DM_SLOTS = 5;                                // weight-chunk ring: chunk g+3 is copied while chunk g multiplies
 constexpr int DM_AHEAD = 3;
+constexpr int DM_MAX_GEMMS = 1 + 2 * FDLS_DEFORM_MAX_HEADS;
 
 template <int N>
 __device__ __forceinline__ void dm_cp_async_wait() {
@@ -252,32 +254,64 @@ __device__ __forceinline__ void dm_issue_chunk(uint32_t tmem_d, uint32_t a_base,
   }
 }
 
-// Warp-specialised: the PRODUCER warp streams the weight chunks (cp.async ring) and issues every MMA as soon as its
-// operands exist; the 16 EPILOGUE warps turn accumulators into the next GEMM's A operand (or the outputs).  They meet
-// only at GEMM boundaries, through two mbarriers that flip once per GEMM:
-//   a_ready   (512 arrivals): the A operand of GEMM q is in shared memory          epilogue -> producer
-//   acc_ready (tcgen05.commit): the accumulator of GEMM q is complete, and sA free  producer -> epilogue
-// so a chunk costs the producer no CTA-wide barrier, and copies / MMA issue run ahead of the epilogues.
+// The producer's walk over (pair of tiles, GEMM, tile slot, chunk): GEMM q of slot 0, then GEMM q of slot 1, then q+1 ...
+// so that slot 1's MMAs run while group 0 turns slot 0's accumulator into its next operand, and vice versa.
+struct DmWalk {
+  int pair, q, s, ci;
+  __device__ __forceinline__ bool valid(int n_pairs) const { return pair < n_pairs; }
+  __device__ __forceinline__ void next(const int* gemm_count, int n_gemms, int my_tiles) {
+    if (++ci < gemm_count[q]) return;
+    ci = 0;
+    const int slots = 2 * pair + 1 < my_tiles ? 2 : 1;
+    if (++s < slots) return;
+    s = 0;
+    if (++q < n_gemms) return;
+    q = 0;
+    ++pair;
+  }
+};
+
+// Warp-specialised, two tiles in flight: the PRODUCER warp streams the weight chunks (cp.async ring) and issues every
+// MMA as soon as its operands exist; two EPILOGUE groups of 8 warps each own one tile slot (its activation buffer in
+// shared memory, its 256 TMEM columns) and turn accumulators into the next GEMM's A operand or into outputs.  Per
+// slot, two mbarriers that flip once per GEMM:
+//   a_ready[s]   (256 arrivals): the A operand of the slot's next GEMM is in shared memory      group s -> producer
+//   acc_ready[s] (tcgen05.commit): the accumulator is complete and the activation buffer free   producer -> group s
 __global__ void __launch_bounds__(DM_THREADS, 1)
 deform_mlp_kernel(DmDev a, DmPlan pl) {
   extern __shared__ __align__(128) unsigned char dm_smem[];
-  __shared__ uint64_t s_done[DM_SLOTS];  // MMAs of the chunk in ring slot s have completed
-  __shared__ uint64_t s_acc_ready, s_a_ready;
+  __shared__ uint64_t s_done[DM_SLOTS];  // MMAs of the chunk in ring slot i have completed
+  __shared__ uint64_t s_full[DM_SLOTS];  // the chunk's bytes have arrived in ring slot i (TMA transaction count)
+  __shared__ uint64_t s_acc_ready[2], s_a_ready[2];
   __shared__ uint32_t s_tmem;
   __shared__ float s_bias[(1 + FDLS_DEFORM_MAX_HEADS) * 128];  // b0, then b1 of every head
+  __shared__ int s_gemm_first[DM_MAX_GEMMS], s_gemm_count[DM_MAX_GEMMS];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int W = a.W, G = a.G;
   const uint32_t x_part = (uint32_t)(G / 8) * DM_ROWS * 16, a_part = (uint32_t)(W / 8) * DM_ROWS * 16;
-  char* sA = reinterpret_cast<char*>(dm_smem);
-  char* sX = sA;  // the input tile is dead once the trunk GEMM has completed, which is when sA is first written
-  char* sW = sA + PARTS * a_part;  // DM_SLOTS ring slots of DM_CHUNK_BYTES
+  char* sW = reinterpret_cast<char*>(dm_smem) + 2 * PARTS * a_part;  // behind the two activation buffers
+  const int n_gemms = 1 + 2 * a.H;
 
   if (warp == 0) tmem_alloc<512>(&s_tmem);
   if (tid == 0) {
-    for (int i = 0; i < DM_SLOTS; ++i) mbar_init(&s_done[i], 1);
-    mbar_init(&s_acc_ready, 1);
-    mbar_init(&s_a_ready, DM_EPI_THREADS);
+    for (int i = 0; i < DM_SLOTS; ++i) {
+      mbar_init(&s_done[i], 1);
+      mbar_init(&s_full[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s_acc_ready[i], 1);
+      mbar_init(&s_a_ready[i], DM_GROUP_THREADS);
+    }
     fence_mbar_init();
+    int q = -1;
+    for (int c = 0; c < pl.n_chunks; ++c) {  // chunks of one GEMM are consecutive in the plan
+      if (pl.c[c].first) {
+        ++q;
+        s_gemm_first[q] = c;
+        s_gemm_count[q] = 0;
+      }
+      ++s_gemm_count[q];
+    }
   }
   for (int i = tid; i < W; i += DM_THREADS) s_bias[i] = a.b0[i];
   for (int h = 0; h < a.H; ++h)
@@ -289,101 +323,93 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
 
   const int n_tiles = (a.P + DM_ROWS - 1) / DM_ROWS;
   const int my_tiles = blockIdx.x < n_tiles ? (n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
-  const long long total_steps = (long long)my_tiles * pl.n_chunks;
+  const int n_pairs = (my_tiles + 1) / 2;
 
   if (warp == DM_EPI_THREADS / 32) {
     // =================================================== PRODUCER ===================================================
-    auto copy_chunk = [&](long long step) {  // 32 lanes; the caller commits the cp.async group
-      if (step >= total_steps) return;
-      const DmChunk& ch = pl.c[step % pl.n_chunks];
-      const char* src = a.prep + ch.off;
-      char* dst = sW + (size_t)(step % DM_SLOTS) * DM_CHUNK_BYTES;
-      for (uint32_t o = lane * 16; o < ch.bytes; o += 32 * 16) {
-        const uint32_t d = smem_u32(dst + o);
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src + o) : "memory");
-      }
-    };
-    for (int i = 0; i < DM_AHEAD; ++i) {  // prime the ring: chunks 0 .. DM_AHEAD-1, one group each
-      copy_chunk(i);
-      asm volatile("cp.async.commit_group;" ::: "memory");
-    }
-    long long g = 0;    // chunks issued so far
-    uint32_t gemm = 0;  // GEMMs started so far
-    for (int t = 0; t < my_tiles; ++t) {
-      for (int c = 0; c < pl.n_chunks; ++c, ++g) {
-        const DmChunk& ch = pl.c[c];
-        // refill the ring: slot (g + AHEAD) % SLOTS == (g - 2) % SLOTS is free once chunk g-2's MMAs are complete
-        if (g >= DM_SLOTS - DM_AHEAD) mbar_wait(&s_done[(g + DM_AHEAD) % DM_SLOTS],
-                                                (uint32_t)(((g + DM_AHEAD - DM_SLOTS) / DM_SLOTS) & 1));
-        copy_chunk(g + DM_AHEAD);
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        dm_cp_async_wait<DM_AHEAD>();  // chunk g has landed (this lane's pieces)
-        fence_proxy_async();
-        if (ch.first) {  // this GEMM's A operand: written by the epilogue warps (fenced by them before arriving)
-          mbar_wait(&s_a_ready, gemm & 1);
-          ++gemm;
+    // One thread: a chunk is ONE TMA bulk copy (cp.async.bulk, completion in bytes on s_full[slot]) and 3 x ksteps MMAs.
+    // (A cp.async loop over the warp's lanes cost ~300 instructions per chunk and made this warp, not the tensor
+    // pipe, the bound of the kernel.)
+    if (lane == 0) {
+      DmWalk pf = {0, 0, 0, 0}, cur = {0, 0, 0, 0};
+      long long pf_step = 0;
+      auto prefetch = [&]() {  // copy the chunk `pf` points at into ring slot pf_step % SLOTS
+        if (pf.valid(n_pairs)) {
+          const DmChunk& ch = pl.c[s_gemm_first[pf.q] + pf.ci];
+          uint64_t* bar = &s_full[pf_step % DM_SLOTS];
+          mbar_expect_tx(bar, ch.bytes);
+          bulk_copy_g2s(sW + (size_t)(pf_step % DM_SLOTS) * DM_CHUNK_BYTES, a.prep + ch.off, ch.bytes, bar);
+          pf.next(s_gemm_count, n_gemms, my_tiles);
         }
-        __syncwarp();
-        if (lane == 0) {
-          tc_fence_after_sync();
-          const uint32_t a_base = ch.kind == DM_KIND_TRUNK ? smem_u32(sX) : smem_u32(sA);
-          const uint32_t a_prt = ch.kind == DM_KIND_TRUNK ? x_part : a_part;
-          const uint32_t d_col = ch.kind == DM_KIND_TRUNK ? 0u : ch.kind == DM_KIND_HIDDEN ? (uint32_t)W : (uint32_t)(2 * W);
-          const uint32_t b_base = smem_u32(sW + (size_t)(g % DM_SLOTS) * DM_CHUNK_BYTES);
-          dm_issue_chunk(tmem + d_col, a_base + (uint32_t)ch.slab0 * DM_ROWS * 16, a_prt, b_base,
-                         (uint32_t)ch.slabs * ch.N * 16, ch.N, ch.slabs / 2, !ch.first);
-          mma_commit(&s_done[g % DM_SLOTS]);
-          if (ch.last) mma_commit(&s_acc_ready);
+        ++pf_step;
+      };
+      for (int i = 0; i < DM_AHEAD; ++i) prefetch();
+      uint32_t gemm_no[2] = {0, 0};  // GEMMs started per slot
+      for (long long g = 0; cur.valid(n_pairs); ++g) {
+        const DmChunk& ch = pl.c[s_gemm_first[cur.q] + cur.ci];
+        const int s = cur.s;
+        // refill the ring: slot (g + AHEAD) % SLOTS held chunk g + AHEAD - SLOTS, whose MMAs must have completed
+        if (g >= DM_SLOTS - DM_AHEAD)
+          mbar_wait(&s_done[(g + DM_AHEAD) % DM_SLOTS], (uint32_t)(((g + DM_AHEAD - DM_SLOTS) / DM_SLOTS) & 1));
+        prefetch();
+        mbar_wait(&s_full[g % DM_SLOTS], (uint32_t)((g / DM_SLOTS) & 1));  // chunk g has landed
+        if (ch.first) {  // this GEMM's A operand: written by group s (fenced by its threads before they arrived)
+          mbar_wait(&s_a_ready[s], gemm_no[s] & 1);
+          ++gemm_no[s];
         }
-        __syncwarp();
+        tc_fence_after_sync();
+        const uint32_t a_base = smem_u32(dm_smem) + (uint32_t)s * PARTS * a_part;  // trunk: the X tile aliases it
+        const uint32_t a_prt = ch.kind == DM_KIND_TRUNK ? x_part : a_part;
+        const uint32_t d_col = (uint32_t)s * 256u + (ch.kind == DM_KIND_TRUNK ? 0u : (uint32_t)W);
+        const uint32_t b_base = smem_u32(sW + (size_t)(g % DM_SLOTS) * DM_CHUNK_BYTES);
+        dm_issue_chunk(tmem + d_col, a_base + (uint32_t)ch.slab0 * DM_ROWS * 16, a_prt, b_base,
+                       (uint32_t)ch.slabs * ch.N * 16, ch.N, ch.slabs / 2, !ch.first);
+        mma_commit(&s_done[g % DM_SLOTS]);
+        if (ch.last) mma_commit(&s_acc_ready[s]);
+        cur.next(s_gemm_count, n_gemms, my_tiles);
       }
     }
-    dm_cp_async_wait<0>();
   } else {
     // =================================================== EPILOGUE ===================================================
-    const int prow = tid & (DM_ROWS - 1);  // point of the tile = TMEM lane
-    const int quarter = tid >> 7;          // which quarter of the columns / slabs this thread takes
-    const uint32_t lane_field = (uint32_t)((warp & 3) * 32) << 16;  // a warp reads the TMEM lane quadrant warp % 4
+    const int grp = tid / DM_GROUP_THREADS;  // tile slot of this group
+    const int eid = tid % DM_GROUP_THREADS;
+    const int prow = eid & (DM_ROWS - 1);    // point of the tile = TMEM lane
+    const int half = eid >> 7;               // which half of the columns / slabs this thread takes
+    char* sA = reinterpret_cast<char*>(dm_smem) + (size_t)grp * PARTS * a_part;
+    char* sX = sA;  // the input tile is dead once the trunk GEMM has completed, which is when sA is first written
+    const uint32_t tbase = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)grp * 256u;  // lane quadrant warp % 4
     uint32_t gemm = 0;  // accumulators consumed so far
     auto operand_ready = [&]() {  // my part of the next GEMM's A operand is written
       fence_proxy_async();
-      mbar_arrive(&s_a_ready);
+      mbar_arrive(&s_a_ready[grp]);
     };
     auto wait_acc = [&]() {
-      mbar_wait(&s_acc_ready, gemm & 1);
+      mbar_wait(&s_acc_ready[grp], gemm & 1);
       ++gemm;
       tc_fence_after_sync();
     };
-    // TMEM columns [col, col + W) + bias, ReLU -> sA; this thread: W/4 columns of its point
+    // TMEM columns [col, col + W) of the slot + bias, ReLU -> sA; this thread: W/2 columns of its point
     auto relu_to_A = [&](uint32_t col, const float* __restrict__ bias) {
-      const int c0 = quarter * (W / 4);
-      if (W == 128) {
+      const int c0 = half * (W / 2);
+      for (int c = c0; c < c0 + W / 2; c += 32) {
         float v[32];
-        tmem_ld32(tmem + lane_field + col + c0, v);
+        tmem_ld32(tbase + col + c, v);
 #pragma unroll
         for (int sl = 0; sl < 4; ++sl) {
           float w8[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) w8[e] = fmaxf(v[sl * 8 + e] + bias[c0 + sl * 8 + e], 0.f);
-          store_row8_split(sA + (size_t)(c0 / 8 + sl) * DM_ROWS * 16 + prow * 16, a_part, w8);
-        }
-      } else {
-        for (int c = c0; c < c0 + W / 4; c += 8) {
-          float v[8];
-          tmem_ld8(tmem + lane_field + col + c, v);
-#pragma unroll
-          for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e] + bias[c + e], 0.f);
-          store_row8_split(sA + (size_t)(c / 8) * DM_ROWS * 16 + prow * 16, a_part, v);
+          for (int e = 0; e < 8; ++e) w8[e] = fmaxf(v[sl * 8 + e] + bias[c + sl * 8 + e], 0.f);
+          store_row8_split(sA + (size_t)(c / 8 + sl) * DM_ROWS * 16 + prow * 16, a_part, w8);
         }
       }
       tc_fence_before_sync();
     };
-    auto write_out = [&](int h, int row) {  // warps 0-3 only (quarter 0)
+    auto write_out = [&](int h, int row) {  // the group's first four warps (half 0); the outputs alias the hidden columns
       const DmHeadDev& hd = a.head[h];
       float y[48];
       for (int c = 0; c < hd.npad; c += 8) {
         float v[8];
-        tmem_ld8(tmem + lane_field + 2 * W + c, v);
+        tmem_ld8(tbase + W + c, v);
 #pragma unroll
         for (int e = 0; e < 8; ++e) y[c + e] = v[e];
       }
@@ -405,10 +431,10 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
       for (int e = 0; e < hd.k; ++e) hd.out[(size_t)row * hd.k + e] = y[e];
     };
 
-    for (int t = 0; t < my_tiles; ++t) {
+    for (int t = grp; t < my_tiles; t += 2) {
       const int row = ((int)blockIdx.x + t * (int)gridDim.x) * DM_ROWS + prow;
       // ---- X tile (aliases sA): every MMA that read sA for the previous tile has completed (last wait_acc below)
-      for (int slab = quarter; slab < G / 8; slab += 4) {
+      for (int slab = half; slab < G / 8; slab += 2) {
         float v[8];
         if (row < a.P) {
           const float4 p = *reinterpret_cast<const float4*>(a.feat + (size_t)row * G + slab * 8);
@@ -423,15 +449,15 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
       operand_ready();  // trunk GEMM may start
       for (int h = 0; h < a.H; ++h) {
         wait_acc();  // trunk (h = 0) or the previous head's layer 2: its accumulator is complete and sA is free
+        if (h > 0 && half == 0) write_out(h - 1, row);  // before layer 1 of head h overwrites these columns
         relu_to_A(0, s_bias);
         operand_ready();  // layer 1 of head h
-        if (h > 0 && quarter == 0) write_out(h - 1, row);  // overlaps the layer-1 MMAs
-        wait_acc();  // layer 1
+        wait_acc();       // layer 1
         relu_to_A((uint32_t)W, s_bias + (1 + h) * 128);
-        operand_ready();  // layer 2 of head h
+        operand_ready();  // layer 2 of head h (its output aliases the hidden columns just consumed)
       }
       wait_acc();  // layer 2 of the last head
-      if (quarter == 0) write_out(a.H - 1, row);
+      if (half == 0) write_out(a.H - 1, row);
     }
   }
   tc_fence_before_sync();
@@ -441,7 +467,7 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
 
 static size_t dm_smem_bytes(int G, int W) {
   const int K = G > W ? G : W;  // the input tile aliases the activation buffer
-  return (size_t)PARTS * (K / 8) * DM_ROWS * 16 + (size_t)DM_SLOTS * DM_CHUNK_BYTES;
+  return (size_t)2 * PARTS * (K / 8) * DM_ROWS * 16 + (size_t)DM_SLOTS * DM_CHUNK_BYTES;  // two tile slots
 }
 
 size_t deform_prep_bytes(const FdlsDeformArgs* a) {

@@ -50,6 +50,19 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// ---- TMA bulk copy (1-D, global -> shared), completion counted in bytes on an mbarrier ----------------------------------
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// size % 16 == 0, both addresses 16-byte aligned; issued by ONE thread; the data arrives through the async proxy, the
+// one tcgen05.mma reads shared memory through, so no proxy fence is needed between the two
+__device__ __forceinline__ void bulk_copy_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
 // ---- proxies and tcgen05 fences -------------------------------------------------------------------------------------
 // shared memory written with ordinary stores / cp.async must be fenced before the tensor core (async proxy) reads it
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
@@ -131,16 +144,14 @@ __device__ __forceinline__ void mma_commit(uint64_t* bar) {
 
 // ---- fp16 x 2 ---------------------------------------------------------------------------------------------------------
 constexpr int PARTS = 2;
-// two floats -> their packed high halves (low 16 bits = x0) and packed remainders
+// two floats -> their packed high halves (low 16 bits = x0) and packed remainders.  PACKED conversions on purpose:
+// cvt.rn.f16x2.f32 is one F2FP on the ALU pipe, the scalar cvt.f16.f32 is an F2F on the quarter-rate XU pipe, and the
+// network's epilogues convert 100k elements per tile (measured: scalar converts made the epilogue, not the tensor
+// pipe, the bound of the kernel).
 __device__ __forceinline__ void split_h2(float x0, float x1, uint32_t& hi, uint32_t& lo) {
-  uint16_t a0, a1, b0, b1;
-  asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(a0) : "f"(x0));
-  asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(a1) : "f"(x1));
-  const float r0 = x0 - __half2float(__ushort_as_half(a0)), r1 = x1 - __half2float(__ushort_as_half(a1));
-  asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(b0) : "f"(r0));
-  asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(b1) : "f"(r1));
-  hi = (uint32_t)a0 | ((uint32_t)a1 << 16);
-  lo = (uint32_t)b0 | ((uint32_t)b1 << 16);
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(x1), "f"(x0));  // d = {hi half: 1st src, lo half: 2nd}
+  const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(x1 - f.y), "f"(x0 - f.x));
 }
 // split 8 consecutive k of one row and store them as one 16-byte piece per part: part p at dst + p * part_bytes
 __device__ __forceinline__ void store_row8_split(char* dst, size_t part_bytes, const float (&v)[8]) {
