@@ -19,5 +19,7 @@ simple_knn = _il.import_module(__name__ + ".simple_knn")
 hexplane = _il.import_module(__name__ + ".hexplane")
 sweep = _il.import_module(__name__ + ".sweep")
 deformation = _il.import_module(__name__ + ".deformation")
+train_ops = _il.import_module(__name__ + ".train_ops")
+gaussian_renderer = _il.import_module(__name__ + ".gaussian_renderer")
 
-__all__ = ["_lib", "_C", "diff_gaussian_rasterization", "simple_knn", "hexplane", "sweep", "deformation"]
+__all__ = ["_lib", "_C", "diff_gaussian_rasterization", "simple_knn", "hexplane", "sweep", "deformation", "train_ops", "gaussian_renderer"]

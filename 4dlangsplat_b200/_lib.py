@@ -124,6 +124,15 @@ SYMBOLS = {
     "fdls_deform_prep_bytes": (C.c_size_t, [C.POINTER(FdlsDeformArgs)]),
     "fdls_deform_prepare": (C.c_int, [C.POINTER(FdlsDeformArgs), C.c_void_p]),
     "fdls_deform_forward": (C.c_int, [C.POINTER(FdlsDeformArgs), C.c_void_p]),
+    "fdls_masked_l1": (C.c_int, [C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p,
+                                 C.c_void_p, C.c_void_p]),
+    "fdls_gt_feature_gather": (C.c_int, [C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_void_p]),
+    "fdls_adam_step": (C.c_int, [C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                 C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_float), C.POINTER(C.c_float),
+                                 C.POINTER(C.c_int32), C.c_double, C.c_double, C.c_void_p]),
+    "fdls_densify_stats": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fdls_compact_rows": (C.c_int, [C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fdls_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fdls_knn_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "fdls_knn_dist2": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),

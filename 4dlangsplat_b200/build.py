@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.environ.get("FDLS_LIB", os.path.join(HERE, "libfdls.so"))  # FDLS_LIB / FDLS_NVCC_EXTRA: A/B builds
 SOURCES = ["api.cu", "preprocess_fwd.cu", "binning.cu", "binning_partition.cu", "radix_sort.cu", "render_fwd.cu", "render_bwd.cu", "render_bwd_shfl.cu",
-           "preprocess_bwd.cu", "knn.cu", "hexplane.cu", "deform_mlp.cu"]
+           "preprocess_bwd.cu", "knn.cu", "hexplane.cu", "deform_mlp.cu", "train_ops.cu"]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler",
               "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr"]
 

@@ -65,6 +65,16 @@ int umma_linear(int rows, int N, int K, const float* X, const float* W, const fl
 size_t deform_prep_bytes(const FdlsDeformArgs* a);
 int deform_prepare(const FdlsDeformArgs* a, cudaStream_t st);
 int deform_forward(const FdlsDeformArgs* a, cudaStream_t st);
+// train_ops.cu
+int masked_l1(int C, long long HW, const float* pred, const float* gt, const float* mask, float weight, float* grad,
+              float* loss, cudaStream_t st);
+int gt_gather(long long HW, int K, int F, const int32_t* seg, const float* fmap, float* out, uint8_t* mask,
+              cudaStream_t st);
+int adam_step(int count, float* const* p, const float* const* g, float* const* m, float* const* v, const long long* n,
+              const float* lr, const float* eps, const int* step, double b1, double b2, cudaStream_t st);
+int densify_stats(int P, const float* vgrad, const uint8_t* filter, float* accum, float* denom, cudaStream_t st);
+int compact_rows(long long n, int width, const uint8_t* keep, const int32_t* dest, const float* in, float* out,
+                 cudaStream_t st);
 // knn.cu
 size_t knn_workspace_bytes(int N);
 int knn_dist2(int N, const float* xyz, float* out, void* ws, size_t ws_bytes, cudaStream_t st);
@@ -410,5 +420,28 @@ FDLS_API int fdls_umma_linear(int32_t rows, int32_t N, int32_t K, const float* X
 FDLS_API size_t fdls_deform_prep_bytes(const FdlsDeformArgs* a) { return deform_prep_bytes(a); }
 FDLS_API int fdls_deform_prepare(const FdlsDeformArgs* a, void* stream) { return deform_prepare(a, (cudaStream_t)stream); }
 FDLS_API int fdls_deform_forward(const FdlsDeformArgs* a, void* stream) { return deform_forward(a, (cudaStream_t)stream); }
+
+FDLS_API int fdls_masked_l1(int32_t C, int64_t HW, const float* pred, const float* gt, const float* mask, float weight,
+                            float* grad, float* loss, void* stream) {
+  return masked_l1(C, HW, pred, gt, mask, weight, grad, loss, (cudaStream_t)stream);
+}
+FDLS_API int fdls_gt_feature_gather(int64_t HW, int32_t K, int32_t F, const int32_t* seg, const float* feature_map,
+                                    float* out, uint8_t* mask, void* stream) {
+  return gt_gather(HW, K, F, seg, feature_map, out, mask, (cudaStream_t)stream);
+}
+FDLS_API int fdls_adam_step(int32_t count, float* const* p, const float* const* g, float* const* m, float* const* v,
+                            const int64_t* n, const float* lr, const float* eps, const int32_t* step, double beta1,
+                            double beta2, void* stream) {
+  if (count > 0 && (!p || !g || !m || !v || !n || !lr || !eps || !step)) return FDLS_EINVAL;
+  return adam_step(count, p, g, m, v, (const long long*)n, lr, eps, step, beta1, beta2, (cudaStream_t)stream);
+}
+FDLS_API int fdls_densify_stats(int32_t P, const float* viewspace_grad, const uint8_t* filter, float* xyz_gradient_accum,
+                                float* denom, void* stream) {
+  return densify_stats(P, viewspace_grad, filter, xyz_gradient_accum, denom, (cudaStream_t)stream);
+}
+FDLS_API int fdls_compact_rows(int64_t n, int32_t width, const uint8_t* keep, const int32_t* dest, const float* in,
+                               float* out, void* stream) {
+  return compact_rows(n, width, keep, dest, in, out, (cudaStream_t)stream);
+}
 
 }  // extern "C"

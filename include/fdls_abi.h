@@ -314,6 +314,32 @@ int fdls_deform_prepare(const FdlsDeformArgs* a, void* stream);
 /* reads feat, biases, base and `prep`; writes out of every head */
 int fdls_deform_forward(const FdlsDeformArgs* a, void* stream);
 
+/* ---- the streaming kernels around the rasterizer in a training iteration ----------------------
+ * fdls_masked_l1: *loss += weight * sum |pred*mask - gt*mask| and, if grad != null, grad = weight * sign(pred*mask -
+ *   gt*mask) * mask in the same pass (l1_loss of utils/loss_utils.py:20-21 as train.py:283-296 uses it; weight = the
+ *   mean's 1/N times args.lam; mask (HW floats, shared by the C channels) may be null = all ones).  pred, gt, grad:
+ *   (C, HW) planar.  The gradient is exactly what fdls_backward takes as dL_dout_color / dL_dout_language.
+ * fdls_gt_feature_gather: out (F, HW) = feature_map[seg[pix]] (negative ids index from the end like tensor indexing),
+ *   mask[pix] = seg[pix] != -1: the per-pixel gather of Camera.get_language_feature (scene/cameras.py:97-118), which
+ *   the reference does on the CPU per view per iteration.
+ * fdls_adam_step: torch.optim.Adam (no weight decay / amsgrad; scene/gaussian_model.py:301) over `count` <= 32 tensors
+ *   in ONE launch; p, g, m, v, n, lr, eps, step are HOST arrays of `count` entries (step = the 1-based step count of
+ *   each tensor's state).
+ * fdls_densify_stats: add_densification_stats (scene/gaussian_model.py:746-748).
+ * fdls_compact_rows: out[dest[i]] = in[i] for rows with keep[i] (prune_points / _prune_optimizer, :487-520); dest = an
+ *   exclusive scan of keep, shared by all arrays of the model. */
+int fdls_masked_l1(int32_t C, int64_t HW, const float* pred, const float* gt, const float* mask, float weight, float* grad,
+                   float* loss, void* stream);
+int fdls_gt_feature_gather(int64_t HW, int32_t K, int32_t F, const int32_t* seg, const float* feature_map, float* out,
+                           uint8_t* mask, void* stream);
+int fdls_adam_step(int32_t count, float* const* p, const float* const* g, float* const* m, float* const* v,
+                   const int64_t* n, const float* lr, const float* eps, const int32_t* step, double beta1, double beta2,
+                   void* stream);
+int fdls_densify_stats(int32_t P, const float* viewspace_grad, const uint8_t* filter, float* xyz_gradient_accum,
+                       float* denom, void* stream);
+int fdls_compact_rows(int64_t n, int32_t width, const uint8_t* keep, const int32_t* dest, const float* in, float* out,
+                      void* stream);
+
 #ifdef __cplusplus
 }
 #endif
