@@ -274,17 +274,13 @@ class deform_network(nn.Module):
     def forward_dynamic(self, point, scales=None, rotations=None, opacity=None, shs=None, lang=None, times_sel=None,
                         init_centers=False, activations=False):
         net = self.deformation_net
-        if net._fusable(point):
-            # the encodings only feed slices [:, :3] / [:, :4] / [:, :1] of themselves into the network
-            # (deformation.py:76,118-147), so the fused path never builds them; the time encoding is only needed by
-            # lang_deform
-            times_emb = None if net.args.no_dlang else poc_fre(times_sel, self.time_poc)
-            return net.forward_dynamic(point, scales, rotations, opacity, shs, lang, None, times_sel, times_emb,
-                                       init_centers, activations)
-        times_emb = poc_fre(times_sel, self.time_poc)
-        return net.forward_dynamic(poc_fre(point, self.pos_poc), poc_fre(scales, self.rotation_scaling_poc),
-                                   poc_fre(rotations, self.rotation_scaling_poc), opacity, shs, lang, None, times_sel,
-                                   times_emb, init_centers, activations)
+        # The reference encodes point / scales / rotations with poc_fre (deformation.py:232-236), but the network only
+        # ever reads the slices [:, :3] / [:, :4] of those encodings (:76,118-147), which ARE the inputs (poc_fre puts
+        # the raw values first): the 63 + 15 + 20 sin/cos columns per point are never used, so neither path builds them
+        # (values and gradients are identical).  The time encoding feeds lang_deform only.
+        times_emb = None if net.args.no_dlang else poc_fre(times_sel, self.time_poc)
+        return net.forward_dynamic(point, scales, rotations, opacity, shs, lang, None, times_sel, times_emb,
+                                   init_centers, activations)
 
     def get_mlp_parameters(self):
         return self.deformation_net.get_mlp_parameters() + list(self.timenet.parameters())

@@ -1091,6 +1091,189 @@ def main_deform(a, rank, world, local, warmup):
         dist.destroy_process_group()
 
 
+def main_train_deform(a, rank, world, local, warmup):
+    """BASELINE.json configs[2] as written: "training step fwd+bwd WITH deformation, batch 4 views".  Per view: the
+    deformation network moves the 300k Gaussians to the view's timestamp (autograd), activations, rasterizer
+    forward + backward, backward through the network; leaves = the canonical Gaussian attributes + every network
+    parameter (7.5 M, mostly HexPlane planes); views sharded over ranks, one flat all-reduce.
+    ours: fused HexPlane forward/backward kernels + the reference's linear layers on cuBLAS (deformation.py, grad path)
+    + this repo's rasterizer.  --impl reference: the reference op sequence on stock torch kernels (18 grid_sample, ...)
+    + the unmodified reference CUDA rasterizer behind an autograd.Function."""
+    import itertools
+    from types import SimpleNamespace
+    import torch.nn.functional as F
+    fd = importlib.import_module("4dlangsplat_b200")
+    fdist = importlib.import_module("4dlangsplat_b200.dist")
+    lib = fd._lib.load()
+    n_views = max(TRAIN_VIEWS, a.gpus)
+    wl = TrainWorkload("cfg3", rank, world, n_views=n_views)
+    s = wl.s
+    torch.manual_seed(7)
+    args = SimpleNamespace(net_width=128, timebase_pe=4, defor_depth=1, posebase_pe=10, scale_rotation_pe=2, opacity_pe=2,
+                           timenet_width=64, timenet_output=32, bounds=1.6, no_dx=False, no_grid=False, no_ds=False,
+                           no_dr=False, no_do=True, no_dshs=True, no_dlang=1, empty_voxel=False, grid_pe=0,
+                           static_mlp=False, apply_rotation=False, multires=[1, 2, 4],
+                           kplanes_config=dict(grid_dimensions=2, input_coordinate_dim=4, output_coordinate_dim=16,
+                                               resolution=[64, 64, 64, 150]))
+    net = fd.deformation.deform_network(args).cuda()
+    with torch.no_grad():
+        for n, q in net.named_parameters():
+            if "grid" in n:
+                q.add_(0.05 * torch.randn_like(q))
+            elif any(h in n for h in ("pos_deform.3", "scales_deform.3", "rotations_deform.3")):
+                q.mul_(0.02)
+    dn = net.deformation_net
+    P = s.P
+    base = wl.params
+    dn.set_aabb((base["means3D"].max(0).values + 0.1).tolist(), (base["means3D"].min(0).values - 0.1).tolist())
+    p = dict(xyz=base["means3D"].clone(), scales=torch.log(base["scales"]), rots=base["rots"].clone(),
+             opac=torch.logit(base["opac"].clamp(1e-4, 1 - 1e-4)), shs=base["shs"].clone(), lang=base["lang"].clone())
+    p = {k: v.requires_grad_(True) for k, v in p.items()}
+    means2D = torch.zeros_like(p["xyz"], requires_grad=True)
+    net_params = [q for q in net.parameters() if q.requires_grad]
+    leaves = list(p.values()) + [means2D] + net_params
+    bucket = fdist.GradBucket(leaves)  # plain (copy) mode: most leaves reach the rasterizer through the network
+    bucket.timing = []
+    times = {v: torch.full((P, 1), (v + 0.5) / n_views, device="cuda") for v in wl.mine}
+    combs = list(itertools.combinations(range(4), 2))
+    dgr = fd.diff_gaussian_rasterization
+
+    def deform_ours(v):
+        return net(p["xyz"], p["scales"], p["rots"], p["opac"], p["shs"], p["lang"], times[v])
+
+    def deform_ref(v):
+        fdm = fd.deformation
+        tm = times[v]
+        pe, se = fdm.poc_fre(p["xyz"], net.pos_poc), fdm.poc_fre(p["scales"], net.rotation_scaling_poc)
+        re_, _ = fdm.poc_fre(p["rots"], net.rotation_scaling_poc), fdm.poc_fre(tm, net.time_poc)
+        aabb = dn.grid.aabb
+        q = torch.cat([(pe[:, :3] - aabb[0]) * (2.0 / (aabb[1] - aabb[0])) - 1.0, tm], dim=-1)
+        feats = []
+        for level in dn.grid.grids:
+            space = 1.0
+            for ci, comb in enumerate(combs):
+                o = F.grid_sample(level[ci], q[..., list(comb)].view(1, 1, -1, 2), align_corners=True, mode="bilinear",
+                                  padding_mode="border")
+                space = space * o.view(level[ci].shape[1], -1).t()
+            feats.append(space)
+        hidden = dn.feature_out(torch.cat(feats, dim=-1))
+        return (pe[:, :3] + dn.pos_deform(hidden), se[:, :3] + dn.scales_deform(hidden),
+                re_[:, :4] + dn.rotations_deform(hidden), p["opac"], p["shs"], p["lang"], None)
+
+    if a.impl == "reference":
+        import refcuda
+        refs = {v: refcuda.Ref(s.F) for v in wl.mine}
+        M = s.shs.shape[1]
+        f32 = dict(dtype=torch.float32, device="cuda")
+
+        class RefRaster(torch.autograd.Function):  # the reference's _RasterizeGaussians, minus the pybind glue
+            @staticmethod
+            def forward(ctx, v, means3D, means2D_, shs, lang, opac, scales, rots):
+                c = wl.views[v]
+                color, langi, depth = torch.zeros((3, s.H, s.W), **f32), torch.zeros((s.F, s.H, s.W), **f32), torch.zeros((1, s.H, s.W), **f32)
+                radii = torch.zeros(P, dtype=torch.int32, device="cuda")
+                args_ = [x.contiguous() for x in (means3D, shs, lang, opac, scales, rots)]
+                R = refs[v].forward_raw(P, s.sh_degree, M, s.W, s.H, wl.bg, args_[0], args_[1], args_[2], args_[3],
+                                        args_[4], args_[5], c["view"], c["proj"], c["campos"], s.tanfovx, s.tanfovy,
+                                        color, langi, depth, radii)
+                ctx.v, ctx.R = v, R
+                ctx.save_for_backward(radii, *args_)
+                return color, langi
+
+            @staticmethod
+            def backward(ctx, dcol, dlang):
+                radii, means3D, shs, lang, opac, scales, rots = ctx.saved_tensors
+                c = wl.views[ctx.v]
+                z = lambda *shape: torch.zeros(shape, **f32)
+                g = SimpleNamespace(means2D=z(P, 3), conic=z(P, 4), opacity=z(P, 1), colors=z(P, 3), lang=z(P, s.F),
+                                    depths=z(P), means3D=z(P, 3), cov3D=z(P, 6), sh=z(P, M, 3), scales=z(P, 3), rots=z(P, 4))
+                refs[ctx.v].backward_raw(P, s.sh_degree, M, ctx.R, s.W, s.H, wl.bg, means3D, shs, lang, scales, rots,
+                                         c["view"], c["proj"], c["campos"], s.tanfovx, s.tanfovy, radii,
+                                         dcol.contiguous(), dlang.contiguous(), z(1, s.H, s.W), g)
+                return None, g.means3D, g.means2D, g.sh, g.lang, g.opacity, g.scales, g.rots
+
+    def render(v):
+        m, sc, ro, op, sh, la, _ = (deform_ours if a.impl == "ours" else deform_ref)(v)
+        sc, ro, op = torch.exp(sc), F.normalize(ro), torch.sigmoid(op)
+        if a.impl == "ours":
+            c = wl.views[v]
+            rs = dgr.GaussianRasterizationSettings(s.H, s.W, s.tanfovx, s.tanfovy, wl.bg, 1.0, c["view"], c["proj"],
+                                                   s.sh_degree, c["campos"], False, False, True)
+            return dgr.GaussianRasterizer(rs)(means3D=m, means2D=means2D, opacities=op, shs=sh,
+                                              language_feature_precomp=la, scales=sc, rotations=ro)
+        return RefRaster.apply(v, m, means2D, sh, la, op, sc, ro)
+
+    def loss_of(v, out):
+        c = wl.views[v]
+        return ((out[0] * c["dcol"]).sum() + (out[1] * c["dlang"]).sum()) * wl.n_views
+
+    def step():
+        for t in leaves:
+            t.grad = None
+        return fdist.sharded_step(render, loss_of, wl.n_views, bucket)
+
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    bucket.timing = []
+    barrier(world)
+    l0 = lib.fdls_kernel_launches()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        loss, nbytes = step()
+    e1.record()
+    barrier(world)
+    clocks = sampler.result()
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    allreduce_ms = max_over_ranks(bucket.allreduce_ms(), world)
+    launches = lib.fdls_kernel_launches() - l0
+    if os.environ.get("FDLS_TORCH_PROFILE") and rank == 0:  # where a step's GPU time goes (stderr)
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            step()
+            torch.cuda.synchronize()
+        sys.stderr.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=25, max_name_column_width=70) + "\n")
+    # end to end: timestamps + ground-truth-side gradients from pinned host memory every step, loss read back
+    host = {v: {k: x.cpu().pin_memory() for k, x in c.items()} for v, c in wl.views.items()}
+    h2d = sum(x.numel() * 4 for c in host.values() for x in c.values())
+    loss_host = torch.zeros(1).pin_memory()
+    barrier(world)
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        for v, c in host.items():
+            wl.views[v] = {k: x.to("cuda", non_blocking=True) for k, x in c.items()}
+        loss, _ = step()
+        loss_host.copy_(loss.reshape(1), non_blocking=True)
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0, world)
+    line = {"metric": "train_with_deformation_iters_per_s", "value": round(a.steps / (ms * 1e-3), 3), "unit": "iters/s",
+            "n_gpus": world, "steps": a.steps, "warmup": warmup, "ms_per_step": round(ms / a.steps, 4),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "cfg3 incl. deformation: %d Gaussians, %dx%d, F=%d, batch of %d views; per view "
+                                   "deformation network (HyperNeRF configuration, 7.5 M parameters) forward + backward "
+                                   "around rasterizer forward + backward" % (P, s.W, s.H, s.F, wl.n_views),
+                       "batch_views": wl.n_views, "views_per_rank": len(wl.mine),
+                       "sharding": "views round-robin over ranks; one flat fp32 all-reduce of all leaf gradients",
+                       "l2": "per view the 58 MB feature matrix, 154 MB of hidden activations per layer and the "
+                             "rasterizer's working set stream through HBM"},
+            "clocks": clocks,
+            "e2e": {"value": round(a.steps / e2e_s, 3), "unit": "iters/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+            "gpu_launches": int(launches), "allreduce_bytes_per_step": int(nbytes), "allreduce_ms": round(allreduce_ms, 4)}
+    if a.impl != "ours":
+        line["impl"] = "reference"
+        line["cpu_baseline"] = {"value": line["value"], "unit": "iters/s", "cores": 1, "kind": "port",
+                                "sample": "reference op sequence for the deformation (stock torch CUDA kernels, autograd) "
+                                          "+ the unmodified reference CUDA rasterizer, same GPU, same steps"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -1099,7 +1282,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--mode", default="render", choices=["render", "train", "hexplane", "deform"],
+    ap.add_argument("--mode", default="render", choices=["render", "train", "hexplane", "deform", "train_deform"],
                     help="render: forward sweep (headline, cfg2); train: fwd+bwd over a batch of 4 views (cfg3)")
     a = ap.parse_args()
     if not torch.cuda.is_available():
@@ -1115,6 +1298,8 @@ def main():
         return main_hexplane(a, rank, world, local, warmup)
     if a.mode == "deform":
         return main_deform(a, rank, world, local, warmup)
+    if a.mode == "train_deform":
+        return main_train_deform(a, rank, world, local, warmup)
     if a.mode == "train" or a.workload in ("cfg3",):
         return main_train(a, rank, world, local, warmup)
     wl = Workload(a.workload, rank, world)
