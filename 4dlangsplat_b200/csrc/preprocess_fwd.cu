@@ -106,6 +106,26 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
   __syncthreads();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int sh_stride = 3 * M + 1;
+  // The Gaussian's own attributes are requested BEFORE the SH staging below, so that their global-memory latency
+  // overlaps the staging's instead of following it (the kernel is latency-bound: two dependent round trips per CTA,
+  // two waves of CTAs).  Values only; the arithmetic on them is unchanged.
+  float3 p_orig = {0.f, 0.f, 0.f}, in_scale = {0.f, 0.f, 0.f};
+  float4 in_rot = {0.f, 0.f, 0.f, 0.f};
+  float in_opacity = 0.f;
+  float in_lang[FDLS_MAX_LANG_CHANNELS];
+#pragma unroll
+  for (int i = 0; i < FDLS_MAX_LANG_CHANNELS; ++i) in_lang[i] = 0.f;
+  if (idx < P) {
+    p_orig = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
+    if (cov3D_precomp == nullptr) {
+      in_scale = make_float3(scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]);
+      in_rot = reinterpret_cast<const float4*>(rotations)[idx];
+    }
+    in_opacity = opacities[idx];
+#pragma unroll
+    for (int i = 0; i < FDLS_MAX_LANG_CHANNELS; ++i)
+      if (lang != nullptr && i < F) in_lang[i] = lang[(size_t)idx * F + i];
+  }
   if (sh_magic != 0) {
     // Coalesced staging of this warp's 32 x (M,3) SH block: the direct per-thread reads are 192-byte strided
     // (forward.cu:20-71 reads sh[idx*max_coeffs + i]) and waste most of every sector; here each warp streams its
@@ -156,7 +176,6 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
   uint32_t out_tiles = 0;
   uint32_t out_depth_bits = 0xffffffffu;  // culled Gaussians sort behind every visible one (depth > 0.2 => sign bit 0)
   if (idx < P) do {
-    const float3 p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
     // in_frustum (auxiliary.h:139-164): only the near-plane test is live.
     const float3 p_view = xform4x3(p_orig, s_view);
     if (p_view.z <= 0.2f) {
@@ -175,9 +194,7 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
 #pragma unroll
       for (int i = 0; i < 6; ++i) cov3D[i] = cov3D_precomp[6 * idx + i];
     } else {
-      const float3 s = {scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
-      const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
-      cov3d_from_scale_rot(s, vp.scale_modifier, q, cov3D);
+      cov3d_from_scale_rot(in_scale, vp.scale_modifier, in_rot, cov3D);
     }
     const float3 cov = cov2d_ewa(p_orig, vp.focal_x, vp.focal_y, vp.tanfovx, vp.tanfovy, cov3D, s_view);
 
@@ -209,13 +226,10 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
     }
     clamped[idx] = cl;
 
-    float l[FDLS_MAX_LANG_CHANNELS];
-#pragma unroll
-    for (int i = 0; i < FDLS_MAX_LANG_CHANNELS; ++i) l[i] = (lang != nullptr && i < F) ? lang[(size_t)idx * F + i] : 0.f;
-
+    const float* l = in_lang;
     float4* r = rec + (size_t)idx * 4;
     r[0] = make_float4(point_image.x, point_image.y, conic.x, conic.y);
-    r[1] = make_float4(conic.z, opacities[idx], p_view.z, rgb.x);
+    r[1] = make_float4(conic.z, in_opacity, p_view.z, rgb.x);
     r[2] = make_float4(rgb.y, rgb.z, l[0], l[1]);
     r[3] = make_float4(l[2], l[3], l[4], l[5]);
     out_radius = my_radius;

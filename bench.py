@@ -906,7 +906,7 @@ def main_hexplane(a, rank, world, local, warmup):
         dist.destroy_process_group()
 
 
-def main_deform(a, rank, world, local, warmup):
+def deform_line(a, rank, world, local, warmup, steps):
     """SURVEY 8f N1 / 8d metric (i) "end to end incl. deformation": cfg2's sweep where every frame first moves the
     300k Gaussians to its timestamp with the deformation network (arguments/hypernerf/default.py: 16-channel HexPlane
     [64,64,64,150] x multires [1,2,4], net_width 128, defor_depth 1, heads pos / scales / rotations) and then
@@ -1005,12 +1005,12 @@ def main_deform(a, rank, world, local, warmup):
         sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for i in range(a.steps * FRAMES_PER_STEP):
+        for i in range(steps * FRAMES_PER_STEP):
             frame(i, with_render)
         e1.record()
         barrier(world)
         res[with_render] = (max_over_ranks(e0.elapsed_time(e1), world), lib.fdls_kernel_launches() - l0, sampler.result())
-    n_frames = a.steps * FRAMES_PER_STEP
+    n_frames = steps * FRAMES_PER_STEP
     # parity inside the bench: the fused deformation equals the op sequence on this very network
     with torch.no_grad():
         mine, theirs = deform_ours(3), deform_ref(3)
@@ -1040,7 +1040,7 @@ def main_deform(a, rank, world, local, warmup):
     W_, G_ = args.net_width, dn.grid.feat_dim
     flops = 2.0 * P * (G_ * W_ + 3 * W_ * W_ + W_ * (3 + 3 + 4))
     line = {"metric": "render_with_deformation_frames_per_s", "value": round(n_frames * world / (ms * 1e-3), 2),
-            "unit": "frames/s", "n_gpus": world, "steps": a.steps, "warmup": warmup, "ms_per_step": round(ms / a.steps, 4),
+            "unit": "frames/s", "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": round(ms / steps, 4),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "cfg2 incl. deformation: %d Gaussians moved to each of %d timestamps per step by the "
                                    "HyperNeRF-configured deformation network (HexPlane 16 ch [64,64,64,150] x [1,2,4], "
@@ -1084,6 +1084,13 @@ def main_deform(a, rank, world, local, warmup):
         line["cpu_baseline"] = {"value": line["value"], "unit": "frames/s", "cores": 1, "kind": "port",
                                 "sample": "the reference's op sequence for the deformation on stock torch CUDA kernels + "
                                           "the unmodified reference CUDA rasterizer, same GPU, same %d frames" % n_frames}
+    del wl, net
+    torch.cuda.empty_cache()
+    return line
+
+
+def main_deform(a, rank, world, local, warmup):
+    line = deform_line(a, rank, world, local, warmup, a.steps)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -1378,6 +1385,11 @@ def main():
         line["train"] = {k: t[k] for k in ("metric", "value", "unit", "ms_per_step", "scaling", "config", "e2e",
                                             "gpu_launches", "roofline", "stages_ms", "allreduce_bytes_per_step",
                                             "allreduce_ms", "clocks") if k in t}
+    # SURVEY 8d metric (i) "end to end incl. deformation": the same sweep with the deformation network in front
+    if a.workload == "cfg2" and os.environ.get("FDLS_BENCH_DEFORM", "1") != "0":
+        dl = deform_line(a, rank, world, local, warmup, max(1, min(3, a.steps)))
+        line["with_deformation"] = {k: dl[k] for k in ("metric", "value", "unit", "steps", "ms_per_step", "config", "e2e",
+                                                       "gpu_launches", "deform", "roofline", "clocks") if k in dl}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
