@@ -80,7 +80,13 @@ def _pack_all(planes):
             out.append(hit[1])
             continue
         _, Cc, H, W = src.shape
-        cl = hit[1] if hit is not None else torch.empty(H, W, Cc, dtype=torch.float32, device=src.device)
+        # With grad enabled an earlier forward may have saved the cached copy for its backward: a changed parameter
+        # then gets a FRESH copy instead of an in-place rewrite behind autograd's back (the reference would raise
+        # "modified by an inplace operation"; here the old graph keeps differentiating against the old planes).
+        reuse = hit is not None and not torch.is_grad_enabled()
+        cl = hit[1] if reuse else torch.empty(H, W, Cc, dtype=torch.float32, device=src.device)
+        if hit is None:  # drop the entry when the parameter dies (30 MB per plane set otherwise leak)
+            weakref.finalize(plane, _packed.pop, key, None)
         _packed[key] = (plane._version, cl, weakref.ref(plane))
         stale.append((src, cl))
         out.append(cl)
