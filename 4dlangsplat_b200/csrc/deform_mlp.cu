@@ -179,7 +179,6 @@ static int dm_make_plan(const FdlsDeformArgs* a, DmPlan* pl) {
     if (k < 1 || k > 48) return FDLS_EUNSUPPORTED;
     pl->npad[h] = dm_npad(k);
     if (!add(DM_KIND_HIDDEN, h, a->W, a->W)) return FDLS_EUNSUPPORTED;
-    if (!add(DM_KIND_OUT, h, pl->npad[h], a->W)) return FDLS_EUNSUPPORTED;
   }
   pl->total_bytes = off;
   return FDLS_OK;
@@ -206,8 +205,8 @@ deform_prep_kernel(const float* __restrict__ Wm, int N, int Npad, int K, char* _
 }
 
 struct DmHeadDev {
-  const float* b1; const float* b2; const float* base; float* out;
-  int k, act, npad;
+  const float* b1; const float* w2; const float* b2; const float* base; float* out;
+  int k, act;
 };
 struct DmDev {
   int P, G, W, H;
@@ -217,17 +216,12 @@ struct DmDev {
 
 constexpr int DM_GROUP_THREADS = 256;                      // one epilogue group: two threads per point, W/2 columns each
 constexpr int DM_EPI_THREADS = 2 * DM_GROUP_THREADS;       // two groups = two tiles in flight per CTA
-constexpr int DM_THREADS = DM_EPI_THREADS + 32;            // + one producer warp: weight copies and MMA issue
-constexpr int DM_SLOTS = 5;                                // weight-chunk ring: chunk g+3 is copied while chunk g multiplies
-constexpr int DM_AHEAD = 3;
-constexpr int DM_MAX_GEMMS = 1 + 2 * FDLS_DEFORM_MAX_HEADS;
+constexpr int DM_THREADS = DM_EPI_THREADS + 64;            // + the MMA-issue warp and the TMA warp (one thread each)
+constexpr int DM_SLOTS = 5;                                // weight-chunk ring
+constexpr int DM_MAX_GEMMS = 1 + FDLS_DEFORM_MAX_HEADS;    // trunk + one layer-1 GEMM per head
+constexpr int DM_OUT_BLOCK = 8;                            // outputs of a head's last layer handled per pass
 
-template <int N>
-__device__ __forceinline__ void dm_cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-
-// like dm_issue_gemm, with the descriptors advanced by adding to their address field (3 instructions per MMA)
+// D[128 x N] (+)= A * B^T for one weight chunk; the descriptors advance by adding to their address field
 __device__ __forceinline__ void dm_issue_chunk(uint32_t tmem_d, uint32_t a_base, uint32_t a_part, uint32_t b_base,
                                                uint32_t b_part, int N, int ksteps, bool accumulate_first) {
   const uint32_t idesc = instr_desc_f16(DM_ROWS, N);
@@ -254,8 +248,8 @@ __device__ __forceinline__ void dm_issue_chunk(uint32_t tmem_d, uint32_t a_base,
   }
 }
 
-// The producer's walk over (pair of tiles, GEMM, tile slot, chunk): GEMM q of slot 0, then GEMM q of slot 1, then q+1 ...
-// so that slot 1's MMAs run while group 0 turns slot 0's accumulator into its next operand, and vice versa.
+// The walk over (pair of tiles, GEMM, tile slot, chunk) shared by the TMA thread and the MMA thread: GEMM q of slot 0,
+// then GEMM q of slot 1, then q+1 ..., so that one slot's MMAs run while the other slot's group is in its epilogue.
 struct DmWalk {
   int pair, q, s, ci;
   __device__ __forceinline__ bool valid(int n_pairs) const { return pair < n_pairs; }
@@ -271,26 +265,36 @@ struct DmWalk {
   }
 };
 
-// Warp-specialised, two tiles in flight: the PRODUCER warp streams the weight chunks (cp.async ring) and issues every
-// MMA as soon as its operands exist; two EPILOGUE groups of 8 warps each own one tile slot (its activation buffer in
-// shared memory, its 256 TMEM columns) and turn accumulators into the next GEMM's A operand or into outputs.  Per
-// slot, two mbarriers that flip once per GEMM:
-//   a_ready[s]   (256 arrivals): the A operand of the slot's next GEMM is in shared memory      group s -> producer
-//   acc_ready[s] (tcgen05.commit): the accumulator is complete and the activation buffer free   producer -> group s
+__device__ __forceinline__ void dm_group_barrier(int grp) {  // the 256 threads of one epilogue group
+  asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "n"(DM_GROUP_THREADS) : "memory");
+}
+
+// Warp-specialised, two 128-point tiles in flight per CTA:
+//   TMA thread     streams the weight chunks of the GEMM sequence through the ring (cp.async.bulk, s_full / s_done)
+//   MMA thread     issues every tcgen05.mma as soon as its operands exist and commits completions to mbarriers
+//   2 groups x 8 warps   own one tile slot each: its activation buffer (shared memory) and its 256 TMEM columns
+// Per tile: trunk GEMM -> cols A; ReLU(trunk + b0) -> sA ONCE, it is the A operand of EVERY head's layer 1; layer-1
+// GEMMs alternate between cols B and cols A (the trunk's columns are dead once sA exists); a head's last layer
+// (W -> k <= 48 outputs) runs on the CUDA cores inside the epilogue, in fp32, straight from the accumulator: as an MMA
+// it cost as many instructions as layer 1 (the tensor core's time per instruction is set by the 128-row A operand,
+// not by N) plus a split / store / hand-off round trip.
+// mbarriers per slot: a_ready (256 arrivals: X tile or sA written), acc_ready[2] (tcgen05.commit, GEMMs alternate
+// between the two so that a completion is never overtaken by the next one on the same barrier), cols_free (256
+// arrivals: head h's accumulator has been consumed, head h+2 may overwrite it).
 __global__ void __launch_bounds__(DM_THREADS, 1)
 deform_mlp_kernel(DmDev a, DmPlan pl) {
   extern __shared__ __align__(128) unsigned char dm_smem[];
-  __shared__ uint64_t s_done[DM_SLOTS];  // MMAs of the chunk in ring slot i have completed
-  __shared__ uint64_t s_full[DM_SLOTS];  // the chunk's bytes have arrived in ring slot i (TMA transaction count)
-  __shared__ uint64_t s_acc_ready[2], s_a_ready[2];
+  __shared__ uint64_t s_done[DM_SLOTS], s_full[DM_SLOTS];
+  __shared__ uint64_t s_acc_ready[2][2], s_a_ready[2], s_cols_free[2];
   __shared__ uint32_t s_tmem;
   __shared__ float s_bias[(1 + FDLS_DEFORM_MAX_HEADS) * 128];  // b0, then b1 of every head
   __shared__ int s_gemm_first[DM_MAX_GEMMS], s_gemm_count[DM_MAX_GEMMS];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int W = a.W, G = a.G;
   const uint32_t x_part = (uint32_t)(G / 8) * DM_ROWS * 16, a_part = (uint32_t)(W / 8) * DM_ROWS * 16;
-  char* sW = reinterpret_cast<char*>(dm_smem) + 2 * PARTS * a_part;  // behind the two activation buffers
-  const int n_gemms = 1 + 2 * a.H;
+  char* sW = reinterpret_cast<char*>(dm_smem) + 2 * PARTS * a_part;              // behind the two activation buffers
+  float* s_part = reinterpret_cast<float*>(sW + (size_t)DM_SLOTS * DM_CHUNK_BYTES);  // [2 groups][128][DM_OUT_BLOCK]
+  const int n_gemms = 1 + a.H;
 
   if (warp == 0) tmem_alloc<512>(&s_tmem);
   if (tid == 0) {
@@ -299,8 +303,10 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
       mbar_init(&s_full[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&s_acc_ready[i], 1);
+      mbar_init(&s_acc_ready[i][0], 1);
+      mbar_init(&s_acc_ready[i][1], 1);
       mbar_init(&s_a_ready[i], DM_GROUP_THREADS);
+      mbar_init(&s_cols_free[i], DM_GROUP_THREADS);
     }
     fence_mbar_init();
     int q = -1;
@@ -325,47 +331,47 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
   const int my_tiles = blockIdx.x < n_tiles ? (n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
   const int n_pairs = (my_tiles + 1) / 2;
 
-  if (warp == DM_EPI_THREADS / 32) {
-    // =================================================== PRODUCER ===================================================
-    // One thread: a chunk is ONE TMA bulk copy (cp.async.bulk, completion in bytes on s_full[slot]) and 3 x ksteps MMAs.
-    // (A cp.async loop over the warp's lanes cost ~300 instructions per chunk and made this warp, not the tensor
-    // pipe, the bound of the kernel.)
+  if (warp == DM_EPI_THREADS / 32 + 1) {
+    // ===================================================== TMA =====================================================
     if (lane == 0) {
-      DmWalk pf = {0, 0, 0, 0}, cur = {0, 0, 0, 0};
-      long long pf_step = 0;
-      auto prefetch = [&]() {  // copy the chunk `pf` points at into ring slot pf_step % SLOTS
-        if (pf.valid(n_pairs)) {
-          const DmChunk& ch = pl.c[s_gemm_first[pf.q] + pf.ci];
-          uint64_t* bar = &s_full[pf_step % DM_SLOTS];
-          mbar_expect_tx(bar, ch.bytes);
-          bulk_copy_g2s(sW + (size_t)(pf_step % DM_SLOTS) * DM_CHUNK_BYTES, a.prep + ch.off, ch.bytes, bar);
-          pf.next(s_gemm_count, n_gemms, my_tiles);
-        }
-        ++pf_step;
-      };
-      for (int i = 0; i < DM_AHEAD; ++i) prefetch();
-      uint32_t gemm_no[2] = {0, 0};  // GEMMs started per slot
+      DmWalk w = {0, 0, 0, 0};
+      for (long long p = 0; w.valid(n_pairs); ++p) {
+        const int slot = (int)(p % DM_SLOTS);
+        if (p >= DM_SLOTS) mbar_wait(&s_done[slot], (uint32_t)(((p - DM_SLOTS) / DM_SLOTS) & 1));  // its MMAs are done
+        const DmChunk& ch = pl.c[s_gemm_first[w.q] + w.ci];
+        mbar_expect_tx(&s_full[slot], ch.bytes);
+        bulk_copy_g2s(sW + (size_t)slot * DM_CHUNK_BYTES, a.prep + ch.off, ch.bytes, &s_full[slot]);
+        w.next(s_gemm_count, n_gemms, my_tiles);
+      }
+    }
+  } else if (warp == DM_EPI_THREADS / 32) {
+    // ===================================================== MMA =====================================================
+    if (lane == 0) {
+      DmWalk cur = {0, 0, 0, 0};
+      uint32_t n_a[2] = {0, 0}, n_free[2] = {0, 0}, n_acc[2][2] = {{0, 0}, {0, 0}};
+      (void)n_acc;
       for (long long g = 0; cur.valid(n_pairs); ++g) {
         const DmChunk& ch = pl.c[s_gemm_first[cur.q] + cur.ci];
-        const int s = cur.s;
-        // refill the ring: slot (g + AHEAD) % SLOTS held chunk g + AHEAD - SLOTS, whose MMAs must have completed
-        if (g >= DM_SLOTS - DM_AHEAD)
-          mbar_wait(&s_done[(g + DM_AHEAD) % DM_SLOTS], (uint32_t)(((g + DM_AHEAD - DM_SLOTS) / DM_SLOTS) & 1));
-        prefetch();
+        const int s = cur.s, q = cur.q;  // q = 0: trunk; q = h + 1: layer 1 of head h
         mbar_wait(&s_full[g % DM_SLOTS], (uint32_t)((g / DM_SLOTS) & 1));  // chunk g has landed
-        if (ch.first) {  // this GEMM's A operand: written by group s (fenced by its threads before they arrived)
-          mbar_wait(&s_a_ready[s], gemm_no[s] & 1);
-          ++gemm_no[s];
+        if (ch.first) {
+          if (q <= 1) {  // the X tile (trunk) or sA (first head) has been written by the slot's group
+            mbar_wait(&s_a_ready[s], n_a[s] & 1);
+            ++n_a[s];
+          } else if (q >= 3) {  // head h = q - 1 >= 2 overwrites the accumulator head h - 2 was read from
+            mbar_wait(&s_cols_free[s], n_free[s] & 1);
+            ++n_free[s];
+          }
         }
         tc_fence_after_sync();
         const uint32_t a_base = smem_u32(dm_smem) + (uint32_t)s * PARTS * a_part;  // trunk: the X tile aliases it
-        const uint32_t a_prt = ch.kind == DM_KIND_TRUNK ? x_part : a_part;
-        const uint32_t d_col = (uint32_t)s * 256u + (ch.kind == DM_KIND_TRUNK ? 0u : (uint32_t)W);
-        const uint32_t b_base = smem_u32(sW + (size_t)(g % DM_SLOTS) * DM_CHUNK_BYTES);
-        dm_issue_chunk(tmem + d_col, a_base + (uint32_t)ch.slab0 * DM_ROWS * 16, a_prt, b_base,
-                       (uint32_t)ch.slabs * ch.N * 16, ch.N, ch.slabs / 2, !ch.first);
+        const uint32_t a_prt = q == 0 ? x_part : a_part;
+        const uint32_t d_col = (uint32_t)s * 256u + ((q & 1) ? (uint32_t)W : 0u);  // trunk, heads 1, 3, ..: cols A
+        dm_issue_chunk(tmem + d_col, a_base + (uint32_t)ch.slab0 * DM_ROWS * 16, a_prt,
+                       smem_u32(sW + (size_t)(g % DM_SLOTS) * DM_CHUNK_BYTES), (uint32_t)ch.slabs * ch.N * 16, ch.N,
+                       ch.slabs / 2, !ch.first);
         mma_commit(&s_done[g % DM_SLOTS]);
-        if (ch.last) mma_commit(&s_acc_ready[s]);
+        if (ch.last) mma_commit(&s_acc_ready[s][q & 1]);
         cur.next(s_gemm_count, n_gemms, my_tiles);
       }
     }
@@ -377,63 +383,20 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
     const int half = eid >> 7;               // which half of the columns / slabs this thread takes
     char* sA = reinterpret_cast<char*>(dm_smem) + (size_t)grp * PARTS * a_part;
     char* sX = sA;  // the input tile is dead once the trunk GEMM has completed, which is when sA is first written
+    float* part = s_part + (size_t)grp * DM_ROWS * DM_OUT_BLOCK;
     const uint32_t tbase = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)grp * 256u;  // lane quadrant warp % 4
-    uint32_t gemm = 0;  // accumulators consumed so far
-    auto operand_ready = [&]() {  // my part of the next GEMM's A operand is written
-      fence_proxy_async();
-      mbar_arrive(&s_a_ready[grp]);
-    };
-    auto wait_acc = [&]() {
-      mbar_wait(&s_acc_ready[grp], gemm & 1);
-      ++gemm;
+    uint32_t n_acc[2] = {0, 0};  // completions consumed on each of the slot's two accumulator barriers
+    auto wait_acc = [&](int q) {
+      mbar_wait(&s_acc_ready[grp][q & 1], n_acc[q & 1] & 1);
+      ++n_acc[q & 1];
       tc_fence_after_sync();
     };
-    // TMEM columns [col, col + W) of the slot + bias, ReLU -> sA; this thread: W/2 columns of its point
-    auto relu_to_A = [&](uint32_t col, const float* __restrict__ bias) {
-      const int c0 = half * (W / 2);
-      for (int c = c0; c < c0 + W / 2; c += 32) {
-        float v[32];
-        tmem_ld32(tbase + col + c, v);
-#pragma unroll
-        for (int sl = 0; sl < 4; ++sl) {
-          float w8[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) w8[e] = fmaxf(v[sl * 8 + e] + bias[c + sl * 8 + e], 0.f);
-          store_row8_split(sA + (size_t)(c / 8 + sl) * DM_ROWS * 16 + prow * 16, a_part, w8);
-        }
-      }
-      tc_fence_before_sync();
-    };
-    auto write_out = [&](int h, int row) {  // the group's first four warps (half 0); the outputs alias the hidden columns
-      const DmHeadDev& hd = a.head[h];
-      float y[48];
-      for (int c = 0; c < hd.npad; c += 8) {
-        float v[8];
-        tmem_ld8(tbase + W + c, v);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) y[c + e] = v[e];
-      }
-      tc_fence_before_sync();
-      if (row >= a.P) return;
-      float nrm = 0.f;
-      for (int e = 0; e < hd.k; ++e) {
-        float t = y[e] + __ldg(hd.b2 + e);
-        if (hd.base) t = hd.base[(size_t)row * hd.k + e] + t;
-        if (hd.act == FDLS_DEFORM_ACT_EXP) t = expf(t);
-        else if (hd.act == FDLS_DEFORM_ACT_SIGMOID) t = 1.f / (1.f + expf(-t));
-        y[e] = t;
-        nrm += t * t;
-      }
-      if (hd.act == FDLS_DEFORM_ACT_NORMALIZE) {
-        const float inv = 1.f / fmaxf(sqrtf(nrm), 1e-12f);
-        for (int e = 0; e < hd.k; ++e) y[e] *= inv;
-      }
-      for (int e = 0; e < hd.k; ++e) hd.out[(size_t)row * hd.k + e] = y[e];
-    };
+    const int c0 = half * (W / 2);
 
     for (int t = grp; t < my_tiles; t += 2) {
       const int row = ((int)blockIdx.x + t * (int)gridDim.x) * DM_ROWS + prow;
-      // ---- X tile (aliases sA): every MMA that read sA for the previous tile has completed (last wait_acc below)
+      // ---- X tile (aliases sA): every MMA that read sA for the previous tile has completed (its accumulators were
+      // all waited for below)
       for (int slab = half; slab < G / 8; slab += 2) {
         float v[8];
         if (row < a.P) {
@@ -446,18 +409,82 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
         }
         store_row8_split(sX + (size_t)slab * DM_ROWS * 16 + prow * 16, x_part, v);
       }
-      operand_ready();  // trunk GEMM may start
-      for (int h = 0; h < a.H; ++h) {
-        wait_acc();  // trunk (h = 0) or the previous head's layer 2: its accumulator is complete and sA is free
-        if (h > 0 && half == 0) write_out(h - 1, row);  // before layer 1 of head h overwrites these columns
-        relu_to_A(0, s_bias);
-        operand_ready();  // layer 1 of head h
-        wait_acc();       // layer 1
-        relu_to_A((uint32_t)W, s_bias + (1 + h) * 128);
-        operand_ready();  // layer 2 of head h (its output aliases the hidden columns just consumed)
+      fence_proxy_async();
+      mbar_arrive(&s_a_ready[grp]);  // trunk GEMM may start
+      // ---- trunk accumulator (cols A) + b0, ReLU -> sA: the A operand of every head's first layer
+      wait_acc(0);
+      for (int c = c0; c < c0 + W / 2; c += 32) {
+        float v[32];
+        tmem_ld32(tbase + c, v);
+#pragma unroll
+        for (int sl = 0; sl < 4; ++sl) {
+          float w8[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) w8[e] = fmaxf(v[sl * 8 + e] + s_bias[c + sl * 8 + e], 0.f);
+          store_row8_split(sA + (size_t)(c / 8 + sl) * DM_ROWS * 16 + prow * 16, a_part, w8);
+        }
       }
-      wait_acc();  // layer 2 of the last head
-      if (half == 0) write_out(a.H - 1, row);
+      tc_fence_before_sync();
+      fence_proxy_async();
+      mbar_arrive(&s_a_ready[grp]);  // layer 1 of heads 0 and 1 may start (cols B, cols A)
+      // ---- per head: hidden = ReLU(acc + b1); out = act(base + hidden W2^T + b2), DM_OUT_BLOCK outputs per pass
+      for (int h = 0; h < a.H; ++h) {
+        const DmHeadDev& hd = a.head[h];
+        wait_acc(h + 1);
+        const uint32_t col = ((h + 1) & 1) ? (uint32_t)W : 0u;
+        const float* b1 = s_bias + (1 + h) * 128;
+        for (int e0 = 0; e0 < hd.k; e0 += DM_OUT_BLOCK) {
+          float acc[DM_OUT_BLOCK];
+#pragma unroll
+          for (int e = 0; e < DM_OUT_BLOCK; ++e) acc[e] = 0.f;
+          for (int c = c0; c < c0 + W / 2; c += 32) {
+            float v[32];
+            tmem_ld32(tbase + col + c, v);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + b1[c + j], 0.f);
+#pragma unroll
+            for (int e = 0; e < DM_OUT_BLOCK; ++e) {
+              if (e0 + e < hd.k) {  // warp-uniform
+                const float4* wr = reinterpret_cast<const float4*>(hd.w2 + (size_t)(e0 + e) * W + c);
+#pragma unroll
+                for (int j4 = 0; j4 < 8; ++j4) {
+                  const float4 wv = __ldg(wr + j4);  // same address in every lane: one L1 broadcast
+                  acc[e] += v[4 * j4] * wv.x + v[4 * j4 + 1] * wv.y + v[4 * j4 + 2] * wv.z + v[4 * j4 + 3] * wv.w;
+                }
+              }
+            }
+          }
+          // the two halves of a point's hidden vector live in two threads of different warps: combine through shared
+          dm_group_barrier(grp);  // the previous pass's partial sums have been read
+          if (half == 1) {
+#pragma unroll
+            for (int e = 0; e < DM_OUT_BLOCK; ++e) part[prow * DM_OUT_BLOCK + e] = acc[e];
+          }
+          dm_group_barrier(grp);
+          if (half == 0 && row < a.P) {
+            float y[DM_OUT_BLOCK];
+            float nrm = 0.f;
+#pragma unroll
+            for (int e = 0; e < DM_OUT_BLOCK; ++e) {
+              y[e] = 0.f;
+              if (e0 + e < hd.k) {
+                float tv = acc[e] + part[prow * DM_OUT_BLOCK + e] + __ldg(hd.b2 + e0 + e);
+                if (hd.base) tv = hd.base[(size_t)row * hd.k + e0 + e] + tv;
+                if (hd.act == FDLS_DEFORM_ACT_EXP) tv = expf(tv);
+                else if (hd.act == FDLS_DEFORM_ACT_SIGMOID) tv = 1.f / (1.f + expf(-tv));
+                y[e] = tv;
+                nrm += tv * tv;
+              }
+            }
+            const float inv = hd.act == FDLS_DEFORM_ACT_NORMALIZE ? 1.f / fmaxf(sqrtf(nrm), 1e-12f) : 1.f;  // k <= 8
+#pragma unroll
+            for (int e = 0; e < DM_OUT_BLOCK; ++e)
+              if (e0 + e < hd.k) hd.out[(size_t)row * hd.k + e0 + e] = y[e] * inv;
+          }
+        }
+        tc_fence_before_sync();
+        if (h + 2 < a.H) mbar_arrive(&s_cols_free[grp]);  // head h + 2 may overwrite this accumulator
+      }
     }
   }
   tc_fence_before_sync();
@@ -467,7 +494,8 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
 
 static size_t dm_smem_bytes(int G, int W) {
   const int K = G > W ? G : W;  // the input tile aliases the activation buffer
-  return (size_t)2 * PARTS * (K / 8) * DM_ROWS * 16 + (size_t)DM_SLOTS * DM_CHUNK_BYTES;  // two tile slots
+  return (size_t)2 * PARTS * (K / 8) * DM_ROWS * 16 + (size_t)DM_SLOTS * DM_CHUNK_BYTES +  // two tile slots, ring,
+         (size_t)2 * DM_ROWS * DM_OUT_BLOCK * sizeof(float);                                   // partial sums
 }
 
 size_t deform_prep_bytes(const FdlsDeformArgs* a) {
@@ -490,7 +518,6 @@ int deform_prepare(const FdlsDeformArgs* a, cudaStream_t st) {
   for (int h = 0; h < a->H; ++h) {
     if (!a->head[h].w1 || !a->head[h].w2) return FDLS_EINVAL;
     run(a->head[h].w1, a->W, a->W, a->W, DM_KIND_HIDDEN, h);
-    run(a->head[h].w2, a->head[h].k, pl.npad[h], a->W, DM_KIND_OUT, h);
   }
   return cudaGetLastError() == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
 }
@@ -507,8 +534,8 @@ int deform_forward(const FdlsDeformArgs* a, cudaStream_t st) {
   d.feat = a->feat; d.b0 = a->b0; d.prep = (const char*)a->prep;
   for (int h = 0; h < a->H; ++h) {
     const FdlsDeformHead& s = a->head[h];
-    if (!s.b1 || !s.b2 || !s.out) return FDLS_EINVAL;
-    d.head[h] = {s.b1, s.b2, s.base, s.out, s.k, s.act, pl.npad[h]};
+    if (!s.b1 || !s.w2 || !s.b2 || !s.out) return FDLS_EINVAL;
+    d.head[h] = {s.b1, s.w2, s.b2, s.base, s.out, s.k, s.act};
   }
   const size_t smem = dm_smem_bytes(a->G, a->W);
   static SmemOptIn optin;
