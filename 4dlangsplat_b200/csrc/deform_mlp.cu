@@ -145,10 +145,13 @@ struct DmPlan {
   int n_chunks;
   int npad[FDLS_DEFORM_MAX_HEADS];
   size_t total_bytes;
+  int gemm_first[1 + FDLS_DEFORM_MAX_HEADS], gemm_count[1 + FDLS_DEFORM_MAX_HEADS];  // chunks of GEMM q (consecutive)
+  uint32_t w2_off[FDLS_DEFORM_MAX_HEADS];  // last-layer weights, fp32 [k rounded up to 4][W], zero rows behind k
   DmChunk c[DM_MAX_CHUNKS];
 };
 
 static int dm_npad(int k) { return ((k + 15) / 16) * 16; }
+static int dm_kpad(int k) { return (k + 3) & ~3; }
 
 static int dm_make_plan(const FdlsDeformArgs* a, DmPlan* pl) {
   if (!a || a->G < 16 || a->G > 128 || (a->G % 16) || (a->W != 64 && a->W != 128) || a->H < 1 ||
@@ -177,10 +180,23 @@ static int dm_make_plan(const FdlsDeformArgs* a, DmPlan* pl) {
   for (int h = 0; h < a->H; ++h) {
     const int k = a->head[h].k;
     if (k < 1 || k > 48) return FDLS_EUNSUPPORTED;
+    if (a->head[h].act == FDLS_DEFORM_ACT_NORMALIZE && k > 4) return FDLS_EUNSUPPORTED;  // normalised within one pass
     pl->npad[h] = dm_npad(k);
     if (!add(DM_KIND_HIDDEN, h, a->W, a->W)) return FDLS_EUNSUPPORTED;
   }
+  for (int h = 0; h < a->H; ++h) {
+    pl->w2_off[h] = (uint32_t)off;
+    off += align_up((size_t)dm_kpad(a->head[h].k) * a->W * sizeof(float), 128);
+  }
   pl->total_bytes = off;
+  for (int c = 0, q = -1; c < pl->n_chunks; ++c) {
+    if (pl->c[c].first) {
+      ++q;
+      pl->gemm_first[q] = c;
+      pl->gemm_count[q] = 0;
+    }
+    ++pl->gemm_count[q];
+  }
   return FDLS_OK;
 }
 
@@ -219,34 +235,7 @@ constexpr int DM_EPI_THREADS = 2 * DM_GROUP_THREADS;       // two groups = two t
 constexpr int DM_THREADS = DM_EPI_THREADS + 64;            // + the MMA-issue warp and the TMA warp (one thread each)
 constexpr int DM_SLOTS = 5;                                // weight-chunk ring
 constexpr int DM_MAX_GEMMS = 1 + FDLS_DEFORM_MAX_HEADS;    // trunk + one layer-1 GEMM per head
-constexpr int DM_OUT_BLOCK = 8;                            // outputs of a head's last layer handled per pass
-
-// D[128 x N] (+)= A * B^T for one weight chunk; the descriptors advance by adding to their address field
-__device__ __forceinline__ void dm_issue_chunk(uint32_t tmem_d, uint32_t a_base, uint32_t a_part, uint32_t b_base,
-                                               uint32_t b_part, int N, int ksteps, bool accumulate_first) {
-  const uint32_t idesc = instr_desc_f16(DM_ROWS, N);
-  const uint32_t a_slab = DM_ROWS * 16, b_slab = (uint32_t)N * 16;
-  uint64_t da[PARTS], db[PARTS];
-#pragma unroll
-  for (int p = 0; p < PARTS; ++p) {
-    da[p] = smem_desc(a_base + p * a_part, a_slab, 128);
-    db[p] = smem_desc(b_base + p * b_part, b_slab, 128);
-  }
-  const uint64_t a_inc = (2 * a_slab) >> 4, b_inc = (2 * b_slab) >> 4;  // one K = 16 step, in 16-byte units
-  bool acc = accumulate_first;
-  for (int ks = 0; ks < ksteps; ++ks) {
-#pragma unroll
-    for (int t = 0; t < DM_NTERMS; ++t) {
-      mma_f16(tmem_d, da[DM_TERMS[t][0]], db[DM_TERMS[t][1]], idesc, acc);
-      acc = true;
-    }
-#pragma unroll
-    for (int p = 0; p < PARTS; ++p) {
-      da[p] += a_inc;
-      db[p] += b_inc;
-    }
-  }
-}
+constexpr int DM_OUT_BLOCK = 4;                            // outputs of a head's last layer handled per pass
 
 // The walk over (pair of tiles, GEMM, tile slot, chunk) shared by the TMA thread and the MMA thread: GEMM q of slot 0,
 // then GEMM q of slot 1, then q+1 ..., so that one slot's MMAs run while the other slot's group is in its epilogue.
@@ -287,8 +276,7 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
   __shared__ uint64_t s_done[DM_SLOTS], s_full[DM_SLOTS];
   __shared__ uint64_t s_acc_ready[2][2], s_a_ready[2], s_cols_free[2];
   __shared__ uint32_t s_tmem;
-  __shared__ float s_bias[(1 + FDLS_DEFORM_MAX_HEADS) * 128];  // b0, then b1 of every head
-  __shared__ int s_gemm_first[DM_MAX_GEMMS], s_gemm_count[DM_MAX_GEMMS];
+  __shared__ __align__(16) float s_bias[(1 + FDLS_DEFORM_MAX_HEADS) * 128];  // b0, then b1 of every head
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int W = a.W, G = a.G;
   const uint32_t x_part = (uint32_t)(G / 8) * DM_ROWS * 16, a_part = (uint32_t)(W / 8) * DM_ROWS * 16;
@@ -309,15 +297,6 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
       mbar_init(&s_cols_free[i], DM_GROUP_THREADS);
     }
     fence_mbar_init();
-    int q = -1;
-    for (int c = 0; c < pl.n_chunks; ++c) {  // chunks of one GEMM are consecutive in the plan
-      if (pl.c[c].first) {
-        ++q;
-        s_gemm_first[q] = c;
-        s_gemm_count[q] = 0;
-      }
-      ++s_gemm_count[q];
-    }
   }
   for (int i = tid; i < W; i += DM_THREADS) s_bias[i] = a.b0[i];
   for (int h = 0; h < a.H; ++h)
@@ -333,47 +312,75 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
 
   if (warp == DM_EPI_THREADS / 32 + 1) {
     // ===================================================== TMA =====================================================
-    if (lane == 0) {
-      DmWalk w = {0, 0, 0, 0};
-      for (long long p = 0; w.valid(n_pairs); ++p) {
-        const int slot = (int)(p % DM_SLOTS);
-        if (p >= DM_SLOTS) mbar_wait(&s_done[slot], (uint32_t)(((p - DM_SLOTS) / DM_SLOTS) & 1));  // its MMAs are done
-        const DmChunk& ch = pl.c[s_gemm_first[w.q] + w.ci];
-        mbar_expect_tx(&s_full[slot], ch.bytes);
-        bulk_copy_g2s(sW + (size_t)slot * DM_CHUNK_BYTES, a.prep + ch.off, ch.bytes, &s_full[slot]);
-        w.next(s_gemm_count, n_gemms, my_tiles);
+    // the whole warp walks the sequence (every value stays warp-uniform, i.e. in uniform registers); one elected lane
+    // issues the copies
+    DmWalk w = {0, 0, 0, 0};
+    uint32_t ring = 0, lap = 0;
+    while (w.valid(n_pairs)) {
+      if (lap) mbar_wait(&s_done[ring], (lap - 1) & 1);  // the MMAs of the chunk that had this ring slot are done
+      const DmChunk& ch = pl.c[pl.gemm_first[w.q] + w.ci];
+      if (elect_one()) {
+        mbar_expect_tx(&s_full[ring], ch.bytes);
+        bulk_copy_g2s(sW + (size_t)ring * DM_CHUNK_BYTES, a.prep + ch.off, ch.bytes, &s_full[ring]);
       }
+      __syncwarp();
+      if (++ring == DM_SLOTS) {
+        ring = 0;
+        ++lap;
+      }
+      w.next(pl.gemm_count, n_gemms, my_tiles);
     }
   } else if (warp == DM_EPI_THREADS / 32) {
     // ===================================================== MMA =====================================================
-    if (lane == 0) {
-      DmWalk cur = {0, 0, 0, 0};
-      uint32_t n_a[2] = {0, 0}, n_free[2] = {0, 0}, n_acc[2][2] = {{0, 0}, {0, 0}};
-      (void)n_acc;
-      for (long long g = 0; cur.valid(n_pairs); ++g) {
-        const DmChunk& ch = pl.c[s_gemm_first[cur.q] + cur.ci];
-        const int s = cur.s, q = cur.q;  // q = 0: trunk; q = h + 1: layer 1 of head h
-        mbar_wait(&s_full[g % DM_SLOTS], (uint32_t)((g / DM_SLOTS) & 1));  // chunk g has landed
-        if (ch.first) {
-          if (q <= 1) {  // the X tile (trunk) or sA (first head) has been written by the slot's group
-            mbar_wait(&s_a_ready[s], n_a[s] & 1);
-            ++n_a[s];
-          } else if (q >= 3) {  // head h = q - 1 >= 2 overwrites the accumulator head h - 2 was read from
-            mbar_wait(&s_cols_free[s], n_free[s] & 1);
-            ++n_free[s];
-          }
+    // Same shape: warp-uniform walk, elected issue.  (Run by a single lane, the loop cost ~300 dependent scalar
+    // instructions per chunk -- register -> uniform-register moves around every descriptor -- and that one thread, not
+    // the tensor core, set the kernel's time.)
+    DmWalk cur = {0, 0, 0, 0};
+    uint32_t ph_a = 0, ph_free = 0, ring = 0, ring_phase = 0;  // phase bits, one per tile slot
+    const uint32_t act0 = smem_u32(dm_smem), ring0 = smem_u32(sW);
+    while (cur.valid(n_pairs)) {
+      const DmChunk& ch = pl.c[pl.gemm_first[cur.q] + cur.ci];
+      const uint32_t s = (uint32_t)cur.s, q = (uint32_t)cur.q;  // q = 0: trunk; q = h + 1: layer 1 of head h
+      mbar_wait(&s_full[ring], ring_phase);  // the chunk has landed
+      if (ch.first) {
+        if (q <= 1) {  // the X tile (trunk) or sA (first head) has been written by the slot's group
+          mbar_wait(&s_a_ready[s], (ph_a >> s) & 1);
+          ph_a ^= 1u << s;
+        } else if (q >= 3) {  // head h = q - 1 >= 2 overwrites the accumulator head h - 2 was read from
+          mbar_wait(&s_cols_free[s], (ph_free >> s) & 1);
+          ph_free ^= 1u << s;
         }
-        tc_fence_after_sync();
-        const uint32_t a_base = smem_u32(dm_smem) + (uint32_t)s * PARTS * a_part;  // trunk: the X tile aliases it
-        const uint32_t a_prt = q == 0 ? x_part : a_part;
-        const uint32_t d_col = (uint32_t)s * 256u + ((q & 1) ? (uint32_t)W : 0u);  // trunk, heads 1, 3, ..: cols A
-        dm_issue_chunk(tmem + d_col, a_base + (uint32_t)ch.slab0 * DM_ROWS * 16, a_prt,
-                       smem_u32(sW + (size_t)(g % DM_SLOTS) * DM_CHUNK_BYTES), (uint32_t)ch.slabs * ch.N * 16, ch.N,
-                       ch.slabs / 2, !ch.first);
-        mma_commit(&s_done[g % DM_SLOTS]);
-        if (ch.last) mma_commit(&s_acc_ready[s][q & 1]);
-        cur.next(s_gemm_count, n_gemms, my_tiles);
       }
+      tc_fence_after_sync();
+      if (elect_one()) {
+        // descriptors as their low words (address >> 4 | LBO >> 4 << 16); a K = 16 step advances the address field
+        const uint32_t N = ch.N, a_prt = q == 0 ? x_part : a_part;  // the X tile aliases the activation buffer
+        const uint32_t idesc = instr_desc_f16(DM_ROWS, (int)N);
+        uint32_t da0 = ((act0 + s * PARTS * a_part + (uint32_t)ch.slab0 * DM_ROWS * 16) >> 4) | ((DM_ROWS * 16u >> 4) << 16);
+        uint32_t da1 = da0 + (a_prt >> 4);
+        uint32_t db0 = ((ring0 + ring * DM_CHUNK_BYTES) >> 4) | (N << 16);
+        uint32_t db1 = db0 + (uint32_t)ch.slabs * N;
+        const uint32_t d = tmem + s * 256u + ((q & 1) ? (uint32_t)W : 0u);  // trunk, heads 1, 3, ..: cols A
+        uint32_t acc = ch.first ? 0u : 1u;
+        for (int ks = ch.slabs >> 1; ks > 0; --ks) {
+          mma_f16_lo(d, da1, db0, idesc, acc);  // lo * hi, hi * lo, hi * hi: small terms first
+          mma_f16_lo(d, da0, db1, idesc, 1u);
+          mma_f16_lo(d, da0, db0, idesc, 1u);
+          acc = 1u;
+          da0 += 2 * DM_ROWS * 16 >> 4;
+          da1 += 2 * DM_ROWS * 16 >> 4;
+          db0 += 2 * N;
+          db1 += 2 * N;
+        }
+        mma_commit(&s_done[ring]);
+        if (ch.last) mma_commit(&s_acc_ready[s][q & 1]);
+      }
+      __syncwarp();
+      if (++ring == DM_SLOTS) {
+        ring = 0;
+        ring_phase ^= 1;
+      }
+      cur.next(pl.gemm_count, n_gemms, my_tiles);
     }
   } else {
     // =================================================== EPILOGUE ===================================================
@@ -420,7 +427,7 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
         for (int sl = 0; sl < 4; ++sl) {
           float w8[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) w8[e] = fmaxf(v[sl * 8 + e] + s_bias[c + sl * 8 + e], 0.f);
+          for (int e = 0; e < 8; ++e) w8[e] = fmaxf(v[sl * 8 + e] + s_bias[c + sl * 8 + e], 0.f);  // LDS.128 x 2
           store_row8_split(sA + (size_t)(c / 8 + sl) * DM_ROWS * 16 + prow * 16, a_part, w8);
         }
       }
@@ -430,53 +437,73 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
       // ---- per head: hidden = ReLU(acc + b1); out = act(base + hidden W2^T + b2), DM_OUT_BLOCK outputs per pass
       for (int h = 0; h < a.H; ++h) {
         const DmHeadDev& hd = a.head[h];
-        wait_acc(h + 1);
+        const int kpad = (hd.k + 3) & ~3;  // W2 is stored with zero rows up to a multiple of 4: no guards in the FMAs
         const uint32_t col = ((h + 1) & 1) ? (uint32_t)W : 0u;
-        const float* b1 = s_bias + (1 + h) * 128;
-        for (int e0 = 0; e0 < hd.k; e0 += DM_OUT_BLOCK) {
-          float acc[DM_OUT_BLOCK];
+        const float4* b1 = reinterpret_cast<const float4*>(s_bias + (1 + h) * 128);
+        for (int e0 = 0; e0 < kpad; e0 += DM_OUT_BLOCK) {
+          // canonical attribute of this pass: requested before the accumulator wait, consumed after the FMAs
+          float bs[DM_OUT_BLOCK];
 #pragma unroll
-          for (int e = 0; e < DM_OUT_BLOCK; ++e) acc[e] = 0.f;
-          for (int c = c0; c < c0 + W / 2; c += 32) {
-            float v[32];
-            tmem_ld32(tbase + col + c, v);
+          for (int e = 0; e < DM_OUT_BLOCK; ++e)
+            bs[e] = (half == 0 && row < a.P && hd.base && e0 + e < hd.k) ? __ldg(hd.base + (size_t)row * hd.k + e0 + e) : 0.f;
+          if (e0 == 0) wait_acc(h + 1);
+          float2 acc2[DM_OUT_BLOCK];  // (sum over even columns, sum over odd columns)
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j] + b1[c + j], 0.f);
+          for (int e = 0; e < DM_OUT_BLOCK; ++e) acc2[e] = make_float2(0.f, 0.f);
+          const float4* w2 = reinterpret_cast<const float4*>(hd.w2 + (size_t)e0 * W);
+          for (int c = c0; c < c0 + W / 2; c += 16) {
+            float v[16];
+            tmem_ld16(tbase + col + c, v);
+            float2 vp[8];
 #pragma unroll
-            for (int e = 0; e < DM_OUT_BLOCK; ++e) {
-              if (e0 + e < hd.k) {  // warp-uniform
-                const float4* wr = reinterpret_cast<const float4*>(hd.w2 + (size_t)(e0 + e) * W + c);
+            for (int j4 = 0; j4 < 4; ++j4) {
+              const float4 bv = b1[c / 4 + j4];
+              vp[2 * j4] = make_float2(fmaxf(v[4 * j4] + bv.x, 0.f), fmaxf(v[4 * j4 + 1] + bv.y, 0.f));
+              vp[2 * j4 + 1] = make_float2(fmaxf(v[4 * j4 + 2] + bv.z, 0.f), fmaxf(v[4 * j4 + 3] + bv.w, 0.f));
+            }
 #pragma unroll
-                for (int j4 = 0; j4 < 8; ++j4) {
-                  const float4 wv = __ldg(wr + j4);  // same address in every lane: one L1 broadcast
-                  acc[e] += v[4 * j4] * wv.x + v[4 * j4 + 1] * wv.y + v[4 * j4 + 2] * wv.z + v[4 * j4 + 3] * wv.w;
+            for (int ep = 0; ep < DM_OUT_BLOCK; ep += 2) {  // two outputs at a time: 8 loads in flight, then 16 FFMA2
+              float4 wv[2][4];
+#pragma unroll
+              for (int i = 0; i < 2; ++i)
+#pragma unroll
+                for (int j4 = 0; j4 < 4; ++j4) wv[i][j4] = __ldg(w2 + ((ep + i) * W + c) / 4 + j4);  // L1 broadcast
+#pragma unroll
+              for (int j4 = 0; j4 < 4; ++j4)
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                  acc2[ep + i] = ffma2(vp[2 * j4], make_float2(wv[i][j4].x, wv[i][j4].y), acc2[ep + i]);
+                  acc2[ep + i] = ffma2(vp[2 * j4 + 1], make_float2(wv[i][j4].z, wv[i][j4].w), acc2[ep + i]);
                 }
-              }
             }
           }
+          float acc[DM_OUT_BLOCK];
+#pragma unroll
+          for (int e = 0; e < DM_OUT_BLOCK; ++e) acc[e] = acc2[e].x + acc2[e].y;
           // the two halves of a point's hidden vector live in two threads of different warps: combine through shared
           dm_group_barrier(grp);  // the previous pass's partial sums have been read
           if (half == 1) {
-#pragma unroll
-            for (int e = 0; e < DM_OUT_BLOCK; ++e) part[prow * DM_OUT_BLOCK + e] = acc[e];
+            *reinterpret_cast<float4*>(part + prow * DM_OUT_BLOCK) = make_float4(acc[0], acc[1], acc[2], acc[3]);
           }
           dm_group_barrier(grp);
           if (half == 0 && row < a.P) {
+            const float4 p0 = *reinterpret_cast<const float4*>(part + prow * DM_OUT_BLOCK);
+            const float other[DM_OUT_BLOCK] = {p0.x, p0.y, p0.z, p0.w};
             float y[DM_OUT_BLOCK];
             float nrm = 0.f;
 #pragma unroll
             for (int e = 0; e < DM_OUT_BLOCK; ++e) {
               y[e] = 0.f;
               if (e0 + e < hd.k) {
-                float tv = acc[e] + part[prow * DM_OUT_BLOCK + e] + __ldg(hd.b2 + e0 + e);
-                if (hd.base) tv = hd.base[(size_t)row * hd.k + e0 + e] + tv;
+                float tv = acc[e] + other[e] + __ldg(hd.b2 + e0 + e);
+                if (hd.base) tv = bs[e] + tv;
                 if (hd.act == FDLS_DEFORM_ACT_EXP) tv = expf(tv);
                 else if (hd.act == FDLS_DEFORM_ACT_SIGMOID) tv = 1.f / (1.f + expf(-tv));
                 y[e] = tv;
                 nrm += tv * tv;
               }
             }
-            const float inv = hd.act == FDLS_DEFORM_ACT_NORMALIZE ? 1.f / fmaxf(sqrtf(nrm), 1e-12f) : 1.f;  // k <= 8
+            const float inv = hd.act == FDLS_DEFORM_ACT_NORMALIZE ? 1.f / fmaxf(sqrtf(nrm), 1e-12f) : 1.f;  // k <= 4
 #pragma unroll
             for (int e = 0; e < DM_OUT_BLOCK; ++e)
               if (e0 + e < hd.k) hd.out[(size_t)row * hd.k + e0 + e] = y[e] * inv;
@@ -518,6 +545,10 @@ int deform_prepare(const FdlsDeformArgs* a, cudaStream_t st) {
   for (int h = 0; h < a->H; ++h) {
     if (!a->head[h].w1 || !a->head[h].w2) return FDLS_EINVAL;
     run(a->head[h].w1, a->W, a->W, a->W, DM_KIND_HIDDEN, h);
+    const size_t row = (size_t)a->W * sizeof(float);
+    if (cudaMemsetAsync(prep + pl.w2_off[h], 0, dm_kpad(a->head[h].k) * row, st) != cudaSuccess ||
+        cudaMemcpyAsync(prep + pl.w2_off[h], a->head[h].w2, a->head[h].k * row, cudaMemcpyDeviceToDevice, st) != cudaSuccess)
+      return FDLS_ECUDA;
   }
   return cudaGetLastError() == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
 }
@@ -534,8 +565,8 @@ int deform_forward(const FdlsDeformArgs* a, cudaStream_t st) {
   d.feat = a->feat; d.b0 = a->b0; d.prep = (const char*)a->prep;
   for (int h = 0; h < a->H; ++h) {
     const FdlsDeformHead& s = a->head[h];
-    if (!s.b1 || !s.w2 || !s.b2 || !s.out) return FDLS_EINVAL;
-    d.head[h] = {s.b1, s.w2, s.b2, s.base, s.out, s.k, s.act};
+    if (!s.b1 || !s.b2 || !s.out) return FDLS_EINVAL;
+    d.head[h] = {s.b1, (const float*)(d.prep + pl.w2_off[h]), s.b2, s.base, s.out, s.k, s.act};
   }
   const size_t smem = dm_smem_bytes(a->G, a->W);
   static SmemOptIn optin;
