@@ -139,6 +139,8 @@ SYMBOLS = {
     "fdls_sort_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "fdls_sort_pairs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int,
                                   C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "fdls_sort_pairs_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int,
+                                         C.c_int, C.c_void_p]),
     "fdls_hexplane_forward": (C.c_int, [C.POINTER(FdlsHexArgs), C.c_void_p]),
     "fdls_hexplane_backward": (C.c_int, [C.POINTER(FdlsHexArgs), C.c_void_p]),
     "fdls_hexplane_pack": (C.c_int, [C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -31,6 +31,8 @@ size_t sort_scratch_bytes(long long n_max);
 int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
                const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes,
                cudaStream_t st);
+int sort_pairs_static(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
+                      const uint32_t* n_dev, int begin_bit, int end_bit, cudaStream_t st);
 int sort_prepare(long long n_max, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, cudaStream_t st);
 uint32_t* sort_hist(void* scratch);
 int sort_run(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
@@ -175,6 +177,7 @@ FDLS_API const char* fdls_strerror(int code) {
     case FDLS_EWORKSPACE: return "workspace too small";
     case FDLS_ECUDA: return "CUDA error";
     case FDLS_EUNSUPPORTED: return "unsupported configuration";
+    case FDLS_ELIMIT: return "size exceeds the fixed maximum of an allocation-free entry point";
     default: return "unknown error";
   }
 }
@@ -388,6 +391,12 @@ FDLS_API int fdls_sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_
   if (n_max < 0 || (n_max > 0 && (!keys_a || !keys_b || !vals_a || !vals_b || !scratch))) return FDLS_EINVAL;
   return sort_pairs(keys_a, keys_b, vals_a, vals_b, n_max, n_dev, begin_bit, end_bit, scratch, scratch_bytes,
                     (cudaStream_t)stream);
+}
+
+FDLS_API int fdls_sort_pairs_static(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,
+                                    int64_t n_max, const uint32_t* n_dev, int begin_bit, int end_bit, void* stream) {
+  if (n_max < 0 || (n_max > 0 && (!keys_a || !keys_b || !vals_a || !vals_b))) return FDLS_EINVAL;
+  return sort_pairs_static(keys_a, keys_b, vals_a, vals_b, n_max, n_dev, begin_bit, end_bit, (cudaStream_t)stream);
 }
 
 FDLS_API int fdls_hexplane_forward(const FdlsHexArgs* a, void* stream) {

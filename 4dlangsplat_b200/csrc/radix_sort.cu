@@ -367,4 +367,42 @@ int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* v
   return sort_run(keys_a, keys_b, vals_a, vals_b, n_max, n_dev, begin_bit, end_bit, scratch, scratch_bytes, false, st);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant (fdls_sort_pairs_static): the scratch of sort_pairs lives in a file-scope device array instead
+// of a caller-provided workspace, for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that
+// forbid cudaMalloc).  Every GPU that loads the library holds the array (8.0 MiB) until exit.  All calls on a device
+// share it: calls that overlap on the GPU (different streams) race.  sort_prepare zeroes the part a call uses, so the
+// previous call's contents never leak into the next.
+constexpr size_t RS_STATIC_BYTES =
+    ((size_t)RS_MAX_PASSES * RS_BINS * sizeof(uint32_t) + 32 * sizeof(uint32_t) +
+     (size_t)RS_MAX_PASSES * (FDLS_SORT_STATIC_MAX_PAIRS / (RS_THREADS * 8)) * RS_BINS * sizeof(uint32_t) + 255) / 256 * 256;
+static __device__ __align__(256) unsigned char g_rs_static_scratch[RS_STATIC_BYTES];
+
+// device address of the array on the CURRENT device (the symbol's name is a host-side stand-in, not a device pointer)
+static int rs_static_scratch(void** out) {
+  constexpr int MAX_DEVICES = 64;
+  static std::mutex mu;
+  static void* ptrs[MAX_DEVICES] = {};
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) return FDLS_ECUDA;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    if (cudaGetSymbolAddress(&p, g_rs_static_scratch) != cudaSuccess || !p) return FDLS_ECUDA;
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return FDLS_OK;
+}
+
+int sort_pairs_static(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
+                      const uint32_t* n_dev, int begin_bit, int end_bit, cudaStream_t st) {
+  if (n_max > FDLS_SORT_STATIC_MAX_PAIRS) return FDLS_ELIMIT;
+  if (sort_scratch_bytes(n_max) > RS_STATIC_BYTES) return FDLS_ELIMIT;  // cannot happen below the limit
+  void* scratch = nullptr;
+  int rc = rs_static_scratch(&scratch);
+  if (rc < 0) return rc;
+  return sort_pairs(keys_a, keys_b, vals_a, vals_b, n_max, n_dev, begin_bit, end_bit, scratch, RS_STATIC_BYTES, st);
+}
+
 }  // namespace fdls

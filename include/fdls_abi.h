@@ -37,6 +37,7 @@ extern "C" {
 #define FDLS_EWORKSPACE (-2)  /* a caller-provided workspace is too small */
 #define FDLS_ECUDA (-3)       /* a CUDA launch or API call failed; see cudaGetLastError */
 #define FDLS_EUNSUPPORTED (-4) /* e.g. F > FDLS_MAX_LANG_CHANNELS, or NUM_CHANNELS != 3 without colours */
+#define FDLS_ELIMIT (-5)      /* size beyond the fixed maximum of an allocation-free entry point */
 
 #define FDLS_MAX_LANG_CHANNELS 6 /* the reference is built with 3 (CLIP) or 6 (video) latents: scripts/train_eval.sh:3-4 */
 #define FDLS_TILE 16             /* cuda_rasterizer/config.h:18-19 */
@@ -224,6 +225,17 @@ size_t fdls_sort_scratch_bytes(int64_t n_max);
 int fdls_sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, int64_t n_max,
                     const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes,
                     void* stream);
+/* fdls_sort_pairs without a scratch argument and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  The scratch is a static device array inside the library, sized for
+ * n_max <= FDLS_SORT_STATIC_MAX_PAIRS (8.0 MiB, held by every GPU that loads the library until exit); larger n_max
+ * returns FDLS_ELIMIT.  Same arguments, result and return value as fdls_sort_pairs otherwise; the caller still owns
+ * the key / value double buffers.  Calls no cudaMalloc / cudaFree / allocating routine.  All calls on one device
+ * share the array (the part a call uses is zeroed on its stream first): calls that overlap on the GPU race, so
+ * serialise them on one stream or with events.  The calling thread's current device must own `stream`. */
+#define FDLS_SORT_STATIC_MAX_PAIRS 2097152
+int fdls_sort_pairs_static(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, int64_t n_max,
+                           const uint32_t* n_dev, int begin_bit, int end_bit, void* stream);
 
 /* ---- SURVEY 8f N1, first step: the HexPlane feature field that feeds the deformation network ----------------------
  * Replaces HexPlaneField.forward / get_density (scene/hexplane.py:145-170): normalize_aabb (:20-21), then per
