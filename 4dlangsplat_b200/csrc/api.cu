@@ -52,7 +52,9 @@ cudaError_t launch_render_fwd(int F, const uint2* ranges, const uint32_t* point_
 cudaError_t launch_render_bwd(int F, const uint2* ranges, const uint32_t* point_list, const float4* rec, int W, int H,
                               int gx, int gy, const float* bg, const float* final_T, const uint32_t* n_contrib,
                               const uint32_t* tile_max, const float* dpix, const float* dpix_F, const float* dpix_D,
-                              float* grad_rec, cudaStream_t st);
+                              float* grad_rec, const uint32_t* tile_order, cudaStream_t st);
+cudaError_t launch_bwd_prepare(float* grad_rec, size_t n_floats, const uint32_t* tile_max, int tiles, uint32_t* tile_order,
+                               cudaStream_t st);
 cudaError_t launch_render_bwd_shfl(int F, const uint2* ranges, const uint32_t* point_list, const float4* rec, int W,
                                    int H, int gx, int gy, const float* bg, const float* final_T,
                                    const uint32_t* n_contrib, const uint32_t* tile_max, const float* dpix,
@@ -342,17 +344,33 @@ FDLS_API int fdls_backward(const FdlsBwdArgs* a, void* stream) {
   ViewParams vp = make_view(a->viewmatrix, a->projmatrix, a->campos, a->background, a->W, a->H, a->tanfovx, a->tanfovy,
                             a->scale_modifier);
   rec(a->stage_events, 0, st);
-  if (cudaMemsetAsync(a->grad_ws, 0, (size_t)a->P * 16 * sizeof(float), st) != cudaSuccess) return FDLS_ECUDA;
+  // zero the gradient records; the same kernel orders the tiles deepest-first for render_bwd (the order goes into
+  // tile_cursor, a scratch array of the forward's binning that is dead once the forward has run)
+  static const bool use_order = [] {
+    const char* e = getenv("FDLS_TILE_ORDER");
+    return !(e && e[0] == '0');
+  }();
+  const bool render = a->num_rendered > 0 && b;
+  uint32_t* tile_order = render && use_order && a->bwd_algo != 1 ? (uint32_t*)(const_cast<char*>(im) + L.tile_cursor) : nullptr;
+  if (launch_bwd_prepare((float*)a->grad_ws, (size_t)a->P * 16, (const uint32_t*)(im + L.tile_max_contrib), gx * gy,
+                         tile_order, st) != cudaSuccess)
+    return FDLS_ECUDA;
   rec(a->stage_events, 1, st);
-  if (a->num_rendered > 0 && b) {
+  if (render) {
     const int F = a->include_feature ? a->F : 0;
-    auto* launch = a->bwd_algo == 1 ? launch_render_bwd_shfl : launch_render_bwd;
-    if (launch(F, (const uint2*)(im + L.ranges), (const uint32_t*)(b + L.vals), (const float4*)(g + L.rec),
-                          a->W, a->H, gx, gy, a->background, (const float*)(im + L.final_T),
-                          (const uint32_t*)(im + L.n_contrib), (const uint32_t*)(im + L.tile_max_contrib),
-                          a->dL_dout_color, a->dL_dout_language, a->dL_dout_depth, (float*)a->grad_ws,
-                          st) != cudaSuccess)
-      return FDLS_ECUDA;
+    cudaError_t e;
+    if (a->bwd_algo == 1)
+      e = launch_render_bwd_shfl(F, (const uint2*)(im + L.ranges), (const uint32_t*)(b + L.vals),
+                                 (const float4*)(g + L.rec), a->W, a->H, gx, gy, a->background,
+                                 (const float*)(im + L.final_T), (const uint32_t*)(im + L.n_contrib),
+                                 (const uint32_t*)(im + L.tile_max_contrib), a->dL_dout_color, a->dL_dout_language,
+                                 a->dL_dout_depth, (float*)a->grad_ws, st);
+    else
+      e = launch_render_bwd(F, (const uint2*)(im + L.ranges), (const uint32_t*)(b + L.vals), (const float4*)(g + L.rec),
+                            a->W, a->H, gx, gy, a->background, (const float*)(im + L.final_T),
+                            (const uint32_t*)(im + L.n_contrib), (const uint32_t*)(im + L.tile_max_contrib),
+                            a->dL_dout_color, a->dL_dout_language, a->dL_dout_depth, (float*)a->grad_ws, tile_order, st);
+    if (e != cudaSuccess) return FDLS_ECUDA;
   }
   rec(a->stage_events, 2, st);
   if (launch_preprocess_bwd(a, vp, (const uint8_t*)(g + L.clamped), (const float4*)a->grad_ws, st) != cudaSuccess)
