@@ -132,19 +132,22 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       const float test_T = T * (1 - alpha);
       if (test_T < 0.0001f) {
         done = true;
-        continue;
+        break;
       }
       const float4 c = s_rec[buf][2][j];  // g, b, l0, l1
-      C[0] += b.w * alpha * T;
-      C[1] += c.x * alpha * T;
-      C[2] += c.y * alpha * T;
+      // the reference forms (c * alpha) * T per channel (forward.cu:362-369); c * (alpha * T) is one multiply per pair
+      // instead of one per channel and differs by one rounding (2^-24 relative per term; images are held to 1e-5)
+      const float w = alpha * T;
+      C[0] = fmaf(b.w, w, C[0]);
+      C[1] = fmaf(c.x, w, C[1]);
+      C[2] = fmaf(c.y, w, C[2]);
       if (F > 0) {
         const float4 e = s_rec[buf][3][j];  // l2..l5
         const float l[6] = {c.z, c.w, e.x, e.y, e.z, e.w};
 #pragma unroll
-        for (int ch = 0; ch < F; ch++) Fa[ch] += l[ch] * alpha * T;
+        for (int ch = 0; ch < F; ch++) Fa[ch] = fmaf(l[ch], w, Fa[ch]);
       }
-      D += b.z * alpha * T;
+      D = fmaf(b.z, w, D);
       T = test_T;
       last_contributor = base + j + 1;
     }
