@@ -202,7 +202,9 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
   // byte offset of this lane inside a parked row, kept opaque so that it stays in a register (under the 80-register
   // cap the compiler otherwise re-derives it from %tid every step)
   uint32_t lane4, park_w;  // park_w: shared-window address of this warp's first parked row (sm.u is sizeof(sm.w) above)
-  asm volatile("mov.u32 %0, %1;" : "=r"(lane4) : "r"(lane * 4));
+  // (a plain mov is transparent to ptxas, which then rebuilds lane * 4 from %tid -- S2R + 2 ALU -- in EVERY step; the
+  // result of a volatile shuffle cannot be rematerialised)
+  asm volatile("shfl.sync.idx.b32 %0, %1, %2, 0x1f, 0xffffffff;" : "=r"(lane4) : "r"(lane * 4), "r"(lane));
   asm volatile("mov.u32 %0, %1;" : "=r"(park_w) : "r"((uint32_t)__cvta_generic_to_shared(sm.w[warp])));
   static_assert(offsetof(RbSmem<NCH>, u) - offsetof(RbSmem<NCH>, w) == sizeof(float) * RB_WARPS * RB_GROUP * RB_ASTRIDE,
                 "sm.u must follow sm.w");

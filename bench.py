@@ -530,8 +530,10 @@ def run_train_ours(wl, steps, warmup, world):
     launches0 = lib.fdls_kernel_launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    t_host = time.perf_counter()
     for _ in range(steps):
         loss, nbytes = step()
+    t_host = (time.perf_counter() - t_host) * 1e3 / max(1, steps)  # host time to ISSUE a step (no sync inside)
     e1.record()
     barrier(world)
     launches = lib.fdls_kernel_launches() - launches0
@@ -616,7 +618,7 @@ def run_train_ours(wl, steps, warmup, world):
     V = int((torch.as_tensor(0)).item())
     return dict(ms=ms, n_frames=steps, stage_ms=fwd_ev.stage_ms(1), bwd_stage_ms=bwd_ev.stage_ms(1), R=float(R), V=V,
                 launches=int(launches), e2e_s=e2e_s, h2d=h2d, d2h=4, allreduce_bytes=nbytes, allreduce_ms=allreduce_ms,
-                R_staged=R_staged)
+                R_staged=R_staged, host_issue_ms=t_host)
 
 
 def run_train_reference(wl, steps, warmup, world):
@@ -767,6 +769,7 @@ def train_line(a, rank, world, local, warmup, name, n_views, steps):
         line["stages_ms"].update({"bwd_zero": round(bwd[0], 4), "render_bwd": round(bwd[1], 4), "preprocess_bwd": round(bwd[2], 4)})
         line["allreduce_bytes_per_step"] = r["allreduce_bytes"]
         line["allreduce_ms"] = round(r["allreduce_ms"], 4)  # compute stream held by the collective, max over ranks
+        line["host_issue_ms_per_step"] = round(r["host_issue_ms"], 4)  # Python time to enqueue one step (rank 0)
     else:
         line["impl"] = "reference"
         line["cpu_baseline"] = {"value": line["value"], "unit": "iters/s", "cores": 1, "kind": "reference",
@@ -1384,7 +1387,7 @@ def main():
         t = train_line(a, rank, world, local, warmup, "cfg3", max(TRAIN_VIEWS, a.gpus), a.steps)
         line["train"] = {k: t[k] for k in ("metric", "value", "unit", "ms_per_step", "scaling", "config", "e2e",
                                             "gpu_launches", "roofline", "stages_ms", "allreduce_bytes_per_step",
-                                            "allreduce_ms", "clocks") if k in t}
+                                            "allreduce_ms", "host_issue_ms_per_step", "clocks") if k in t}
     # SURVEY 8d metric (i) "end to end incl. deformation": the same sweep with the deformation network in front
     if a.workload == "cfg2" and os.environ.get("FDLS_BENCH_DEFORM", "1") != "0":
         dl = deform_line(a, rank, world, local, warmup, max(1, min(3, a.steps)))

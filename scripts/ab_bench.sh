@@ -8,6 +8,6 @@ for spec in "$@"; do
   python - "$label" <<PY
 import json, sys
 d = json.loads(open("gpurun_out/ab_%s.json" % sys.argv[1]).read()); t = d.get("train", {})
-print(sys.argv[1], "render", d["value"], "one_stream", d.get("value_one_stream"), "e2e", d["e2e"]["value"], "train", t.get("value"), t.get("stages_ms"))
+print(sys.argv[1], "render", d["value"], "one_stream", d.get("value_one_stream"), "e2e", d["e2e"]["value"], "train", t.get("value"), "host_issue_ms", t.get("host_issue_ms_per_step"), t.get("stages_ms"))
 PY
 done
