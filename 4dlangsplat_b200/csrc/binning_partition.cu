@@ -41,11 +41,21 @@ static size_t pt_smem_bytes(int T, bool scatter) {
   const size_t words = (size_t)(T + 1) / 2;
   return (PT_WARPS * words + (scatter ? (size_t)T + 1 : 0)) * sizeof(uint32_t);
 }
+// Cost units per CTA span.  Every CTA zeroes, prefixes and reads back 8 warps x T private counters, so at cfg2 (12 M
+// cost units, T = 2040) 740 CTAs of 16 K units spent more instructions on their 12 M counters than on the 2.5 M
+// instances; 370 CTAs of 32 K units: same latency on an empty GPU (80 -> 79 us), and 4280 -> 4950 frames/s with four
+// frames in flight, where the SMs the binning leaves alone run another frame's compositor.  Longer spans lose again
+// (40 K: 92 us).  Small scenes keep at least two CTAs per SM.
+#ifndef PT_SPAN_COST
+#define PT_SPAN_COST 32768
+#endif
 static int pt_ctas(long long capacity, int P, int T) {
   // total cost <= capacity + PT_C * P (PT_C = 32, see below).  A CTA span of cost c holds at most c / 33 Gaussians,
-  // which must stay below 65536 (u16 per-tile counters): c <= 2e6.  Target: ~16K cost units per CTA.
+  // which must stay below 65536 (u16 per-tile counters): c <= 2e6.  Target: PT_SPAN_COST cost units per CTA.
   const long long cost = capacity + 32LL * P;
-  long long lo = (cost + 1999999) / 2000000, g = (cost + 16383) / 16384;
+  long long lo = (cost + 1999999) / 2000000, g = (cost + PT_SPAN_COST - 1) / PT_SPAN_COST;
+  const long long floor_g = (cost + 4095) / 4096 < 2 * PT_SMS ? (cost + 4095) / 4096 : 2 * PT_SMS;
+  if (g < floor_g) g = floor_g;
   if (lo < 1) lo = 1;
   long long per_sm = (long long)(PT_SMEM_PER_SM / (pt_smem_bytes(T, true) + 1024));
   if (per_sm < 1) per_sm = 1;
