@@ -33,42 +33,45 @@ constexpr int PT_MAX_TILES = 10240;  // 8 warps x 10240 x 2 B + 10240 x 4 B = 20
 // the cost span [c*I, (c+1)*I) of the depth-ordered stream (I = ceil(total / ctas), read on the device), warp w an
 // eighth of it; a Gaussian whose instances straddle a boundary is shared (its tiles are distinct, so any split
 // keeps the per-tile order).
-// ctas: enough CTAs for the u16 per-tile counters to be safe, and -- unless that bound needs more -- at most one
-// resident wave of the scatter kernel (148 SMs x the CTAs its shared memory allows), so no partial second wave trails behind.
+// ctas: see pt_ctas below.
 constexpr int PT_SMS = 148;                 // B200
 constexpr size_t PT_SMEM_PER_SM = 227 * 1024;
 static size_t pt_smem_bytes(int T, bool scatter) {
   const size_t words = (size_t)(T + 1) / 2;
   return (PT_WARPS * words + (scatter ? (size_t)T + 1 : 0)) * sizeof(uint32_t);
 }
-// Cost units per CTA span.  Every CTA zeroes, prefixes and reads back 8 warps x T private counters, so at cfg2 (12 M
-// cost units, T = 2040) 740 CTAs of 16 K units spent more instructions on their 12 M counters than on the 2.5 M
-// instances; 370 CTAs of 32 K units: same latency on an empty GPU (80 -> 79 us), and 4280 -> 4950 frames/s with four
-// frames in flight, where the SMs the binning leaves alone run another frame's compositor.  Longer spans lose again
-// (40 K: 92 us).  Small scenes keep at least two CTAs per SM.
-#ifndef PT_SPAN_COST
-#define PT_SPAN_COST 32768
-#endif
+// Cost units per CTA span: 16 per tile.  Every CTA zeroes, prefixes and reads back 8 warps x T private counters, so
+// a span must be worth its counters: at cfg2 (12 M cost units, T = 2040) 740 CTAs of 16 K units spent more
+// instructions on their 12 M counters than on the 2.5 M instances; 370 CTAs of 32 K units have the same latency on an
+// empty GPU (80 -> 79 us) and give 4280 -> 4950 frames/s with four frames in flight, where the SMs the binning leaves
+// alone run another frame's compositor; 40 K units lose again (92 us).  The same ratio is the measured optimum at cfg4
+// (T = 5440: 64-96 K units) and cfg5 (T = 8160: 128 K units, 245 -> 279 frames/s against 64 K).  Spans stay below 256 K
+// units: CTAs that run together then work on neighbouring stretches of the stream and their 4-byte stores into a
+// tile's list share sectors in L2 (round 1: 2.5x faster scatter at R = 185M than one wave of very long spans).
 static int pt_ctas(long long capacity, int P, int T) {
   // total cost <= capacity + PT_C * P (PT_C = 32, see below).  A CTA span of cost c holds at most c / 33 Gaussians,
-  // which must stay below 65536 (u16 per-tile counters): c <= 2e6.  Target: PT_SPAN_COST cost units per CTA.
+  // which must stay below 65536 (u16 per-tile counters): c <= 2e6.
   const long long cost = capacity + 32LL * P;
-  long long lo = (cost + 1999999) / 2000000, g = (cost + PT_SPAN_COST - 1) / PT_SPAN_COST;
+  const long long hard = (cost + 1999999) / 2000000;
+  long long span = 16LL * T;
+  if (span < 16384) span = 16384;
+  if (span > 262144) span = 262144;
+  long long g = (cost + span - 1) / span;
+  // small scenes: at least two CTAs per SM while a span is still worth 4 K units
   const long long floor_g = (cost + 4095) / 4096 < 2 * PT_SMS ? (cost + 4095) / 4096 : 2 * PT_SMS;
   if (g < floor_g) g = floor_g;
-  if (lo < 1) lo = 1;
+  if (g < hard) g = hard;
+  if (g < 1) g = 1;
   long long per_sm = (long long)(PT_SMEM_PER_SM / (pt_smem_bytes(T, true) + 1024));
   if (per_sm < 1) per_sm = 1;
   if (per_sm > 8) per_sm = 8;
-  const long long wave = per_sm * PT_SMS;
-  // ... but never spans above 64K cost units: CTAs that run together then work on neighbouring stretches of the
-  // stream and their 4-byte stores into a tile's list share sectors in L2 (measured: 2.5x faster scatter at R = 185M
-  // than one wave of long spans, whose stores each dirty a sector of their own)
-  const long long fine = (cost + 65535) / 65536;
-  if (lo < fine) lo = fine;
-  const long long hi = lo > wave ? lo : wave;
-  if (g < lo) g = lo;
-  if (g > hi) g = hi;
+  const long long wave = per_sm * PT_SMS;  // resident CTAs of the scatter kernel
+  if (g > wave) {
+    // several waves: a whole number of them (a few CTAs trailing behind a full wave cost a wave's time; cfg4: +3.5 %)
+    long long r = (g + wave / 2) / wave * wave;
+    if (r < hard) r = (hard + wave - 1) / wave * wave;
+    g = r;
+  }
   return (int)g;
 }
 
