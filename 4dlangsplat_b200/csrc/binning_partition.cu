@@ -238,23 +238,22 @@ part_count_kernel(int P, int T, const uint32_t* __restrict__ num_rendered,
                   const uint32_t* __restrict__ offsets, const int* __restrict__ radii, const float4* __restrict__ rec,
                   int gx, int gy, uint32_t* __restrict__ table) {
   pdl_grid_sync();
+  // ONE counter set for the whole CTA: only the CTA's totals are wanted here and counting needs no order, so the
+  // warps' atomics may interleave (the scatter kernel needs a set per warp).  T / 2 words instead of 4 T: at cfg5
+  // (T = 8160) 16 KB per CTA instead of 131 KB, i.e. the SM holds eight CTAs instead of one.  A CTA span holds fewer
+  // than 65536 Gaussians (pt_ctas), so the u16 counters cannot overflow.
   extern __shared__ uint32_t pt_smem[];
-  const int words = (T + 1) / 2;  // per-warp counter words
+  const int words = (T + 1) / 2;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int i = tid; i < PT_WARPS * words; i += PT_THREADS) pt_smem[i] = 0;
+  for (int i = tid; i < words; i += PT_THREADS) pt_smem[i] = 0;
   __syncthreads();
   unsigned long long ws, we;
   int V;
   pt_span(num_rendered, depth_hist, P, warp, ws, we, V);
-  walk<false>(ws, we, V, order, offsets, radii, rec, gx, gy, pt_smem + warp * words, nullptr, nullptr, nullptr, 0, lane);
+  walk<false>(ws, we, V, order, offsets, radii, rec, gx, gy, pt_smem, nullptr, nullptr, nullptr, 0, lane);
   __syncthreads();
   uint32_t* row = table + (size_t)blockIdx.x * T;
-  for (int t = tid; t < T; t += PT_THREADS) {
-    uint32_t c = 0;
-#pragma unroll
-    for (int w = 0; w < PT_WARPS; ++w) c += cnt_get(pt_smem + w * words, t);
-    row[t] = c;
-  }
+  for (int t = tid; t < T; t += PT_THREADS) row[t] = cnt_get(pt_smem, t);
 }
 
 // per tile: exclusive scan over the CTAs (table is [ctas][T], coalesced along t); tile_total[t] = column sum.
@@ -411,7 +410,7 @@ cudaError_t launch_partition(int P, int gx, int gy, const uint32_t* order, const
                              const uint32_t* depth_hist, long long capacity, cudaStream_t st) {
   const int T = gx * gy, ctas = partition_ctas(capacity, P, T);
   static SmemOptIn optin_a, optin_b;  // per device (common.cuh)
-  const size_t sa = pt_smem_bytes(T, false), sb = pt_smem_bytes(T, true);
+  const size_t sa = (size_t)((T + 1) / 2) * sizeof(uint32_t), sb = pt_smem_bytes(T, true);
   if (cudaError_t e = optin_a.ensure(part_count_kernel, sa)) return e;
   if (cudaError_t e = optin_b.ensure(part_scatter_kernel, sb)) return e;
   launch_pdl(part_count_kernel, dim3(ctas), dim3(PT_THREADS), sa, st, P, T, num_rendered, depth_hist, order, offsets, radii, rec, gx, gy, table);
