@@ -18,9 +18,10 @@ cudaError_t launch_preprocess_fwd(const FdlsFwdArgs* a, const ViewParams& vp, fl
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 // binning.cu
 size_t scan_scratch_bytes(int P);
+size_t scan_state_bytes(int P);
 cudaError_t launch_scan(int P, const uint32_t* tiles_touched, const uint32_t* order, uint32_t* offsets,
-                        uint32_t* block_sums, uint32_t* num_rendered, long long capacity, uint32_t* host_mirror,
-                        cudaStream_t st);
+                        uint32_t* block_sums, unsigned long long* state, uint32_t* num_rendered, long long capacity,
+                        uint32_t* host_mirror, cudaStream_t st);
 cudaError_t launch_duplicate(int P, const float4* rec, const uint32_t* order, const uint32_t* offsets, const int* radii,
                              uint64_t* keys, uint32_t* vals, int gx, int gy, long long capacity, uint32_t* global_hist,
                              int passes, cudaStream_t st);
@@ -33,7 +34,8 @@ int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* v
                cudaStream_t st);
 int sort_pairs_static(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
                       const uint32_t* n_dev, int begin_bit, int end_bit, cudaStream_t st);
-int sort_prepare(long long n_max, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, cudaStream_t st);
+int sort_prepare(long long n_max, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, cudaStream_t st,
+                 size_t zero_before = 0);
 uint32_t* sort_hist(void* scratch);
 int sort_run(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
              const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, bool have_hist,
@@ -112,7 +114,8 @@ static void compute_layout(int P, int W, int H, long long capacity, FdlsLayout* 
   L->num_rendered = o;  o += align_up(16);
   L->scan_scratch = o;  o += scan_scratch_bytes((int)Pz);
   L->depth_order = o;   o += align_up(Pz * 4);
-  L->depth_scratch = o; o += align_up(Pz * 8) * 2 + align_up(Pz * 4) + sort_scratch_bytes((long long)Pz);
+  // [keys_a | keys_b | vals_b | scan state words | onesweep scratch]: see depth_sort_scratch()
+  L->depth_scratch = o; o += align_up(Pz * 8) * 2 + align_up(Pz * 4) + scan_state_bytes((int)Pz) + sort_scratch_bytes((long long)Pz);
   S->geom_bytes = o;
   o = 0;
   L->final_T = o;          o += align_up(HW * 4);
@@ -130,6 +133,12 @@ static void compute_layout(int P, int W, int H, long long capacity, FdlsLayout* 
   L->sort_scratch = o; o += sort_scratch_bytes((long long)cap);
   L->part_table = o;   o += partition_supported(gx, gy) ? partition_table_bytes((long long)cap, (int)Pz, (int)tiles) : 256;
   S->binning_bytes = o;
+}
+
+// the depth sort's onesweep scratch inside the geometry workspace; the scan's state words sit directly in front of it
+// so that ONE memset per frame (sort_prepare) zeroes both
+static char* depth_sort_scratch(char* g, const FdlsLayout& L, size_t Pz) {
+  return g + L.depth_scratch + 2 * align_up(Pz * 8) + align_up(Pz * 4) + scan_state_bytes((int)Pz);
 }
 
 static ViewParams make_view(const float* view, const float* proj, const float* campos, const float* bg, int W, int H,
@@ -219,11 +228,12 @@ FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
   uint64_t* dk_a = (uint64_t*)(g + L.depth_scratch);
   uint64_t* dk_b = (uint64_t*)(g + L.depth_scratch + align_up(Pz * 8));
   uint32_t* dv_b = (uint32_t*)(g + L.depth_scratch + 2 * align_up(Pz * 8));
-  char* dscr = g + L.depth_scratch + 2 * align_up(Pz * 8) + align_up(Pz * 4);
+  char* dscr = depth_sort_scratch(g, L, Pz);
+  unsigned long long* scan_state = (unsigned long long*)(dscr - scan_state_bytes((int)Pz));
   uint32_t* order = (uint32_t*)(g + L.depth_order);
   // the depth sort's digit histograms are accumulated by the preprocess kernel itself (no separate pass over the keys)
   const size_t dscr_bytes = sort_scratch_bytes((long long)Pz);
-  rc = sort_prepare(a->P, 0, 32, dscr, dscr_bytes, st);
+  rc = sort_prepare(a->P, 0, 32, dscr, dscr_bytes, st, scan_state_bytes((int)Pz));
   if (rc < 0) return rc;
   if (launch_preprocess_fwd(a, vp, (float4*)(g + L.rec), (uint32_t*)(g + L.tiles_touched), (uint8_t*)(g + L.clamped),
                             dk_a, order, a->P > 0 ? sort_hist(dscr) : nullptr, nr + 2, st) != cudaSuccess)
@@ -235,7 +245,7 @@ FDLS_API int fdls_preprocess(const FdlsFwdArgs* a, void* stream) {
   if (sel != 0) return FDLS_ECUDA;  // 4 passes: result is back in the `a` buffers by construction
   // (2) ... and scan the tile counts in that order, so instances are emitted depth-sorted
   if (launch_scan(a->P, (uint32_t*)(g + L.tiles_touched), order, (uint32_t*)(g + L.point_offsets),
-                  (uint32_t*)(g + L.scan_scratch), nr, a->capacity, a->num_rendered_host, st) != cudaSuccess)
+                  (uint32_t*)(g + L.scan_scratch), scan_state, nr, a->capacity, a->num_rendered_host, st) != cudaSuccess)
     return FDLS_ECUDA;
   rec(a->stage_events, 2, st);
   return FDLS_OK;
@@ -265,7 +275,7 @@ FDLS_API int fdls_bin_and_render(const FdlsFwdArgs* a, void* stream) {
       // digit histograms of the depth sort (top-byte bin 0xff = culled Gaussians), still in the geometry workspace
       const size_t Pz2 = (size_t)(a->P < 1 ? 1 : a->P);
       const uint32_t* depth_hist =
-          sort_hist(g + L.depth_scratch + 2 * align_up(Pz2 * 8) + align_up(Pz2 * 4));
+          sort_hist(depth_sort_scratch(g, L, Pz2));
       // binning_partition.cu: count / scans / scatter -- every instance goes straight to its final sorted slot
       if (launch_partition(a->P, gx, gy, (const uint32_t*)(g + L.depth_order), (const uint32_t*)(g + L.point_offsets),
                            a->radii, (const float4*)(g + L.rec), (uint32_t*)(b + L.part_table),

@@ -167,6 +167,119 @@ scan_apply_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __rest
   }
 }
 
+// ---- single-pass scan (default): reduce + look-back + apply in ONE kernel --------------------------------------------
+// The two-kernel scan above loads every element twice through the same dependent chain (order[k], then in[order[k]])
+// and pays two launches on the frame's critical path: 11 + 7.5 us at cfg2 for 74 blocks that keep the GPU 6 % busy.
+// Here a block takes a tile by ticket (so it only ever waits for blocks that already started), publishes its aggregate
+// in a 64-bit state word {flag, value}, obtains its exclusive prefix by decoupled look-back over its predecessors' words
+// (one warp, 32 predecessors per step), publishes the inclusive value, and writes its part of the scan.  The state words
+// and the two tickets start at zero (the depth sort's scratch memset covers them, see api.cu); the block that finishes
+// last re-zeroes the tickets.
+constexpr uint64_t SCAN_FLAG_AGG = 1ull << 32, SCAN_FLAG_INC = 2ull << 32;
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_onepass_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __restrict__ order,
+                    unsigned long long* __restrict__ state, uint32_t* __restrict__ out,
+                    uint32_t* __restrict__ num_rendered, long long capacity, uint32_t* host_mirror) {
+  pdl_grid_sync();
+  __shared__ uint32_t s_warp[33];
+  __shared__ uint32_t s_tile, s_prefix;
+  if (threadIdx.x == 0) s_tile = atomicAdd(&num_rendered[2], 1u);
+  __syncthreads();
+  const int tile = (int)s_tile, nb = gridDim.x;
+  // blocked arrangement: thread t owns items [t*ITEMS, t*ITEMS+ITEMS) of the tile
+  const int base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+  uint32_t v[SCAN_ITEMS];
+  if (base + SCAN_ITEMS <= P) {
+    if (order != nullptr) {  // gather in depth order
+      const uint4* p4 = reinterpret_cast<const uint4*>(order + base);
+      const uint4 a = p4[0], b = p4[1];
+      const uint32_t id[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < SCAN_ITEMS; ++i) v[i] = in[id[i]];
+    } else {
+      const uint4* p4 = reinterpret_cast<const uint4*>(in + base);
+      const uint4 a = p4[0], b = p4[1];
+      v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) v[i] = (base + i < P) ? in[order ? order[base + i] : base + i] : 0;
+  }
+  uint32_t s = 0;
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; ++i) s += v[i];
+  uint32_t total;
+  uint32_t ex = block_excl_scan<SCAN_THREADS>(s, total, s_warp);
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    volatile unsigned long long* vs = state;
+    if (lane == 0) {
+      vs[tile] = (tile == 0 ? SCAN_FLAG_INC : SCAN_FLAG_AGG) | total;
+      __threadfence();
+    }
+    uint32_t prefix = 0;
+    for (int j0 = tile - 1; j0 >= 0; j0 -= 32) {
+      const int j = j0 - lane;
+      unsigned long long w = SCAN_FLAG_INC;  // lanes before tile 0 read as "inclusive 0"
+      if (j >= 0) {
+        do w = vs[j]; while ((w >> 32) == 0);
+      }
+      const uint32_t inc = __ballot_sync(0xffffffffu, (w & SCAN_FLAG_INC) != 0);
+      const int stop = __ffs(inc) - 1;  // nearest predecessor that already knows its inclusive value (-1: none)
+      uint32_t val = (stop < 0 || lane <= stop) ? (uint32_t)w : 0u;
+#pragma unroll
+      for (int d = 16; d >= 1; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
+      prefix += val;
+      if (stop >= 0) break;
+    }
+    if (lane == 0) {
+      if (tile > 0) {
+        vs[tile] = SCAN_FLAG_INC | (unsigned long long)(prefix + total);
+        __threadfence();
+      }
+      s_prefix = prefix;
+    }
+  }
+  __syncthreads();
+  ex += s_prefix;
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; ++i) {
+    ex += v[i];
+    v[i] = ex;
+  }
+  if (base + SCAN_ITEMS <= P) {
+    uint4* o4 = reinterpret_cast<uint4*>(out + base);
+    o4[0] = make_uint4(v[0], v[1], v[2], v[3]);
+    o4[1] = make_uint4(v[4], v[5], v[6], v[7]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i)
+      if (base + i < P) out[base + i] = v[i];
+  }
+  if (threadIdx.x == 0) {
+    if (tile == nb - 1) {  // the grand total: R and the overflow flag
+      const uint32_t R = s_prefix + total;
+      num_rendered[0] = R;
+      num_rendered[1] = ((long long)R > capacity) ? 1u : 0u;
+      if (host_mirror != nullptr) {  // pinned, device-mapped host memory: no copy-engine hop between the kernels
+        volatile uint32_t* h = host_mirror;
+        h[0] = R;
+        h[1] = ((long long)R > capacity) ? 1u : 0u;
+        __threadfence_system();
+      }
+      __threadfence();
+    }
+    // every block counts itself out on the partition's ticket word (zero between its uses); the last one resets both
+    if (atomicAdd(&num_rendered[3], 1u) == (uint32_t)nb - 1) {
+      num_rendered[2] = 0;
+      num_rendered[3] = 0;
+    }
+  }
+}
+
+size_t scan_state_bytes(int P) { return align_up((size_t)cdiv(P < 1 ? 1 : P, SCAN_TILE) * sizeof(unsigned long long)); }
+
 // rasterizer_impl.cu:70-111, warp-cooperative.  Thread `pos` handles the pos-th Gaussian in DEPTH order
 // (order[pos]); within a Gaussian the tiles are emitted y-major, x-minor like the reference.  Because instances
 // leave this kernel already depth-sorted, the following stable sort only has to look at the tile bits -- and since the
@@ -291,9 +404,18 @@ tile_ranges_kernel(const uint32_t* __restrict__ num_rendered, long long capacity
 size_t scan_scratch_bytes(int P) { return align_up((size_t)(cdiv(P, SCAN_TILE) + 1) * sizeof(uint32_t)); }
 
 cudaError_t launch_scan(int P, const uint32_t* tiles_touched, const uint32_t* order, uint32_t* offsets,
-                        uint32_t* block_sums, uint32_t* num_rendered, long long capacity, uint32_t* host_mirror,
-                        cudaStream_t st) {
+                        uint32_t* block_sums, unsigned long long* state, uint32_t* num_rendered, long long capacity,
+                        uint32_t* host_mirror, cudaStream_t st) {
   const int nb = cdiv(P, SCAN_TILE);
+  static const bool onepass = [] {
+    const char* e = getenv("FDLS_SCAN");
+    return !(e && e[0] == '2');  // FDLS_SCAN=2: the two-kernel scan, for A/B
+  }();
+  if (P > 0 && onepass && state != nullptr) {
+    launch_pdl(scan_onepass_kernel, dim3(nb), dim3(SCAN_THREADS), 0, st, P, tiles_touched, order, state, offsets, num_rendered, capacity, host_mirror);
+    count_launch();
+    return cudaGetLastError();
+  }
   if (P > 0) {
     launch_pdl(scan_reduce_kernel, dim3(nb), dim3(SCAN_THREADS), 0, st, P, tiles_touched, order, block_sums, num_rendered, capacity, host_mirror);
     count_launch();

@@ -307,13 +307,16 @@ static RsScratch rs_carve(void* scratch, long long n_max, int passes) {
 size_t sort_scratch_bytes(long long n_max) { return rs_carve(nullptr, n_max < 1 ? 1 : n_max, RS_MAX_PASSES).total_bytes; }
 
 // Zero the scratch (histograms, tickets, tile states).  Must precede sort_run and any external histogram accumulation.
-int sort_prepare(long long n_max, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+// zero_before: bytes directly in front of the scratch that the same memset clears (the scan's state words, api.cu)
+int sort_prepare(long long n_max, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, cudaStream_t st,
+                 size_t zero_before) {
   if (begin_bit < 0 || end_bit <= begin_bit || end_bit > 64) return FDLS_EINVAL;
   if (n_max <= 0) return FDLS_OK;
   const int passes = (end_bit - begin_bit + 7) / 8;
   RsScratch sc = rs_carve(scratch, n_max, passes);
   if (scratch_bytes < sc.total_bytes) return FDLS_EWORKSPACE;
-  return cudaMemsetAsync(scratch, 0, sc.total_bytes, st) == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
+  return cudaMemsetAsync((char*)scratch - zero_before, 0, sc.total_bytes + zero_before, st) == cudaSuccess ? FDLS_OK
+                                                                                                             : FDLS_ECUDA;
 }
 
 // [pass][256] digit counters inside the scratch (for callers that build the histogram while generating the keys)
@@ -362,7 +365,7 @@ int sort_run(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* val
 int sort_pairs(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, long long n_max,
                const uint32_t* n_dev, int begin_bit, int end_bit, void* scratch, size_t scratch_bytes,
                cudaStream_t st) {
-  int rc = sort_prepare(n_max, begin_bit, end_bit, scratch, scratch_bytes, st);
+  int rc = sort_prepare(n_max, begin_bit, end_bit, scratch, scratch_bytes, st, 0);
   if (rc < 0) return rc;
   return sort_run(keys_a, keys_b, vals_a, vals_b, n_max, n_dev, begin_bit, end_bit, scratch, scratch_bytes, false, st);
 }
