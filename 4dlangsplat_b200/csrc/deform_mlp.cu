@@ -235,6 +235,7 @@ constexpr int DM_EPI_THREADS = 2 * DM_GROUP_THREADS;       // two groups = two t
 constexpr int DM_THREADS = DM_EPI_THREADS + 64;            // + the MMA-issue warp and the TMA warp (one thread each)
 constexpr int DM_SLOTS = 5;                                // weight-chunk ring
 constexpr int DM_MAX_GEMMS = 1 + FDLS_DEFORM_MAX_HEADS;    // trunk + one layer-1 GEMM per head
+constexpr int DM_W2_ROWS = 16;                             // last-layer rows (all heads, padded) kept in shared memory
 constexpr int DM_OUT_BLOCK = 4;                            // outputs of a head's last layer handled per pass
 
 // The walk over (pair of tiles, GEMM, tile slot, chunk) shared by the TMA thread and the MMA thread: GEMM q of slot 0,
@@ -270,6 +271,7 @@ __device__ __forceinline__ void dm_group_barrier(int grp) {  // the 256 threads 
 // mbarriers per slot: a_ready (256 arrivals: X tile or sA written), acc_ready[2] (tcgen05.commit, GEMMs alternate
 // between the two so that a completion is never overtaken by the next one on the same barrier), cols_free (256
 // arrivals: head h's accumulator has been consumed, head h+2 may overwrite it).
+template <bool W2_SMEM>
 __global__ void __launch_bounds__(DM_THREADS, 1)
 deform_mlp_kernel(DmDev a, DmPlan pl) {
   extern __shared__ __align__(128) unsigned char dm_smem[];
@@ -277,6 +279,10 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
   __shared__ uint64_t s_acc_ready[2][2], s_a_ready[2], s_cols_free[2];
   __shared__ uint32_t s_tmem;
   __shared__ __align__(16) float s_bias[(1 + FDLS_DEFORM_MAX_HEADS) * 128];  // b0, then b1 of every head
+  // last-layer weights of all heads (rows zero-padded to a multiple of four per head), when they fit: read as shared
+  // memory broadcasts with immediate offsets instead of global loads through the L1 (a descriptor move per load)
+  __shared__ __align__(16) float s_w2[W2_SMEM ? DM_W2_ROWS * 128 : 4];
+  __shared__ int s_w2_row[FDLS_DEFORM_MAX_HEADS];  // first row of head h in s_w2
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int W = a.W, G = a.G;
   const uint32_t x_part = (uint32_t)(G / 8) * DM_ROWS * 16, a_part = (uint32_t)(W / 8) * DM_ROWS * 16;
@@ -299,6 +305,15 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
     fence_mbar_init();
   }
   for (int i = tid; i < W; i += DM_THREADS) s_bias[i] = a.b0[i];
+  if (W2_SMEM) {
+    int r0 = 0;
+    for (int h = 0; h < a.H; ++h) {
+      const int rows = (a.head[h].k + 3) & ~3;
+      for (int i = tid; i < rows * W; i += DM_THREADS) s_w2[r0 * W + i] = a.head[h].w2[i];
+      if (tid == 0) s_w2_row[h] = r0;
+      r0 += rows;
+    }
+  }
   for (int h = 0; h < a.H; ++h)
     for (int i = tid; i < W; i += DM_THREADS) s_bias[(1 + h) * 128 + i] = a.head[h].b1[i];
   tc_fence_before_sync();
@@ -450,7 +465,8 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
           float2 acc2[DM_OUT_BLOCK];  // (sum over even columns, sum over odd columns)
 #pragma unroll
           for (int e = 0; e < DM_OUT_BLOCK; ++e) acc2[e] = make_float2(0.f, 0.f);
-          const float4* w2 = reinterpret_cast<const float4*>(hd.w2 + (size_t)e0 * W);
+          const float4* w2 = W2_SMEM ? reinterpret_cast<const float4*>(s_w2 + (s_w2_row[h] + e0) * W)
+                                     : reinterpret_cast<const float4*>(hd.w2 + (size_t)e0 * W);
           for (int c = c0; c < c0 + W / 2; c += 16) {
             float v[16];
             tmem_ld16(tbase + col + c, v);
@@ -467,7 +483,8 @@ deform_mlp_kernel(DmDev a, DmPlan pl) {
 #pragma unroll
               for (int i = 0; i < 2; ++i)
 #pragma unroll
-                for (int j4 = 0; j4 < 4; ++j4) wv[i][j4] = __ldg(w2 + ((ep + i) * W + c) / 4 + j4);  // L1 broadcast
+                for (int j4 = 0; j4 < 4; ++j4)  // the same address in every lane: a broadcast
+                  wv[i][j4] = W2_SMEM ? w2[((ep + i) * W + c) / 4 + j4] : __ldg(w2 + ((ep + i) * W + c) / 4 + j4);
 #pragma unroll
               for (int j4 = 0; j4 < 4; ++j4)
 #pragma unroll
@@ -570,13 +587,19 @@ int deform_forward(const FdlsDeformArgs* a, cudaStream_t st) {
   }
   const size_t smem = dm_smem_bytes(a->G, a->W);
   static SmemOptIn optin;
-  if (optin.ensure(deform_mlp_kernel, smem) != cudaSuccess) return FDLS_ECUDA;
+  int w2_rows = 0;
+  for (int h = 0; h < a->H; ++h) w2_rows += dm_kpad(a->head[h].k);
+  const bool w2_smem = w2_rows <= DM_W2_ROWS;
+  static SmemOptIn optin_g;
+  if ((w2_smem ? optin.ensure(deform_mlp_kernel<true>, smem) : optin_g.ensure(deform_mlp_kernel<false>, smem)) != cudaSuccess)
+    return FDLS_ECUDA;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int n_tiles = cdiv(a->P, DM_ROWS);
   count_launch();
-  deform_mlp_kernel<<<n_tiles < sms ? n_tiles : sms, DM_THREADS, smem, st>>>(d, pl);
+  if (w2_smem) deform_mlp_kernel<true><<<n_tiles < sms ? n_tiles : sms, DM_THREADS, smem, st>>>(d, pl);
+  else deform_mlp_kernel<false><<<n_tiles < sms ? n_tiles : sms, DM_THREADS, smem, st>>>(d, pl);
   return cudaGetLastError() == cudaSuccess ? FDLS_OK : FDLS_ECUDA;
 }
 
