@@ -32,6 +32,10 @@ _deferred = None
 # of the still-pending compositor CTAs of an older one.  Stage 2 stays on the current stream, ordered behind stage 1.
 _front = None
 
+# The torch.cuda.Stream object that is current, when the caller knows it (sweep.render_sweep): torch.cuda.current_stream()
+# costs ~14 us per call.
+_current = None
+
 # parity tests set this: the partition binning then also writes the reference-format sorted keys (not needed to render)
 emit_keys = False
 
@@ -178,17 +182,17 @@ def rasterize_gaussians(background, means3D, colors, language_feature, opacity, 
         a.capacity = capacity
         ev = ss["event"]
         if _front is not None:
-            cur = torch.cuda.current_stream(dev)
+            cur = _current if _current is not None else torch.cuda.current_stream(dev)
             _front.wait_stream(cur)  # inputs and recycled workspaces are ordered on the current stream
             _lib.check(lib.fdls_preprocess(C.byref(a), C.c_void_p(_front.cuda_stream)), "fdls_preprocess")
             ev.record(_front)
             cur.wait_event(ev)
         else:
             _lib.check(lib.fdls_preprocess(C.byref(a), stream), "fdls_preprocess")
-            ev.record(torch.cuda.current_stream(dev))
+            ev.record(_current if _current is not None else torch.cuda.current_stream(dev))
         result[6] = run_stage2(capacity, -1)
         defer = _deferred is not None and not torch.is_grad_enabled()
-        tstream = torch.cuda.current_stream(dev) if defer else None
+        tstream = (_current if _current is not None else torch.cuda.current_stream(dev)) if defer else None
 
         def finish():
             ev.synchronize()

@@ -34,6 +34,21 @@ def _side_streams(device, n, priority=0):
     return have[:n]
 
 
+class _UseStream:
+    __slots__ = ("stream", "prev")
+
+    def __init__(self, stream, prev):
+        self.stream, self.prev = stream, prev
+
+    def __enter__(self):
+        torch.cuda.set_stream(self.stream)
+        return self.stream
+
+    def __exit__(self, *exc):
+        torch.cuda.set_stream(self.prev)
+        return False
+
+
 class StreamRing:
     def __init__(self, n_streams=2, device=None, include_main=True):
         self.main = torch.cuda.current_stream(device)
@@ -50,8 +65,10 @@ class StreamRing:
         return self
 
     def stream(self, i):
-        """Context manager that makes stream i mod n current."""
-        return torch.cuda.stream(self.streams[i % len(self.streams)])
+        """Context manager that makes stream i mod n current (and the ring's main stream current again on exit).
+        torch.cuda.stream() looks the current stream up with device=None on every entry, which goes through
+        torch.cuda.is_available() -- a cudaGetDeviceCount round trip per frame; set_stream() does not."""
+        return _UseStream(self.streams[i % len(self.streams)], self.main)
 
     def __exit__(self, *exc):
         for s in self.streams:
@@ -100,14 +117,16 @@ def render_sweep(render_fns, n_streams=3, sync_to_caller=True, front_priority=Fa
                 # the stream's memory can be handed to this frame (no record_stream: that would park the big
                 # workspaces in the allocator until the caller's stream catches up, and force fresh cudaMallocs)
                 ring.streams[i % len(ring)].wait_stream(ring.main)
-            with ring.stream(i):
+            with ring.stream(i) as cur:
                 _C._deferred = closures = []
                 _C._front = front[i % len(ring)] if front is not None else None
+                _C._current = cur  # spares the binding two torch.cuda.current_stream() look-ups per frame
                 try:
                     out = fn()
                 finally:
                     _C._deferred = None
                     _C._front = None
+                    _C._current = None
             pending.append((out, closures, ring.streams[i % len(ring)]))
         while pending:
             yield finish(pending.popleft())
