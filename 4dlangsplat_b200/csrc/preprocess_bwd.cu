@@ -63,6 +63,40 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
   else if (threadIdx.x < 35) s_cam[threadIdx.x - 32] = vp.campos != nullptr ? vp.campos[threadIdx.x - 32] : 0.f;
   __syncthreads();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  // M == 16: this warp's 32 x 192-byte SH block is contiguous.  It is streamed into shared memory with coalesced 16-byte
+  // loads (all twelve in flight before the first store) and re-read per thread conflict-free (row stride 49 words); the
+  // direct per-thread reads (45 scalar loads at a 192-byte lane stride, backward.cu:20-139 reads sh[idx*max_coeffs + i])
+  // touch 32 sectors per instruction for 4 bytes each.
+  extern __shared__ float pb_sh[];
+  constexpr int PB_SH_STRIDE = 49;
+  if (VEC_SH && shs != nullptr && D > 0) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g0 = blockIdx.x * 256 + warp * 32;
+    if (g0 < P) {
+      const int n_fl = min(32, P - g0) * 48;
+      const float* src = shs + (size_t)g0 * 48;
+      float* dst = pb_sh + warp * 32 * PB_SH_STRIDE;
+      if (n_fl == 1536) {
+        const float4* src4 = reinterpret_cast<const float4*>(src);
+        float4 q[12];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) q[i] = __ldg(src4 + lane + 32 * i);
+#pragma unroll
+        for (int i = 0; i < 12; ++i) {
+          const float v[4] = {q[i].x, q[i].y, q[i].z, q[i].w};
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint32_t e = 4 * (lane + 32 * i) + k;
+            const uint32_t g = __umulhi(e, 89478486u);  // e / 48 for e < 2^20
+            dst[g * PB_SH_STRIDE + (e - g * 48)] = v[k];
+          }
+        }
+      } else {
+        for (int e = lane; e < n_fl; e += 32) dst[(e / 48) * PB_SH_STRIDE + e % 48] = src[e];
+      }
+    }
+    __syncwarp();
+  }
   if (idx >= P) return;
   const bool vis = radii[idx] > 0;
 
@@ -228,7 +262,7 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
     }
     // ---------------- SH backward (backward.cu:20-139)
     if (shs != nullptr) {
-      const float* shp = shs + (size_t)idx * M * 3;
+      const float* shp = VEC_SH ? pb_sh + threadIdx.x * PB_SH_STRIDE : shs + (size_t)idx * M * 3;
       auto SH = [&](int i) { return V3{shp[3 * i], shp[3 * i + 1], shp[3 * i + 2]}; };
       V3 pos = {mean.x, mean.y, mean.z};
       V3 cam = {s_cam[0], s_cam[1], s_cam[2]};
@@ -448,12 +482,20 @@ cudaError_t launch_preprocess_bwd(const FdlsBwdArgs* a, const ViewParams& vp, co
   BwdOut o = {a->dL_dmeans3D, a->dL_dmeans2D, a->dL_dsh, a->dL_dcolors, a->dL_dlanguage, a->dL_dopacity,
               a->dL_dscales, a->dL_drotations, a->dL_dcov3D, a->dL_dconic, a->dL_ddepths, a->dL_dsh_rgb};
   const int grid = cdiv(a->P, 256);
+  const size_t pb_smem = (size_t)256 * 49 * sizeof(float);  // staged SH rows (M == 16)
   count_launch();
 #define PB_LAUNCH(VEC, ACCUM)                                                                                      \
-  launch_pdl(preprocess_bwd_kernel<VEC, ACCUM>, dim3(grid), dim3(256), 0, st, a->P, a->D, a->M, a->F, a->means3D, \
-             a->radii, a->shs, clamped, a->scales, a->rotations, a->cov3D_precomp, vp, grad_rec, o)
+  launch_pdl(preprocess_bwd_kernel<VEC, ACCUM>, dim3(grid), dim3(256), VEC ? pb_smem : 0, st, a->P, a->D, a->M, a->F, \
+             a->means3D, a->radii, a->shs, clamped, a->scales, a->rotations, a->cov3D_precomp, vp, grad_rec, o)
   if (a->M == 16) {
-    if (a->accumulate) PB_LAUNCH(true, true); else PB_LAUNCH(true, false);
+    static SmemOptIn opt_acc, opt_set;  // per device (common.cuh)
+    if (a->accumulate) {
+      if (cudaError_t e = opt_acc.ensure(preprocess_bwd_kernel<true, true>, pb_smem)) return e;
+      PB_LAUNCH(true, true);
+    } else {
+      if (cudaError_t e = opt_set.ensure(preprocess_bwd_kernel<true, false>, pb_smem)) return e;
+      PB_LAUNCH(true, false);
+    }
   } else {
     if (a->accumulate) PB_LAUNCH(false, true); else PB_LAUNCH(false, false);
   }
