@@ -83,13 +83,10 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
         for (int i = 0; i < 12; ++i) q[i] = __ldg(src4 + lane + 32 * i);
 #pragma unroll
         for (int i = 0; i < 12; ++i) {
-          const float v[4] = {q[i].x, q[i].y, q[i].z, q[i].w};
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const uint32_t e = 4 * (lane + 32 * i) + k;
-            const uint32_t g = __umulhi(e, 89478486u);  // e / 48 for e < 2^20
-            dst[g * PB_SH_STRIDE + (e - g * 48)] = v[k];
-          }
+          const uint32_t j = lane + 32 * i;            // 16-byte group; a row is twelve of them
+          const uint32_t g = __umulhi(j, 357913942u);  // j / 12 for j < 2^16
+          float* d = dst + g * PB_SH_STRIDE + (j - g * 12) * 4;
+          d[0] = q[i].x; d[1] = q[i].y; d[2] = q[i].z; d[3] = q[i].w;
         }
       } else {
         for (int e = lane; e < n_fl; e += 32) dst[(e / 48) * PB_SH_STRIDE + e % 48] = src[e];

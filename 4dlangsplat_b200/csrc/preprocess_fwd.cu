@@ -143,13 +143,12 @@ preprocess_fwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
         for (int i = 0; i < 12; ++i) q[i] = src4[lane + 32 * i];
 #pragma unroll
         for (int i = 0; i < 12; ++i) {
-          const float v[4] = {q[i].x, q[i].y, q[i].z, q[i].w};
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const uint32_t e = 4 * (lane + 32 * i) + k;
-            const uint32_t g = __umulhi(e, sh_magic);  // e / 48
-            dst[g * sh_stride + (e - g * 48)] = v[k];
-          }
+          // a row is twelve 16-byte groups: group j = lane + 32 i belongs to row j / 12 (one division per group, the
+          // four words go to consecutive addresses)
+          const uint32_t j = lane + 32 * i;
+          const uint32_t g = __umulhi(j, 357913942u);  // j / 12 for j < 2^16
+          float* d = dst + g * sh_stride + (j - g * 12) * 4;
+          d[0] = q[i].x; d[1] = q[i].y; d[2] = q[i].z; d[3] = q[i].w;
         }
       } else
       for (int e0 = 4 * lane; e0 < n_fl; e0 += 128) {
