@@ -146,6 +146,21 @@ CAMS = [dict(view_index=v, n_views=4) for v in range(4)] + [dict(pose="rot2"), d
 CAM_IDS = ["view%d_of4" % v for v in range(4)] + ["rot2", "rot3"]
 
 
+@pytest.mark.parametrize("P", [19997, 4097, 31])
+def test_gaussian_counts_that_fill_no_warp(synth, P):
+    """P not a multiple of 32 / 256 / 4096: the last warp's SH block is staged through the guarded path (preprocess
+    forward and backward), the single-pass scan's last tile is partial, the depth sort's last tile is ragged."""
+    _need_ref(3)
+    s = synth.scene("small", P=P, F=3)
+    dcol, dlang, ddepth = synth.upstream_grads(s, depth=True)
+    ref = refcuda.Ref(3)
+    r = ref.forward(s)
+    gr = ref.backward(dcol, dlang, ddepth)
+    o = helpers.run_forward(s)
+    _check_forward(s, r, o)
+    _check_backward(helpers.run_backward(s, o, dcol, dlang, ddepth), gr, what="P=%d" % P)
+
+
 @pytest.mark.parametrize("cam", CAMS, ids=CAM_IDS)
 @pytest.mark.parametrize("name,F", [("tiny", 3), ("small", 6)])
 def test_rotated_cameras_forward_bit_exact_and_backward(synth, name, F, cam):
