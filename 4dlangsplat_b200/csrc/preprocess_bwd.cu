@@ -393,7 +393,8 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
 // view-dependent basis values (backward.cu:41-126) and the masked colour gradient, so a batch of B views needs
 // 3 floats per view and Gaussian, not 48 per Gaussian and rank, to cross the interconnect (dist.GradBucket lowrank_sh).
 // slots: B records of `stride` floats: [0..2] camera position, [3] 1.0 if the slot holds a view, [4..] (P,3) dL_dRGB.
-__global__ void __launch_bounds__(256)
+constexpr int SGE_THREADS = 128;  // 128 x 49 words of staging = 25 KB of static shared memory
+__global__ void __launch_bounds__(SGE_THREADS)
 sh_grad_expand_kernel(int P, int D, int M, int B, const float* __restrict__ means3D, const float* __restrict__ slots,
                       size_t stride, float* __restrict__ dL_dsh, int accumulate) {
   pdl_grid_sync();
@@ -437,7 +438,38 @@ sh_grad_expand_kernel(int P, int D, int M, int B, const float* __restrict__ mean
     }
   }
   float* out = dL_dsh + (size_t)idx * M * 3;
-  if (M == 16) {  // 12 x 16-byte accesses per Gaussian, like preprocess_bwd's own SH stores
+  if (M == 16) {
+    // A warp's 32 rows of 192 bytes are contiguous: they go through shared memory (row stride 49 words, conflict-free
+    // both ways) and leave as coalesced 16-byte stores, instead of twelve 16-byte stores per thread at a 192-byte lane
+    // stride (32 sectors per instruction).  The last, partial warp of the array stores directly.
+    __shared__ float s_out[SGE_THREADS * 49];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g0 = blockIdx.x * SGE_THREADS + warp * 32;
+    if (g0 + 32 <= P) {
+      float* row = s_out + threadIdx.x * 49;
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        row[3 * k] = dsh[k].x;
+        row[3 * k + 1] = dsh[k].y;
+        row[3 * k + 2] = dsh[k].z;
+      }
+      __syncwarp();
+      float4* dst = reinterpret_cast<float4*>(dL_dsh + (size_t)g0 * 48);
+      const float* src = s_out + warp * 32 * 49;
+#pragma unroll
+      for (int i = 0; i < 12; ++i) {
+        const uint32_t j = lane + 32 * i;            // 16-byte group of the warp's block; a row is twelve of them
+        const uint32_t g = __umulhi(j, 357913942u);  // j / 12
+        const float* q = src + g * 49 + (j - g * 12) * 4;
+        float4 v = make_float4(q[0], q[1], q[2], q[3]);
+        if (accumulate) {
+          const float4 c = dst[j];
+          v = make_float4(c.x + v.x, c.y + v.y, c.z + v.z, c.w + v.w);
+        }
+        dst[j] = v;
+      }
+      return;
+    }
     float4* o4 = reinterpret_cast<float4*>(out);
     const float* f = reinterpret_cast<const float*>(dsh);
 #pragma unroll
@@ -468,7 +500,7 @@ cudaError_t launch_sh_grad_expand(int P, int D, int M, int B, const float* means
                                   float* dL_dsh, int accumulate, cudaStream_t st) {
   if (P == 0 || B == 0) return cudaSuccess;
   count_launch();
-  launch_pdl(sh_grad_expand_kernel, dim3(cdiv(P, 256)), dim3(256), 0, st, P, D, M, B, means3D, slots, stride, dL_dsh,
+  launch_pdl(sh_grad_expand_kernel, dim3(cdiv(P, SGE_THREADS)), dim3(SGE_THREADS), 0, st, P, D, M, B, means3D, slots, stride, dL_dsh,
              accumulate);
   return cudaGetLastError();
 }
