@@ -67,7 +67,8 @@ typedef struct FdlsLayout {
   size_t ranges;    /* uint2[tiles] */
   size_t tile_max_contrib; /* u32[tiles]: max n_contrib over the tile's pixels (lets backward skip the tail) */
   size_t tile_start;       /* u32[tiles+1]: exclusive scan of the per-tile instance counts (binning_algo 0) */
-  size_t tile_cursor;      /* u32[tiles]: per-tile counters / scatter cursors (binning_algo 0) */
+  size_t tile_cursor;      /* u32[tiles]: per-tile instance totals (binning_algo 0).  fdls_backward reuses it: afterwards it
+                              holds the tiles ordered deepest-first, the launch order of the compositor backward */
   /* binning */
   size_t keys_alt; /* u64[capacity] ping-pong partner of `keys` */
   size_t keys;     /* u64[capacity] sorted keys after the forward (reference: point_list_keys) */
