@@ -123,9 +123,12 @@ __device__ __forceinline__ void walk(unsigned long long ws, unsigned long long w
                                      const uint32_t* __restrict__ order, const uint32_t* __restrict__ offsets,
                                      const int* __restrict__ radii, const float4* __restrict__ rec, int gx, int gy,
                                      uint32_t* wcnt, const uint32_t* blockbase, uint32_t* __restrict__ point_list,
-                                     uint64_t* __restrict__ keys, long long capacity, int lane) {
+                                     uint64_t* __restrict__ keys, long long capacity, int lane, int& start) {
+  // start: position of the span's first Gaussian; < 0 = not known yet (found by the 32-ary search, four dependent
+  // rounds of loads, and handed back so that a second walk of the same span starts at once)
   if (ws >= we) return;
-  for (int g0 = first_pos_above(offsets, V, ws, lane);; g0 += 32) {
+  if (start < 0) start = first_pos_above(offsets, V, ws, lane);
+  for (int g0 = start;; g0 += 32) {
     const int pos = g0 + lane;
     uint32_t idx = 0, depth_bits = 0, j0 = 0, j1 = 0, packed = 0, magic = 0;
     bool past = pos >= V;
@@ -250,7 +253,8 @@ part_count_kernel(int P, int T, const uint32_t* __restrict__ num_rendered,
   unsigned long long ws, we;
   int V;
   pt_span(num_rendered, depth_hist, P, warp, ws, we, V);
-  walk<false>(ws, we, V, order, offsets, radii, rec, gx, gy, pt_smem, nullptr, nullptr, nullptr, 0, lane);
+  int start = -1;
+  walk<false>(ws, we, V, order, offsets, radii, rec, gx, gy, pt_smem, nullptr, nullptr, nullptr, 0, lane, start);
   __syncthreads();
   uint32_t* row = table + (size_t)blockIdx.x * T;
   for (int t = tid; t < T; t += PT_THREADS) row[t] = cnt_get(pt_smem, t);
@@ -320,7 +324,9 @@ part_scatter_kernel(int P, int T, const uint32_t* __restrict__ num_rendered,
   int V;
   pt_span(num_rendered, depth_hist, P, warp, ws, we, V);
   // walk 1: per-warp tile counts (same as kernel A)
-  walk<false>(ws, we, V, order, offsets, radii, rec, gx, gy, pt_smem + warp * words, nullptr, nullptr, nullptr, 0, lane);
+  int start = -1;
+  walk<false>(ws, we, V, order, offsets, radii, rec, gx, gy, pt_smem + warp * words, nullptr, nullptr, nullptr, 0, lane,
+              start);
   __syncthreads();
   // counts -> exclusive prefix across the warps of this CTA (in place); global base of the CTA per tile
   const uint32_t* row = table + (size_t)blockIdx.x * T;
@@ -339,7 +345,7 @@ part_scatter_kernel(int P, int T, const uint32_t* __restrict__ num_rendered,
   __syncthreads();
   // walk 2: the running counters now start at each warp's prefix -> final slots
   walk<true>(ws, we, V, order, offsets, radii, rec, gx, gy, pt_smem + warp * words, blockbase, point_list, keys,
-             capacity, lane);
+             capacity, lane, start);
 }
 
 // tile_scan_kernel lives in binning_scan below: exclusive scan over tile totals -> tile_start, ranges, R
