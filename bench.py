@@ -772,10 +772,17 @@ def train_line(a, rank, world, local, warmup, name, n_views, steps):
         R_staged = r.get("R_staged") or r["R"]
         bytes_rb = (44 + 4 * s.F) * R_staged + (24 + 4 * s.F) * HW + (48 + 4 * s.F) * s.P
         ach = bytes_rb / (bwd[1] * 1e-3) / 1e9 if bwd[1] > 0 else 0.0
+        # round 1 counted all R instances of the forward (the reference's backward walks them all); kept beside the
+        # staged-instance figure so that the two rounds' fractions can be compared on one byte model
+        bytes_all = (44 + 4 * s.F) * r["R"] + (24 + 4 * s.F) * HW + (48 + 4 * s.F) * s.P
+        ach_all = bytes_all / (bwd[1] * 1e-3) / 1e9 if bwd[1] > 0 else 0.0
         line["roofline"] = {"bound": "hbm", "kernel": "render_bwd", "achieved": round(ach, 1), "peak": pk["hbm_gbs"],
                             "unit": "GB/s", "frac": round(ach / pk["hbm_gbs"], 4), "traffic": None,
                             "peak_source": pk_kind, "algorithmic_bytes_per_launch": int(bytes_rb),
-                            "instances_staged": int(R_staged), "avg_launch_ms": round(bwd[1], 4)}
+                            "instances_staged": int(R_staged), "avg_launch_ms": round(bwd[1], 4),
+                            "all_instances_model": {"algorithmic_bytes_per_launch": int(bytes_all),
+                                                    "achieved": round(ach_all, 1),
+                                                    "frac": round(ach_all / pk["hbm_gbs"], 4)}}
         names = ["preprocess", "scan", "duplicate", "sort", "tile_ranges", "render"]
         line["stages_ms"] = dict(zip(names, [round(float(x), 4) for x in r["stage_ms"]]))
         line["stages_ms"].update({"bwd_zero": round(bwd[0], 4), "render_bwd": round(bwd[1], 4), "preprocess_bwd": round(bwd[2], 4)})
