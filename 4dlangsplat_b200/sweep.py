@@ -90,7 +90,8 @@ def render_sweep(render_fns, n_streams=3, sync_to_caller=True, front_priority=Fa
     be consumed on the stream it was issued on (`i mod n_streams`) until the generator is exhausted.
     front_priority (off by default) runs each frame's stage 1 (preprocess, depth sort, scan) on a high-priority stream
     so that its small grids are placed ahead of an older frame's pending compositor CTAs: 3600 -> 3750 frames/s on
-    cfg2 in most runs, but 3240 in one of five, so it is left as an option.
+    cfg2 in most runs of the first round-2 kernels, but 3240 in one of five; with the final kernels 5120 -> 4800 in
+    every run (four of four), so it stays an option that is off.
     """
     from collections import deque
 
