@@ -229,7 +229,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, language_fe
                                  scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
                                  dL_dout_color, dL_dout_language_feature, dL_dout_depth, sh, degree, campos, geomBuffer,
                                  R, binningBuffer, imageBuffer, debug, include_feature, want=None, out=None,
-                                 accumulate=False, sh_rgb_out=None):
+                                 accumulate=False, sh_rgb_out=None, sh_rgb_header=False):
     """RasterizeGaussiansBackwardCUDA (rasterize_points.cu:131-235).  Returns (dL_dmeans2D, dL_dcolors,
     dL_dlanguage_feature, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations).
     `want` (an addition; None = all, like the reference): 9 booleans in that order -- gradients not wanted are neither
@@ -237,7 +237,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, language_fe
     `out` (an addition): 9 optional tensors in that order to write into instead of allocating; with `accumulate` the
     kernels add to every output (caller-provided ones must hold the running sum, fresh ones are zero-filled here).
     `sh_rgb_out`: optional (P,3) tensor that receives the masked colour gradient (FdlsBwdArgs.dL_dsh_rgb), the
-    view-dependent factor of the rank-1 SH gradient; see sh_grad_expand."""
+    view-dependent factor of the rank-1 SH gradient; see sh_grad_expand.  `sh_rgb_header`: the kernel also writes the
+    slot header {campos, 1.0} into the four floats in front of sh_rgb_out (FdlsBwdArgs.sh_rgb_header)."""
     lib = _lib.load()
     means3D = _prep(means3D, "means3D")
     dev = means3D.device
@@ -296,6 +297,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, language_fe
     a.bwd_algo = 1 if os.environ.get("FDLS_RENDER_BWD", "mma") == "shfl" else 0
     a.accumulate = int(bool(accumulate))
     a.dL_dsh_rgb = dp(sh_rgb_out)
+    a.sh_rgb_header = int(bool(sh_rgb_header and sh_rgb_out is not None))
     if profile["bwd"] is not None:
         a.stage_events = profile["bwd"]
     _lib.check(lib.fdls_backward(C.byref(a), _stream(dev)), "fdls_backward")

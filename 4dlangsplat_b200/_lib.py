@@ -69,6 +69,7 @@ class FdlsBwdArgs(C.Structure):
         ("bwd_algo", C.c_int32),
         ("accumulate", C.c_int32),
         ("dL_dsh_rgb", _f32p),
+        ("sh_rgb_header", C.c_int32),
     ]
 
 

@@ -11,6 +11,7 @@ struct BwdOut {
   float* means3D; float* means2D; float* sh; float* colors; float* lang; float* opacity; float* scales; float* rots;
   float* cov3D; float* conic; float* depths;
   float* sh_rgb;  // (P,3) dL_dRGB after the clamp mask: the view-dependent factor of the rank-1 SH gradient (never ACC)
+  int sh_rgb_header;  // also write {campos, 1.0f} into sh_rgb[-4 .. -1] (the slot header of sh_grad_expand)
 };
 
 // forward.cu:118-152 recomputed (the forward does not keep cov3D; it is 30 flops)
@@ -106,6 +107,12 @@ preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ mean
   } else {
 #pragma unroll
     for (int k = 0; k < 16; ++k) g[k] = 0.f;
+  }
+  if (o.sh_rgb && o.sh_rgb_header && idx == 0) {
+    o.sh_rgb[-4] = s_cam[0];
+    o.sh_rgb[-3] = s_cam[1];
+    o.sh_rgb[-2] = s_cam[2];
+    o.sh_rgb[-1] = 1.0f;
   }
   if (o.sh_rgb) {  // backward.cu:53-56: clamped channels pass no gradient to the SH coefficients
     const uint8_t cl = vis ? clamped[idx] : (uint8_t)0;
@@ -509,7 +516,8 @@ cudaError_t launch_preprocess_bwd(const FdlsBwdArgs* a, const ViewParams& vp, co
                                   const float4* grad_rec, cudaStream_t st) {
   if (a->P == 0) return cudaSuccess;
   BwdOut o = {a->dL_dmeans3D, a->dL_dmeans2D, a->dL_dsh, a->dL_dcolors, a->dL_dlanguage, a->dL_dopacity,
-              a->dL_dscales, a->dL_drotations, a->dL_dcov3D, a->dL_dconic, a->dL_ddepths, a->dL_dsh_rgb};
+              a->dL_dscales, a->dL_drotations, a->dL_dcov3D, a->dL_dconic, a->dL_ddepths, a->dL_dsh_rgb,
+              a->sh_rgb_header};
   const int grid = cdiv(a->P, 256);
   const size_t pb_smem = (size_t)256 * 49 * sizeof(float);  // staged SH rows (M == 16)
   count_launch();

@@ -122,7 +122,8 @@ class _RasterizeGaussians(torch.autograd.Function):
                     b.zero_if_fresh()
         grads = _guarded(
             lambda *args: _C.rasterize_gaussians_backward(*args, want=want, out=out, accumulate=acc,
-                                                          sh_rgb_out=sh_rgb), native_args,
+                                                          sh_rgb_out=sh_rgb, sh_rgb_header=sh_rgb is not None),
+            native_args,
             rs.debug, "snapshot_bw.dump", "\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
         for b in owners:
             b.fresh = False

@@ -73,6 +73,7 @@ class GradBucket:
         if lowrank_sh is not None:
             self.sh_all = self.flat[self.numel:].view(n_slots, self.sh_stride)
             self.sh_local = self.sh_all[rank * self.sh_local_n:(rank + 1) * self.sh_local_n]
+            self.sh_slot_views = [self.sh_local[i][4:].view(-1, 3) for i in range(self.sh_local_n)]  # (P,3) of each slot
             self.sh_grad = torch.zeros_like(lowrank_sh)
             self.sh_used, self.sh_means, self.sh_degree, self.sh_work = 0, None, 0, None
             self._one = torch.ones(1, dtype=torch.float32, device=dev)
@@ -110,11 +111,10 @@ class GradBucket:
         """Called by the rasterizer's backward: the (P,3) array of this rank's next view slot; records the camera."""
         if self.sh_used >= self.sh_local_n:
             raise RuntimeError("GradBucket(lowrank_sh): more views on this rank than n_views / world_size allows")
-        slot = self.sh_local[self.sh_used]
-        slot[:4].copy_(torch.cat([campos.reshape(3), self._one]))  # header: camera position, valid flag
+        view = self.sh_slot_views[self.sh_used]  # the slot's header (camera, valid flag) is written by the backward kernel
         self.sh_used += 1
         self.sh_means, self.sh_degree = means3D, int(degree)
-        return slot[4:].view(-1, 3)
+        return view
 
     def zero_if_fresh(self):
         if self.fresh:

@@ -182,6 +182,10 @@ typedef struct FdlsBwdArgs {
    * multi-view / multi-GPU step can keep 3 floats per view and Gaussian and expand them once with
    * fdls_sh_grad_expand instead of writing, accumulating and all-reducing 3*M floats per Gaussian; pass dL_dsh = null. */
   float* dL_dsh_rgb;
+  /* non-zero (with dL_dsh_rgb): the library also writes the slot header fdls_sh_grad_expand reads -- the view's camera
+   * position and the valid flag 1.0f -- into the four floats directly in FRONT of dL_dsh_rgb, so the caller does not
+   * have to launch copies for it. */
+  int32_t sh_rgb_header;
 } FdlsBwdArgs;
 #define FDLS_BWD_EVENTS 4
 
