@@ -223,7 +223,11 @@ scan_onepass_kernel(int P, const uint32_t* __restrict__ in, const uint32_t* __re
       const int j = j0 - lane;
       unsigned long long w = SCAN_FLAG_INC;  // lanes before tile 0 read as "inclusive 0"
       if (j >= 0) {
-        do w = vs[j]; while ((w >> 32) == 0);
+        uint32_t polls = 0;
+        do {
+          w = vs[j];
+          if (++polls > (1u << 26)) __trap();  // a predecessor that never publishes must fail loudly, not hang the GPU
+        } while ((w >> 32) == 0);
       }
       const uint32_t inc = __ballot_sync(0xffffffffu, (w & SCAN_FLAG_INC) != 0);
       const int stop = __ffs(inc) - 1;  // nearest predecessor that already knows its inclusive value (-1: none)
