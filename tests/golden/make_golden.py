@@ -19,15 +19,17 @@ for p in (ROOT, os.path.join(ROOT, "oracle")):
     if p not in sys.path:
         sys.path.insert(0, p)
 
-CASES = [("tiny", 3, (1.0, 1.0, 1.0)), ("tiny", 6, (0.0, 0.0, 0.0))]
+# (scene, F, background, camera pose of synth.POSES or None = identity).  The rotated case pins the expression trees of
+# transformPoint4x3 / computeCov2D, which are exact whatever the FMA contraction when the view matrix is the identity.
+CASES = [("tiny", 3, (1.0, 1.0, 1.0), None), ("tiny", 6, (0.0, 0.0, 0.0), None), ("tiny", 3, (1.0, 1.0, 1.0), "rot2")]
 
 
 def main(outdir):
     import refcuda
     synth = importlib.import_module("4dlangsplat_b200.synth")
     os.makedirs(outdir, exist_ok=True)
-    for name, F, bg in CASES:
-        s = synth.scene(name, F=F, bg=bg)
+    for name, F, bg, pose in CASES:
+        s = synth.scene(name, F=F, bg=bg, **({"pose": pose} if pose else {}))
         dcol, dlang, ddepth = synth.upstream_grads(s, depth=True)
         ref = refcuda.Ref(F)
         r = ref.forward(s)
@@ -46,7 +48,7 @@ def main(outdir):
             g_means2D=n(g.means2D), g_conic=n(g.conic), g_opacity=n(g.opacity), g_colors=n(g.colors), g_lang=n(g.lang),
             g_depths=n(g.depths), g_means3D=n(g.means3D), g_cov3D=n(g.cov3D), g_sh=n(g.sh), g_scales=n(g.scales),
             g_rots=n(g.rots))
-        path = os.path.join(outdir, "ref_%s_f%d.npz" % (name, F))
+        path = os.path.join(outdir, "ref_%s%s_f%d.npz" % (name, "-" + pose if pose else "", F))
         np.savez_compressed(path, **out)
         print(path, "R=%d visible=%d" % (r.R, int(vis.sum())), os.path.getsize(path), "bytes")
 

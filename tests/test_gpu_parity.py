@@ -585,14 +585,15 @@ def test_gradient_bucket_sink_equals_autograd_accumulation(synth, fdls, lowrank)
     assert not fdls._C.grad_sinks
 
 
-@pytest.mark.parametrize("F", [3, 6])
-def test_against_committed_golden_vectors(synth, F):
-    """The product path against tests/golden/ref_tiny_f{F}.npz (outputs of the reference CUDA build, committed): the
-    same bars as above, without needing oracle/_ref at run time."""
+@pytest.mark.parametrize("F,pose", [(3, None), (6, None), (3, "rot2")], ids=["f3", "f6", "f3-rot2"])
+def test_against_committed_golden_vectors(synth, F, pose):
+    """The product path against tests/golden/ref_tiny[-pose]_f{F}.npz (outputs of the reference CUDA build, committed):
+    the same bars as above, without needing oracle/_ref at run time."""
     import os
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_tiny_f%d.npz" % F)
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden",
+                        "ref_tiny%s_f%d.npz" % ("-" + pose if pose else "", F))
     gold = np.load(path)
-    s = synth.scene("tiny", F=F, bg=(1.0, 1.0, 1.0) if F == 3 else (0.0, 0.0, 0.0))
+    s = synth.scene("tiny", F=F, bg=(1.0, 1.0, 1.0) if F == 3 else (0.0, 0.0, 0.0), **({"pose": pose} if pose else {}))
     o = helpers.run_forward(s)
     T = lambda a: torch.as_tensor(np.ascontiguousarray(a)).cuda()
     assert o.R == int(gold["R"])

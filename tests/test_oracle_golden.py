@@ -24,7 +24,8 @@ def _scene_of(path, synth):
     name, f = os.path.basename(path)[4:-4].rsplit("_f", 1)
     F = int(f)
     bg = (1.0, 1.0, 1.0) if F == 3 else (0.0, 0.0, 0.0)  # tests/golden/make_golden.py CASES
-    return synth.scene(name, F=F, bg=bg)
+    name, _, pose = name.partition("-")  # "tiny-rot2": the camera pose of synth.POSES
+    return synth.scene(name, F=F, bg=bg, **({"pose": pose} if pose else {}))
 
 
 def test_golden_fixtures_present():
