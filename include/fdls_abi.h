@@ -68,7 +68,8 @@ typedef struct FdlsLayout {
   size_t tile_max_contrib; /* u32[tiles]: max n_contrib over the tile's pixels (lets backward skip the tail) */
   size_t tile_start;       /* u32[tiles+1]: exclusive scan of the per-tile instance counts (binning_algo 0) */
   size_t tile_cursor;      /* u32[tiles]: per-tile instance totals (binning_algo 0).  fdls_backward reuses it: afterwards it
-                              holds the tiles ordered deepest-first, the launch order of the compositor backward */
+                              holds the tiles ordered deepest-first, the launch order of the compositor backward (so two
+                              fdls_backward calls on the SAME image workspace must not overlap on the GPU) */
   /* binning */
   size_t keys_alt; /* u64[capacity] ping-pong partner of `keys` */
   size_t keys;     /* u64[capacity] sorted keys after the forward (reference: point_list_keys) */
