@@ -33,8 +33,12 @@ __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+#ifndef RF_MIN_CTAS
+#define RF_MIN_CTAS 5
+#endif
+// 5 CTAs per SM: 48 registers (no spills) and 5 x 38.9 KB of shared memory
 template <int F>
-__global__ void __launch_bounds__(RF_THREADS)
+__global__ void __launch_bounds__(RF_THREADS, RF_MIN_CTAS)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                   const float4* __restrict__ rec, int W, int H, int gx, const float* __restrict__ bg_color,
                   float* __restrict__ final_T, uint32_t* __restrict__ n_contrib, uint32_t* __restrict__ tile_max_contrib,
