@@ -50,8 +50,11 @@ __device__ __forceinline__ void put4(float4* p, float4 v) {
   *p = v;
 }
 
+#ifndef FDLS_PB_MINBLOCKS
+#define FDLS_PB_MINBLOCKS 3  // 80 registers (~200 B of spills), 3 CTAs per SM: the accumulate variant (3 of 4 views) is latency-bound
+#endif
 template <bool VEC_SH, bool ACC>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, FDLS_PB_MINBLOCKS)
 preprocess_bwd_kernel(int P, int D, int M, int F, const float* __restrict__ means3D, const int* __restrict__ radii,
                       const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
                       const float* __restrict__ scales, const float* __restrict__ rotations,
